@@ -1,0 +1,264 @@
+"""TEST INFRASTRUCTURE ONLY — drives the *unmodified* reference engine headlessly.
+
+This file exists to pin `oracle/headless.py` against the reference's own code and to
+generate the golden vectors under `tests/golden/`. It only works in the build
+container, where `/root/reference` is mounted; nothing on the GPU box imports it
+(tests that need it skip when the reference is absent).
+
+How: the monolith imports tkinter/matplotlib at module top
+(`qmmx_monolithic.py:5-13`), neither of which is installed.  We register dummy modules
+for those names in `sys.modules`, import `qmmx_monolithic`, build a
+`MonolithicEngine` on an in-memory SQLite DB and drive `evaluate_entry`
+(`qmmx_monolithic.py:1492-1771`) with a transcription of the live loop's tick order
+and exit block (`qmmx_monolithic.py:2927-3016`, `3044-3115`).
+"""
+from __future__ import annotations
+
+import json
+import os
+import sqlite3
+import sys
+import types
+from types import SimpleNamespace
+
+REFERENCE_DIR = os.environ.get("QMMX_REFERENCE_DIR", "/root/reference")
+
+
+def reference_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_DIR, "qmmx_monolithic.py"))
+
+
+_q = None
+_captured_messages: list = []
+
+
+def _stub_gui_modules() -> None:
+    class _Any:
+        def __init__(self, *a, **k):
+            pass
+
+        def __getattr__(self, name):
+            return _Any()
+
+        def __call__(self, *a, **k):
+            return _Any()
+
+    def mod(name, **attrs):
+        m = types.ModuleType(name)
+        m.__dict__.update(attrs)
+        m.__getattr__ = lambda attr: _Any  # type: ignore[attr-defined]
+        sys.modules[name] = m
+        return m
+
+    class Tk:  # `class QMMXApp(tk.Tk)` executes at import time
+        def __init__(self, *a, **k):
+            pass
+
+    def showinfo(title, msg=None, *a, **k):
+        _captured_messages.append(("info", title, msg))
+
+    def showerror(title, msg=None, *a, **k):
+        _captured_messages.append(("error", title, msg))
+
+    tk = mod("tkinter", Tk=Tk, END="end", Text=_Any, StringVar=_Any, BooleanVar=_Any)
+    ttk = mod("tkinter.ttk")
+    mb = mod("tkinter.messagebox", showinfo=showinfo, showerror=showerror)
+    st = mod("tkinter.scrolledtext")
+    tk.ttk, tk.messagebox, tk.scrolledtext = ttk, mb, st
+    mpl = mod("matplotlib")
+    be = mod("matplotlib.backends")
+    bt = mod("matplotlib.backends.backend_tkagg", FigureCanvasTkAgg=_Any)
+    pp = mod("matplotlib.pyplot")
+    mpl.backends, be.backend_tkagg, mpl.pyplot = be, bt, pp
+
+
+def load_reference():
+    """Import the reference monolith with GUI modules stubbed; returns the module."""
+    global _q
+    if _q is not None:
+        return _q
+    if not reference_available():
+        raise RuntimeError(f"reference not present under {REFERENCE_DIR}")
+    for name in ("tkinter", "matplotlib"):
+        if name not in sys.modules:
+            _stub_gui_modules()
+            break
+    if REFERENCE_DIR not in sys.path:
+        sys.path.insert(0, REFERENCE_DIR)
+    import qmmx_monolithic as q  # noqa: E402
+
+    _q = q
+    return q
+
+
+def make_engine(levels, settings=None):
+    """Fresh reference `MonolithicEngine` on sqlite :memory: with `levels` and `settings`.
+
+    levels: list of {"color","type","index","price"} dicts (any order; the engine reads
+    them back through `load_levels`, i.e. ORDER BY color, level_type, level_index).
+    settings: {key: str(value)} written with `settings_set` before the engine is built.
+    """
+    q = load_reference()
+    conn = sqlite3.connect(":memory:")
+    q.db_init(conn)
+    q.replace_levels(conn, levels)
+    for k, v in (settings or {}).items():
+        q.settings_set(conn, k, str(v))
+    eng = q.MonolithicEngine(conn)
+    eng.model = None
+    return q, conn, eng
+
+
+class _CoefModel:
+    """Stands in for a fitted sklearn LogisticRegression: predict_proba = sigma(b + w.x).
+
+    Used only when sklearn itself is not wanted; `make_sklearn_model` builds a real one.
+    """
+
+    def __init__(self, coef, intercept):
+        self.coef = [float(c) for c in coef]
+        self.intercept = float(intercept)
+
+    def predict_proba(self, X):
+        import math
+
+        out = []
+        for x in X:
+            z = self.intercept
+            for w, xi in zip(self.coef, x):
+                z = z + w * float(xi)
+            p = 1.0 / (1.0 + math.exp(-z))
+            out.append([1.0 - p, p])
+        return out
+
+
+def make_sklearn_model(coef, intercept):
+    """A real sklearn LogisticRegression with hand-set coefficients (no fit)."""
+    import numpy as np
+    from sklearn.linear_model import LogisticRegression
+
+    m = LogisticRegression()
+    m.classes_ = np.array([0, 1])
+    m.coef_ = np.asarray(coef, dtype=np.float64).reshape(1, -1)
+    m.intercept_ = np.asarray([intercept], dtype=np.float64)
+    m.n_features_in_ = m.coef_.shape[1]
+    return m
+
+
+def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy_w=None,
+                         disable_policy_gate=True, steps_per_day=390):
+    """Run the real `evaluate_entry` over one close series with the live loop's order.
+
+    Transcribes `_engine_loop` (`qmmx_monolithic.py:2927-3016`, `3044-3115`) with the
+    frozen choices of SURVEY.md Appendix A: tick i = close i, now_ms = 60000*i,
+    evaluate_entry called once, escalation off, policy minutes = i mod steps_per_day.
+
+    lr_model: None, or an object with predict_proba (set as engine.model).
+    policy_w: None or {"go_long": [7], "go_short": [7], "skip": [7]} or a per-day list of
+              such dicts; the reference `OnlinePolicy` scores them.
+    Returns dict(codes=[...str per step], trades=[...], touch_counts=...).
+    """
+    q, conn, eng = make_engine(levels, settings)
+    eng.model = lr_model if not isinstance(lr_model, list) else None
+    policy = q.OnlinePolicy()
+    cool_s = eng.Q_SIGNAL_COOLDOWN_S
+    codes, trades = [], []
+    pos = None
+    for i, price in enumerate(closes):
+        price = float(price)
+        day = i // steps_per_day
+        if isinstance(lr_model, list):
+            eng.model = lr_model[min(day, len(lr_model) - 1)]
+        prev_price = eng.state.last_price
+        now_ms = 60000 * i
+        eng.state.last_ts_ms = now_ms  # always fresh (Appendix A [CHOICE])
+        ok, code, msg, extras = eng.evaluate_entry(price, prev_price, now_ms, True)
+        eng.state.last_price = price
+        if prev_price is not None and price != prev_price:
+            eng.state.last_direction = "up" if price > prev_price else "down"
+        step_code = code if not isinstance(code, int) else f"INT_{code}"
+        if step_code == "CONF_LOW":
+            # sub-reason lives in the policy_events row the gate just wrote (M:1629, 1733, 1746)
+            row = conn.execute("SELECT features_json FROM policy_events ORDER BY id DESC LIMIT 1").fetchone()
+            sub = json.loads(row[0]).get("reason", "CONF_LOW")
+            step_code = sub if sub in ("ML_CONF_LOW", "COMBINED_LOW") else "CONF_LOW"
+        if eng.state.open_trade_id is not None:
+            side, stop, target = pos["side"], pos["stop"], pos["target"]
+            reason = None
+            if side == "long":
+                if price <= stop:
+                    reason = "STOP"
+                elif price >= target:
+                    reason = "TARGET"
+            else:
+                if price >= stop:
+                    reason = "STOP"
+                elif price <= target:
+                    reason = "TARGET"
+            if reason is not None:
+                tid = eng.state.open_trade_id
+                eng.close_trade(tid, price, reason)
+                row = conn.execute("SELECT pnl FROM trades WHERE id=?", (tid,)).fetchone()
+                eng.state.set_cooldown(now_ms, cool_s)
+                trades.append(dict(entry_bar=pos["entry_bar"], exit_bar=i, side=side,
+                                   level=pos["level"], reason=reason, entry=pos["entry"],
+                                   exit=price, pnl=float(row[0])))
+                pos = None
+        elif ok:
+            pass_gate = True
+            if not disable_policy_gate:
+                w = policy_w
+                if isinstance(w, list):
+                    w = w[min(day, len(w) - 1)]
+                lvl_price = float(extras["level_price"])
+                side = extras["side"]
+                approach = "from_below" if side == "long" else "from_above"
+                cluster = [lv for lv in eng.levels_cache
+                           if abs(float(lv["price"]) - lvl_price) <= 0.6]
+                x = policy.build_features(proximity_abs=abs(price - lvl_price), volume_trend=0.0,
+                                          approach=approach, confluence=(len(cluster) > 1),
+                                          minutes_since_open=i % steps_per_day)
+                if w is not None:
+                    policy.w_entry = {k: list(v) for k, v in w.items()}
+                scores = policy.score_entry(x)
+                chosen = "go_long" if side == "long" else "go_short"
+                pass_gate = (scores.get(chosen, 0.5) >= 0.60) and (scores.get("skip", 0.0) < 0.55)
+            if not pass_gate:
+                step_code = "ONLINE_POLICY"
+            else:
+                eng.open_trade(extras["side"], price, extras["stop"], extras["target"], "sim")
+                pos = dict(side=extras["side"], stop=extras["stop"], target=extras["target"],
+                           entry=price, entry_bar=i, level=tuple(extras["level"]))
+        codes.append(step_code)
+    if pos is not None:
+        last = float(closes[-1])
+        mtm = (last - pos["entry"]) if pos["side"] == "long" else (pos["entry"] - last)
+        trades.append(dict(entry_bar=pos["entry_bar"], exit_bar=-1, side=pos["side"],
+                           level=pos["level"], reason="OPEN", entry=pos["entry"], exit=last,
+                           pnl=0.0, mtm=mtm))
+    return dict(codes=codes, trades=trades,
+                touch_counts=dict(eng.state.level_touch_counts))
+
+
+def run_reference_monte_carlo(bars, levels, settings=None, **kw):
+    """Unbound `QMMXApp.simulate_monte_carlo` (`qmmx_monolithic.py:3353-3538`); returns text."""
+    q, conn, eng = make_engine(levels, settings)
+    eng.recent_bars = [dict(b) for b in bars]
+    fake = SimpleNamespace(engine=eng, conn=conn, _log_ui=lambda *a, **k: None)
+    _captured_messages.clear()
+    q.QMMXApp.simulate_monte_carlo(fake, **kw)
+    return _captured_messages[-1] if _captured_messages else None
+
+
+def run_reference_last_bars(bars, levels, settings=None, **kw):
+    """Unbound `QMMXApp.simulate_last_bars` (`qmmx_monolithic.py:3540-3699`).
+
+    Returns (messagebox tuple, list of audit rows (phase, code, message)).
+    """
+    q, conn, eng = make_engine(levels, settings)
+    eng.recent_bars = [dict(b) for b in bars]
+    fake = SimpleNamespace(engine=eng, conn=conn, _log_ui=lambda *a, **k: None)
+    _captured_messages.clear()
+    q.QMMXApp.simulate_last_bars(fake, **kw)
+    rows = conn.execute("SELECT phase, code, message FROM audit_log WHERE phase='SIM' ORDER BY id").fetchall()
+    return (_captured_messages[-1] if _captured_messages else None), rows

@@ -1,0 +1,56 @@
+"""Differential test: oracle/headless.py vs the UNMODIFIED reference engine, step by step.
+Runs only where /root/reference is mounted (the build container); skipped on the GPU box."""
+import numpy as np
+import pytest
+
+from oracle import headless as H
+from oracle import ref_harness as rh
+from oracle.make_golden import settings_for
+from qmmx_monolithic_monte_carlo_b200 import fixtures as F
+
+pytestmark = pytest.mark.skipif(not rh.reference_available(), reason="reference not mounted")
+
+
+def _check(levels, params, closes, lr=None, pol=None):
+    lv = H.sort_levels(levels)
+    P = H.Params(**params)
+    models = [rh.make_sklearn_model(m.coef, m.intercept) for m in lr] if lr else None
+    for j in range(closes.shape[1]):
+        ref = rh.drive_reference_path(closes[:, j], levels, settings_for(params), lr_model=models,
+                                      policy_w=pol, disable_policy_gate=P.disable_policy_gate)
+        o = H.run_path(closes[:, j], lv, P, lr=lr, policy=pol)
+        assert [H.ENTRY_CODES[c] for c in o.codes] == ref["codes"]
+        assert len(o.trades) == len(ref["trades"])
+        for a, b in zip(ref["trades"], o.trades):
+            assert (a["entry_bar"], a["exit_bar"], a["reason"], a["level"], a["side"]) == \
+                   (b.entry_bar, b.exit_bar, H.EXIT_CODES[b.reason], lv[b.level].key, ("long", "short")[b.side])
+            assert a["pnl"] == b.pnl and a["entry"] == b.entry and a["exit"] == b.exit
+        assert {lv[i].key: t for i, t in enumerate(o.touch_counts) if t} == ref["touch_counts"]
+
+
+@pytest.mark.parametrize("seed", [101, 102, 103])
+def test_random_params_against_reference(seed):
+    rng = np.random.default_rng(seed)
+    params = dict(contact_prox=float(rng.choice([0.05, 0.1, 0.2])),
+                  stop_padding=float(rng.choice([0.1, 0.35, 0.85])),
+                  tp_padding=float(rng.choice([0.15, 0.25, 0.5])),
+                  cooldown_s=int(rng.choice([0, 8, 60, 300, 900])),
+                  q_min_prob=float(rng.choice([0.5, 0.6, 0.75])),
+                  use_blend=bool(rng.integers(2)), enable_veto=bool(rng.integers(2)),
+                  disable_policy_gate=bool(rng.integers(2)))
+    lr = [H.LRModel(rng.normal(0, 0.5, 4).tolist(), float(rng.normal(0.5, 0.5)))]
+    pol = [{k: rng.normal(0.3, 0.8, 7).tolist() for k in ("go_long", "go_short", "skip")}]
+    closes = F.host_gbm_closes(6, 390, seed=seed, round_cents=bool(rng.integers(2)),
+                               sigma=float(rng.choice([0.05, 0.15, 0.4])))
+    _check(F.levels_30(), params, closes, lr=lr, pol=pol)
+
+
+def test_lr_contract_matches_sklearn_predict_proba():
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        coef = rng.normal(0, 1, 4)
+        b = float(rng.normal())
+        m = rh.make_sklearn_model(coef, b)
+        x = [1.0, abs(648.76 - (648.76 - 0.35)), float(rng.integers(1, 4)), float(rng.integers(2))]
+        ours = H.lr_prob(H.LRModel(coef.tolist(), b), *x)
+        assert ours == pytest.approx(float(m.predict_proba([x])[0][1]), abs=2e-16, rel=2e-16)
