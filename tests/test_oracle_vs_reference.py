@@ -53,4 +53,4 @@ def test_lr_contract_matches_sklearn_predict_proba():
         m = rh.make_sklearn_model(coef, b)
         x = [1.0, abs(648.76 - (648.76 - 0.35)), float(rng.integers(1, 4)), float(rng.integers(2))]
         ours = H.lr_prob(H.LRModel(coef.tolist(), b), *x)
-        assert ours == pytest.approx(float(m.predict_proba([x])[0][1]), abs=2e-16, rel=2e-16)
+        assert ours == pytest.approx(float(m.predict_proba([x])[0][1]), abs=1e-15)  # scipy expit vs 1/(1+exp(-z)): last-bit differences only
