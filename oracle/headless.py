@@ -103,6 +103,25 @@ class PathResult:
     touch_counts: List[int] = field(default_factory=list)
 
 
+def dot_py312(w: Sequence[float], x: Sequence[float]) -> float:
+    """`OnlinePolicy._dot` = builtin `sum(wi*xi ...)` (M:334-335) as evaluated by CPython >= 3.12,
+    whose float `sum` is Neumaier-compensated (Python/bltinmodule.c).  Spelled out so the contract
+    does not depend on the interpreter running the oracle; tests assert it equals `sum` here."""
+    f = 0 + w[0] * x[0]
+    c = 0.0
+    for wi, xi in zip(w[1:], x[1:]):
+        v = wi * xi
+        t = f + v
+        if abs(f) >= abs(v):
+            c += (f - t) + v
+        else:
+            c += (v - t) + f
+        f = t
+    if c and math.isfinite(c):
+        f += c
+    return f
+
+
 def sigmoid_policy(x: float) -> float:
     """M:20-26."""
     if x < -50:
@@ -176,8 +195,8 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
     prox = float(P.contact_prox)
     qmin = float(P.q_min_prob or 0.0)
     # M:1714-1719 weight normalisation
-    w_rules = float(P.w_rules or 0.7)
-    w_ml = float(P.w_ml or 0.3)
+    w_rules = float(P.w_rules)   # `float(settings_get(..) or 0.7)`: the `or` guards the *string*, "0" stays 0
+    w_ml = float(P.w_ml)
     s = w_rules + w_ml
     if s <= 0:
         w_rules, w_ml, s = 1.0, 0.0, 1.0
@@ -325,8 +344,8 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
                       1.0 if confl else 0.0, min(1.0, (i % P.steps_per_day) / 390.0)]
                 if w is None:
                     w = {"go_long": [0.0] * 7, "go_short": [0.0] * 7, "skip": [0.0] * 7}
-                s_go = sigmoid_policy(sum(wi * xi for wi, xi in zip(w["go_long" if side == 0 else "go_short"], xf)))
-                s_skip = sigmoid_policy(sum(wi * xi for wi, xi in zip(w["skip"], xf)))
+                s_go = sigmoid_policy(dot_py312(w["go_long" if side == 0 else "go_short"], xf))
+                s_skip = sigmoid_policy(dot_py312(w["skip"], xf))
                 pass_gate = (s_go >= 0.60) and (s_skip < 0.55)
             if not pass_gate:
                 code = E["ONLINE_POLICY"]

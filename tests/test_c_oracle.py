@@ -1,0 +1,120 @@
+"""oracle/qmmx_oracle.c (C restatement) against oracle/headless.py and the reference golden vectors."""
+import random
+
+import numpy as np
+import pytest
+
+from oracle import c_oracle as CO
+from oracle import headless as H
+from qmmx_monolithic_monte_carlo_b200 import abi
+from qmmx_monolithic_monte_carlo_b200 import fixtures as F
+from tests.golden_util import load_engine_cases, oracle_inputs
+
+ENGINE_CASES = load_engine_cases()
+
+
+def c_inputs(case):
+    lv, P, lr, pol = oracle_inputs(case)
+    params = abi.make_params(**case["params"])
+    lr_a = np.array([list(m.coef) + [m.intercept] for m in lr]) if lr else None
+    pol_a = np.array([[w["go_long"], w["go_short"], w["skip"]] for w in pol]) if pol else None
+    return lv, params, lr_a, pol_a
+
+
+@pytest.mark.parametrize("case", ENGINE_CASES, ids=[c["name"] for c in ENGINE_CASES])
+def test_c_oracle_matches_reference_golden(case):
+    lv, params, lr_a, pol_a = c_inputs(case)
+    r = CO.run_paths(case["close"], [l.price for l in lv], [l.solid for l in lv], params,
+                     lr=lr_a, policy=pol_a, want_codes=True, max_trades=64, n_threads=2)
+    assert np.array_equal(r["codes"], case["codes"])
+    for j in range(case["paths"]):
+        gt = case["trades"][j]
+        assert r["counts"][j] == len(gt)
+        for g, t in zip(gt, r["trades"][j]):
+            assert (g["entry_bar"], g["exit_bar"], g["side"], g["level"], g["reason"]) == \
+                   (t["entry_bar"], t["exit_bar"], t["side"], t["level_id"], t["reason"])
+            assert np.float32(g["pnl"]) == t["pnl"] and np.float32(g["entry"]) == t["entry"]
+    a = r["agg"]
+    assert a.n_paths == case["paths"] and a.n_steps == case["paths"] * case["steps"]
+    assert list(a.entry_hist) == np.bincount(case["codes"].ravel(), minlength=20).tolist()
+    closed = [t for tr in case["trades"] for t in tr if t["reason"] != 3]
+    assert a.n_trades == len(closed) and a.n_wins == sum(1 for t in closed if t["pnl"] > 0)
+    assert a.sum_pnl == pytest.approx(sum(t["pnl"] for t in closed), rel=1e-12, abs=1e-12)
+
+
+def test_c_oracle_hl_exit_mode_matches_headless():
+    rng = np.random.default_rng(3)
+    g = abi.make_gbm(sub_steps=4)
+    c, h, l = CO.gen_gbm(77, 0, 64, 390, g, ohlc=True)
+    assert np.all(h >= c) and np.all(l <= c) and np.all(h >= l)
+    lv = H.sort_levels(F.levels_30())
+    P = H.Params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True)
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True)
+    r = CO.run_paths(c, [x.price for x in lv], [x.solid for x in lv], params, high=h, low=l,
+                     want_codes=True, max_trades=64)
+    for j in range(0, 64, 7):
+        o = H.run_path(c[:, j], lv, P, high=h[:, j], low=l[:, j])
+        assert o.codes == r["codes"][:, j].tolist()
+        assert len(o.trades) == r["counts"][j]
+        for a, b in zip(o.trades, r["trades"][j]):
+            assert (a.entry_bar, a.exit_bar, a.side, a.level, a.reason) == \
+                   (b["entry_bar"], b["exit_bar"], b["side"], b["level_id"], b["reason"])
+            assert np.float32(a.pnl) == b["pnl"]
+
+
+def test_dot_py312_is_builtin_sum():
+    rnd = random.Random(4)
+    for _ in range(2000):
+        w = [rnd.gauss(0, 1) * 10 ** rnd.randint(-8, 8) for _ in range(7)]
+        x = [rnd.gauss(0, 1) for _ in range(7)]
+        expect = sum(a * b for a, b in zip(w, x))   # CPython >= 3.12: Neumaier
+        assert H.dot_py312(w, x) == expect
+        wa, xa = np.array(w), np.array(x)
+        assert CO.lib().oq_dot_py312(wa.ctypes.data, xa.ctypes.data, 7) == expect
+
+
+def test_confidence_c_equals_python():
+    rnd = random.Random(5)
+    for _ in range(5000):
+        d, s, tc, prox = rnd.random() * 0.12, rnd.random() < 0.5, rnd.randint(1, 5), rnd.choice([0.05, 0.1, 0.2])
+        assert CO.lib().oq_confidence(d, int(s), tc, prox) == H.compute_confidence(d, s, tc, prox)
+
+
+# Random123 known-answer vectors for philox4x32-10 (kat_vectors in the Random123 distribution)
+PHILOX_KAT = [
+    ([0, 0, 0, 0], [0, 0], [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]),
+    ([0xffffffff] * 4, [0xffffffff] * 2, [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]),
+    ([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0],
+     [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]),
+]
+
+
+@pytest.mark.parametrize("ctr,key,out", PHILOX_KAT)
+def test_philox_known_answers(ctr, key, out):
+    assert CO.philox(ctr, key).tolist() == out
+
+
+def test_gbm_generator_statistics_and_sharding():
+    g = abi.make_gbm()
+    c, _, _ = CO.gen_gbm(20250829, 0, 4096, 390, g)
+    lr = np.diff(np.log(np.vstack([np.full((1, 4096), g.s0, dtype=np.float64), c.astype(np.float64)])), axis=0)
+    sd = 0.15 * np.sqrt(1 / (252 * 390))
+    assert abs(lr.std() / sd - 1) < 0.01 and abs(lr.mean()) < 4 * sd / np.sqrt(lr.size)
+    # path ids are global: a shard starting at offset 1000 reproduces columns 1000.. of the full run
+    c2, _, _ = CO.gen_gbm(20250829, 1000, 96, 390, g)
+    assert np.array_equal(c2, c[:, 1000:1096])
+
+
+def test_bootstrap_generator_uses_window_returns():
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    c, h, l = CO.gen_bootstrap(9, 0, 32, 2 * 390, window, 5)
+    rc = (window[1:, 3] / window[:-1, 3]).astype(np.float32)
+    prev = np.vstack([np.full((1, 32), window[-1, 3], dtype=np.float32), c[:-1]])
+    ratio = c / prev
+    # every step's close ratio is one of the window's 39 ratios (up to fp32 rounding of the product)
+    d = np.abs(ratio[..., None] - rc[None, None, :]).min(axis=-1)
+    assert d.max() < 2e-7
+    assert np.all(h >= l)
