@@ -79,6 +79,8 @@ enum { QMMX_EXIT_STOP = 0, QMMX_EXIT_TARGET, QMMX_EXIT_ESCALATE, QMMX_EXIT_OPEN 
 #define QMMX_F_USE_BLEND            (1u << 2)  /* USE_BLEND                                        */
 #define QMMX_F_DISABLE_POLICY_GATE  (1u << 3)  /* DISABLE_POLICY_GATE (1 = OnlinePolicy bypassed)  */
 #define QMMX_F_EXIT_ON_HL           (1u << 4)  /* exits tested on bar low/high, stop first (M:3621-3636) */
+#define QMMX_F_TINY_PRICES          (1u << 5)  /* prices below 2^-5 may occur: evaluate the +-1e-9 direction guard
+                                                  (M:1529-1537) in float64 on every tick instead of the fp32 shortcut */
 
 typedef struct qmmx_params {
     uint32_t struct_size;      /* = sizeof(qmmx_params) */
@@ -179,9 +181,15 @@ int  qmmx_set_pnl_hist_range(qmmx_ctx* ctx, double lo, double hi);
 /* host arrays, fp32, layout [step][path]; high/low may be NULL (close-only) */
 int  qmmx_upload_bars(qmmx_ctx* ctx, const float* close, const float* high, const float* low,
                       int64_t paths, int32_t steps);
-/* same, but the arrays already live on this ctx's device (e.g. torch tensors); not copied */
+/* same, but the arrays already live on this ctx's device (e.g. torch tensors); not copied.
+ * pitch = row stride in elements (>= paths) */
 int  qmmx_bind_device_bars(qmmx_ctx* ctx, const float* d_close, const float* d_high, const float* d_low,
-                           int64_t paths, int32_t steps);
+                           int64_t paths, int32_t steps, int64_t pitch);
+/* device pointers of the resident bars (NULL when a field is absent) */
+int  qmmx_device_bars(qmmx_ctx* ctx, float** d_close, float** d_high, float** d_low, int64_t* pitch);
+/* page-lock / unlock a caller-owned host buffer so uploads run at full PCIe rate */
+int  qmmx_pin_host(qmmx_ctx* ctx, void* ptr, size_t bytes);
+int  qmmx_unpin_host(qmmx_ctx* ctx, void* ptr);
 int  qmmx_download_bars(qmmx_ctx* ctx, float* close, float* high, float* low);
 /* Philox4x32-10 generators, counter = (global path id, step group), key = seed: results do not
  * depend on how paths are split across GPUs.  path_offset = first global path id of this shard. */
@@ -200,6 +208,10 @@ int  qmmx_gen_bootstrap(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int6
  *   codes_out          [steps][paths] entry code per step or NULL (parity mode, combo 0 only) */
 int  qmmx_run_scan(qmmx_ctx* ctx, qmmx_agg* agg_out, qmmx_trade* trades_out, int32_t* trade_counts_out,
                    int32_t max_trades_per_path, uint8_t* codes_out);
+/* End to end from HOST bars: path chunks are uploaded on a copy stream while the previous chunk is
+ * scanned (double-buffered device staging); aggregates only.  chunk_paths <= 0 picks a default. */
+int  qmmx_run_scan_host(qmmx_ctx* ctx, const float* close, const float* high, const float* low,
+                        int64_t paths, int32_t steps, int64_t chunk_paths, qmmx_agg* agg_out);
 /* generate GBM closes in registers and scan them in the same kernel (no bar traffic to HBM) */
 int  qmmx_run_fused_gbm(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
                         const qmmx_gbm* gbm, qmmx_agg* agg_out);
@@ -234,6 +246,15 @@ int  qmmx_run_jitter(qmmx_ctx* ctx, const double* high, const double* low, int32
                      const double* replay_normals, const double* replay_uniforms,
                      double* out_total_r, double* out_max_dd, int32_t* out_wins, int32_t* out_losses,
                      int32_t* out_opens);
+
+/* Host-side check of the exact price-classification tables the kernels use (no device needed):
+ * for each fp32 price, level_table/level_brute = touched level by table lookup / by the float64 brute force
+ * of M:1543-1545 (-1 = TOO_FAR); conf_mask bit b = confidence gate passes for touch bucket b (tc<=1, 2, >=3)
+ * by threshold compare, conf_brute = the same by float64 compute_confidence; near_table/near_brute = bit j set
+ * when p is inside level j's contact window (|price_j - p| <= prox). Any output may be NULL. */
+int  qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
+                         const float* p, int64_t n, int32_t* level_table, int32_t* level_brute,
+                         uint8_t* conf_mask, uint8_t* conf_brute, uint64_t* near_table, uint64_t* near_brute);
 
 /* device time of the last run's kernels in ms (CUDA events on the ctx stream) */
 int  qmmx_last_timing(qmmx_ctx* ctx, float* ms);

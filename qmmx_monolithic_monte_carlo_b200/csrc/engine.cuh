@@ -2,11 +2,12 @@
 // (qmmx_monolithic.py:1492-1771), the live loop's exit block (M:2966-3014) and the OnlinePolicy gate
 // (M:3046-3109).  Semantics frozen in SURVEY.md Appendix A; checked bit-for-bit against oracle/.
 //
-// Arithmetic contract: prices are fp32 in memory and are evaluated in float64 exactly like CPython
-// wherever a decision is taken on the contact path.  The file is compiled with --fmad=false so no
-// multiply-add is ever contracted; the per-step fast path replaces the O(L) float64 nearest-level search
-// by the exact host-built classification tables (tables.h) and float64 threshold compares by
-// equivalent fp32 compares against directed-rounded thresholds.
+// Arithmetic contract: prices are fp32 in memory and the reference evaluates them in float64.  Every
+// decision that depends only on the price (nearest level, proximity, latch release, confidence threshold,
+// stop/target touch) is taken with fp32 compares against thresholds the host derived EXACTLY from the
+// float64 predicates (tables.h); the logistic gates use host-evaluated float64 probabilities (same libm as
+// CPython) and a float64 Neumaier dot product on the device.  The file is compiled with --fmad=false so no
+// multiply-add is ever contracted.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -17,14 +18,14 @@
 
 namespace qmmx {
 
+constexpr int U_NPATHS = 0, U_NSTEPS = 1, U_NTRADES = 2, U_NWINS = 3, U_NOPEN = 4, U_NOVERFLOW = 5;
+constexpr int U_ENTRY = 6, U_EXIT = U_ENTRY + QMMX_N_ENTRY_CODES, U_HIST = U_EXIT + QMMX_N_EXIT_CODES;
+constexpr int D_SUM_PNL = 0, D_SUM_PNL2 = 1, D_SUM_PATH2 = 2, D_SUM_MTM = 3;
+
 // ---- shared-memory block state -------------------------------------------------------------------------
 struct BlockShared {
-    // tables (subset of DevTables the kernels need)
-    int32_t L, Z, ncell, pad0;
-    float glo, inv_w;
-    double price[kMaxLevels];
-    uint8_t solid[kMaxLevels];
-    uint8_t confl06[kMaxLevels];
+    int32_t L, Z, ncell, shift, obase, pad0, pad1, pad2;
+    DevLevel lev[kMaxLevels];
     float zhi[kMaxZones];
     uint8_t zlev[kMaxZones];
     DevCombo combo;
@@ -34,31 +35,31 @@ struct BlockShared {
     double xmax, xnegmin;
     // per-thread touch counters: 4-bit saturating, 64 levels -> 8 words per thread, [word][thread]
     uint32_t touch[8 * kThreads];
-    // grid cells follow (dynamic)
-    uint8_t cell[1];
+    // grid cells follow (dynamic, ncell bytes rounded up to 16)
+    alignas(16) uint8_t cell[16];
 };
 
-constexpr int U_NPATHS = 0, U_NSTEPS = 1, U_NTRADES = 2, U_NWINS = 3, U_NOPEN = 4, U_NOVERFLOW = 5;
-constexpr int U_ENTRY = 6, U_EXIT = U_ENTRY + QMMX_N_ENTRY_CODES, U_HIST = U_EXIT + QMMX_N_EXIT_CODES;
-constexpr int D_SUM_PNL = 0, D_SUM_PNL2 = 1, D_SUM_PATH2 = 2, D_SUM_MTM = 3;
-
 struct EngineGlobals {            // read-only, global memory
-    const double* lr;  int n_lr;      // [n_lr][5]
-    const double* pol; int n_pol;     // [n_pol][3][7]
+    const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit tc (dir up) / bit 16+tc (dir down) = ML gate FAILS; null = no model
+    const double* mlprob;         // [n_days][kMaxLevels][2][16] P(win) for blend mode; null when unused
+    int32_t n_days;
+    const double* pol;            // [n_pol][3][7]
+    int32_t n_pol;
+    double z_go, z_skip;          // sigmoid(z) >= 0.60 <=> z >= z_go ; sigmoid(z) < 0.55 <=> z < z_skip
     double hist_lo, hist_inv_w;
     int32_t steps;
     // parity-mode outputs (may be null)
     qmmx_trade* trades; int32_t* tcounts; int32_t max_trades; uint8_t* codes;
-    int64_t paths;                    // row stride of codes
+    int64_t paths;                // row stride of codes
 };
 
 __device__ __forceinline__ void smem_inc(unsigned long long* p, unsigned long long v = 1ull) { atomicAdd(p, v); }
 
 // OnlinePolicy._dot under CPython >= 3.12 (Neumaier-compensated builtin sum), M:334-335
-__device__ inline double dot_py312(const double* __restrict__ w, const double* x) {
+__device__ __noinline__ double dot_py312(const double* __restrict__ w, const double* x) {
     double f = 0.0 + w[0] * x[0];
     double c = 0.0;
-#pragma unroll
+#pragma unroll 1
     for (int i = 1; i < QMMX_POLICY_DIM; ++i) {
         const double v = w[i] * x[i];
         const double t = f + v;
@@ -69,13 +70,7 @@ __device__ inline double dot_py312(const double* __restrict__ w, const double* x
     return f;
 }
 
-__device__ inline double sigmoid_policy(double x) {   // M:20-26
-    if (x < -50) return 0.0;
-    if (x > 50) return 1.0;
-    return 1.0 / (1.0 + exp(-x));
-}
-
-__device__ inline double compute_confidence(double dist, bool solid, int tc, double pmax) {   // M:1415-1427
+__device__ __forceinline__ double compute_confidence(double dist, bool solid, int tc, double pmax) {   // M:1415-1427
     double base = 1.0 - (dist / pmax);
     if (!(base > 0.0)) base = 0.0;
     base += solid ? 0.08 : 0.02;
@@ -102,7 +97,9 @@ struct PathEngine {
     float lo_thr, hi_thr;  // exit when low <= lo_thr or high >= hi_thr (directed-rounded stop/target)
     float entry;
     int entry_bar;
-    uint64_t latch;
+    uint32_t latch_lo, latch_hi;
+    // per-path tallies of the frequent codes (everything else goes straight to shared-memory counters)
+    uint32_t n_over, n_conf, n_ml;
     // per-path accumulators
     double pnl, pnl2, mtm;
     int ntr;
@@ -113,20 +110,10 @@ struct PathEngine {
         path = path_;
         prev = __int_as_float(0x7fc00000);
         last_dir = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
-        latch = 0ull; pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
+        latch_lo = 0u; latch_hi = 0u; n_over = 0u; n_conf = 0u; n_ml = 0u;
+        pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) S.touch[w * kThreads + tid] = 0u;
-    }
-
-    __device__ __forceinline__ int touch_get(int k) const {
-        return (S.touch[(k >> 3) * kThreads + tid] >> ((k & 7) * 4)) & 15;
-    }
-    __device__ __forceinline__ int touch_inc(int k) {
-        uint32_t& w = S.touch[(k >> 3) * kThreads + tid];
-        const int sh = (k & 7) * 4;
-        int v = (w >> sh) & 15;
-        if (v < 15) { ++v; w = (w & ~(15u << sh)) | ((uint32_t)v << sh); }
-        return v;
     }
 
     __device__ __forceinline__ void record(int entry_bar_, int exit_bar, int side, int reason, int k,
@@ -142,81 +129,103 @@ struct PathEngine {
         ++ntr;
     }
 
-    // contact path: price is within CONTACT_PROX of level k (rare: a few % of steps)
+    // rare: a neighbouring level is latched while this one is touched -> keep it only while p is still inside
+    // that level's own contact window (M:1572-1576)
+    __device__ __noinline__ static void keep_neighbours(const BlockShared& S, float pf, uint32_t klo, uint32_t khi,
+                                                        uint32_t& llo, uint32_t& lhi) {
+        while (klo) {
+            const int j = __ffs((int)klo) - 1; klo &= klo - 1;
+            if (pf >= S.lev[j].wlo && pf <= S.lev[j].whi) llo |= 1u << j;
+        }
+        while (khi) {
+            const int j = __ffs((int)khi) - 1; khi &= khi - 1;
+            if (pf >= S.lev[32 + j].wlo && pf <= S.lev[32 + j].whi) lhi |= 1u << j;
+        }
+    }
+
+    // rare: blend gate (M:1711-1742) in float64; returns true when the blended score is below Q_MIN_PROB
+    __device__ __noinline__ static bool blend_fails(const BlockShared& S, const EngineGlobals& G, int k, float pf,
+                                                    int tc, int d, int day) {
+        const DevCombo& C = S.combo;
+        const double lp = S.lev[k].price;
+        const double conf = compute_confidence(fabs(lp - (double)pf), (S.lev[k].flags & kLvSolid) != 0, tc, C.pmax);
+        double mlp = conf;
+        if (G.mlprob) {
+            const int dd = day < G.n_days ? day : G.n_days - 1;
+            mlp = G.mlprob[(((size_t)dd * kMaxLevels + k) * 2 + (d - 1)) * 16 + tc];
+        }
+        const double blended = C.wr * conf + C.wm * mlp;
+        return blended < C.qmin;
+    }
+
+    // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
+    __device__ __noinline__ static bool policy_passes(const BlockShared& S, const EngineGlobals& G, int k, float pf,
+                                                      int side, int i) {
+        const DevCombo& C = S.combo;
+        if (G.n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
+        const double lp = S.lev[k].price;
+        double x[QMMX_POLICY_DIM];
+        const double pa = fabs((double)pf - lp);
+        const double tod = (double)(i % C.spd) / 390.0;
+        x[0] = 1.0; x[1] = pa < 1.0 ? pa : 1.0; x[2] = 0.0;
+        x[3] = side == 1 ? 1.0 : 0.0; x[4] = side == 0 ? 1.0 : 0.0;
+        x[5] = (S.lev[k].flags & kLvConfl06) ? 1.0 : 0.0; x[6] = tod < 1.0 ? tod : 1.0;
+        const int day = i / C.spd;
+        const double* w = G.pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < G.n_pol ? day : G.n_pol - 1);
+        const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x);
+        const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x);
+        return (z_side >= G.z_go) && (z_sk < G.z_skip);
+    }
+
+    // contact path: price is nearest to, and within CONTACT_PROX of, level k
     __device__ __forceinline__ int contact(int k, float pf, int d, int i) {
         const DevCombo& C = S.combo;
-        const double p = (double)pf;
-        const double lp = S.price[k];
-        const double dist = fabs(lp - p);
-        const uint64_t bit = 1ull << k;
-        int tc;
-        if (!(latch & bit)) { latch |= bit; tc = touch_inc(k); }           // M:1562-1566
-        else tc = touch_get(k);
-        uint64_t others = latch & ~bit;                                     // M:1572-1576
-        while (others) {
-            const int j = __ffsll((long long)others) - 1;
-            others &= others - 1;
-            if (fabs(S.price[j] - p) > C.prox) latch &= ~(1ull << j);
-        }
-        if (tc >= C.overtouch) return QMMX_LEVEL_OVERTOUCHED;                // M:1579
-        const double conf = compute_confidence(dist, S.solid[k] != 0, tc, C.pmax);
-        if (conf < C.qmin) return QMMX_CONF_LOW;                             // M:1628
-        const int side = (d == 1) ? 0 : 1;                                   // M:1645
-        double stop, target;                                                 // M:1669-1674
-        if (side == 0) { stop = lp - C.sp; target = lp + C.tp; }
-        else { stop = lp + C.sp; target = lp - C.tp; }
-        // M:1677-1705 soft veto: volume slope is identically 0 without per-bar volume => never vetoes
-        const int day = i / C.spd;
-        double mlp = conf;
-        bool ok_ml = true;
-        if (!(C.flags & QMMX_F_DISABLE_ML_GATE) && G.n_lr > 0) {             // M:1454-1466
-            const double* m = G.lr + QMMX_LR_DIM * (day < G.n_lr ? day : G.n_lr - 1);
-            const double distf = fabs(lp - stop);
-            double z = m[4];
-            z = z + m[0] * 1.0;
-            z = z + m[1] * distf;
-            z = z + m[2] * (double)tc;
-            z = z + m[3] * (d == 1 ? 1.0 : 0.0);
-            const double prob = 1.0 / (1.0 + exp(-z));
-            ok_ml = prob >= C.qmin;
-            mlp = prob;
-        }
+        const DevLevel& Lk = S.lev[k];
+        // latch + touch count (M:1562-1576)
+        const uint32_t blo = (k < 32) ? (1u << k) : 0u, bhi = (k < 32) ? 0u : (1u << (k - 32));
+        const bool isnew = ((latch_lo & blo) | (latch_hi & bhi)) == 0u;
+        const uint32_t klo = latch_lo & Lk.cand_lo, khi = latch_hi & Lk.cand_hi;
+        latch_lo = blo; latch_hi = bhi;
+        if (klo | khi) keep_neighbours(S, pf, klo, khi, latch_lo, latch_hi);
+        uint32_t& tw = S.touch[(k >> 3) * kThreads + tid];
+        const int sh = (k & 7) * 4;
+        const uint32_t word = tw;
+        int tc = (word >> sh) & 15;
+        if (isnew && tc < 15) { ++tc; tw = word + (1u << sh); }
+        if (tc >= C.overtouch) { ++n_over; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
+        const int b = (tc < 3 ? tc : 3) - 1;
+        if (!(pf >= Lk.cpass[b][0] && pf <= Lk.cpass[b][1])) { ++n_conf; return QMMX_CONF_LOW; }   // M:1628
+        const int side = d - 1;                                              // M:1645: up -> long(0), down -> short(1)
         if (C.flags & QMMX_F_USE_BLEND) {                                    // M:1730-1742
-            const double blended = C.wr * conf + C.wm * mlp;
-            if (blended < C.qmin) return QMMX_COMBINED_LOW;
-        } else if (!(C.flags & QMMX_F_DISABLE_ML_GATE) && !ok_ml) return QMMX_ML_CONF_LOW;   // M:1745-1755
+            if (blend_fails(S, G, k, pf, tc, d, i / C.spd)) { smem_inc(&S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
+        } else if (G.mlmask) {                                               // M:1454-1466, M:1745-1755
+            int day = i / C.spd; day = day < G.n_days ? day : G.n_days - 1;
+            const uint32_t m = __ldg(&G.mlmask[day * kMaxLevels + k]);
+            if ((m >> (side * 16 + tc)) & 1u) { ++n_ml; return QMMX_ML_CONF_LOW; }
+        }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
         if (!(C.flags & QMMX_F_DISABLE_POLICY_GATE)) {
-            double x[QMMX_POLICY_DIM];
-            const double pa = fabs(p - lp);
-            const double tod = (double)(i % C.spd) / 390.0;
-            x[0] = 1.0; x[1] = pa < 1.0 ? pa : 1.0; x[2] = 0.0;
-            x[3] = side == 1 ? 1.0 : 0.0; x[4] = side == 0 ? 1.0 : 0.0;
-            x[5] = S.confl06[k] ? 1.0 : 0.0; x[6] = tod < 1.0 ? tod : 1.0;
-            double s_go = 0.5, s_skip = 0.5;                                 // zero weights => sigmoid(0)
-            if (G.n_pol > 0) {
-                const double* w = G.pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < G.n_pol ? day : G.n_pol - 1);
-                s_go = sigmoid_policy(dot_py312(w + QMMX_POLICY_DIM * side, x));
-                s_skip = sigmoid_policy(dot_py312(w + QMMX_POLICY_DIM * 2, x));
-            }
-            if (!((s_go >= 0.60) && (s_skip < 0.55))) return QMMX_ONLINE_POLICY;
+            if (!policy_passes(S, G, k, pf, side, i)) { smem_inc(&S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
         }
-        // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick
+        // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
+        // p <= stop (float64, p fp32)  <=>  p <= round_down_fp32(stop);  p >= target  <=>  p >= round_up_fp32(target)
         pos = k | (side << 8);
         entry = pf; entry_bar = i;
-        if (side == 0) { lo_thr = __double2float_rd(stop); hi_thr = __double2float_ru(target); }
-        else { hi_thr = __double2float_ru(stop); lo_thr = __double2float_rd(target); }
+        const double lp = Lk.price;
+        if (side == 0) { lo_thr = __double2float_rd(lp - C.sp); hi_thr = __double2float_ru(lp + C.tp); }   // M:1669-1674
+        else { hi_thr = __double2float_ru(lp + C.sp); lo_thr = __double2float_rd(lp - C.tp); }
         return QMMX_OK_ENTRY;
     }
 
     __device__ __forceinline__ void do_exit(float pf, bool hit_lo, bool hit_hi, int i) {
         const DevCombo& C = S.combo;
         const int k = pos & 0xff, side = pos >> 8;
+        // long: stop below (tested first), target above; short: stop above (tested first), target below
         const int reason = (side == 0) ? (hit_lo ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET)
                                        : (hit_hi ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET);
         double exit_px = (double)pf;
         if (HL) {   // exit at the stop/target level itself (M:3636)
-            const double lp = S.price[k];
+            const double lp = S.lev[k].price;
             if (side == 0) exit_px = (reason == QMMX_EXIT_STOP) ? lp - C.sp : lp + C.tp;
             else exit_px = (reason == QMMX_EXIT_STOP) ? lp + C.sp : lp - C.tp;
         }
@@ -235,13 +244,27 @@ struct PathEngine {
         pos = -1;
     }
 
+    // price -> level index touched, or kFar (exact: see tables.h)
+    __device__ __forceinline__ uint32_t classify(float pf) const {
+        uint32_t v = S.cell[cell_of_bits(__float_as_int(pf), S.obase, S.shift, S.ncell)];
+        if (v == kMixed) {
+            int a = 0, b = S.Z - 1;
+            while (a < b) {
+                const int m = (a + b) >> 1;
+                if (pf <= S.zhi[m]) b = m; else a = m + 1;
+            }
+            v = S.zlev[a];
+        }
+        return v;
+    }
+
     // one tick: price pf = bar i's close (hh/ll = its high/low when HL)
     __device__ __forceinline__ void step(float pf, float hh, float ll, int i) {
         int code = QMMX_TOO_FAR;
         // direction (M:1529-1537) and last_direction update (M:2954-2955)
         int d;
         if (!TINY) {
-            // |p|,|prev| >= 2^-5 (guaranteed by the host): fp32 spacing > 2e-9, so the +-1e-9 guard band of
+            // |p|,|prev| >= 2^-5 (QMMX_F_TINY_PRICES unset): fp32 spacing > 1.8e-9, so the +-1e-9 guard band of
             // the reference cannot change any comparison and d doubles as the updated last_direction
             d = (pf > prev) ? 1 : ((pf < prev) ? 2 : last_dir);
         } else {
@@ -264,19 +287,8 @@ struct PathEngine {
             code = QMMX_DIR_UNKNOWN;                                         // M:1538
             smem_inc(&S.u[U_ENTRY + QMMX_DIR_UNKNOWN]);
         } else {
-            uint32_t v = S.cell[cell_of(pf, S.glo, S.inv_w, S.ncell)];
-            if (v == kMixed) {
-                int a = 0, b = S.Z - 1;
-                while (a < b) {
-                    const int m = (a + b) >> 1;
-                    if (pf <= S.zhi[m]) b = m; else a = m + 1;
-                }
-                v = S.zlev[a];
-            }
-            if (v != kFar) {                                                 // else TOO_FAR, M:1545
-                code = contact((int)v, pf, d, i);
-                smem_inc(&S.u[U_ENTRY + code]);
-            }
+            const uint32_t v = classify(pf);
+            if (v != kFar) code = contact((int)v, pf, d, i);                 // else TOO_FAR, M:1545
         }
         if (!TINY) last_dir = d;
         else if (prev == prev && pf != prev) last_dir = (pf > prev) ? 1 : 2;
@@ -314,7 +326,7 @@ __device__ __forceinline__ double warp_max(double v) {
     return v;
 }
 
-__device__ __forceinline__ void smem_max(double* addr, double v) {
+__device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
     unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
     unsigned long long old = *a;
     while (__longlong_as_double((long long)old) < v) {
@@ -324,32 +336,29 @@ __device__ __forceinline__ void smem_max(double* addr, double v) {
     }
 }
 
-__device__ __forceinline__ void global_max(double* addr, double v) {
-    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
-    unsigned long long old = *a;
-    while (__longlong_as_double((long long)old) < v) {
-        const unsigned long long assumed = old;
-        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(v));
-        if (old == assumed) break;
-    }
-}
-
-// add one finished path (active lanes only contribute non-neutral values) to the block aggregate
-__device__ __forceinline__ void block_accumulate(BlockShared& S, bool active, double pnl, double pnl2, double mtm) {
+// add one finished path per lane (inactive lanes contribute neutral values) to the block aggregate
+template <class Engine>
+__device__ __forceinline__ void warp_accumulate(BlockShared& S, bool active, const Engine& E) {
     const int lane = threadIdx.x & 31;
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
-    const double s1 = warp_sum(active ? pnl : 0.0);
-    const double s2 = warp_sum(active ? pnl2 : 0.0);
-    const double s3 = warp_sum(active ? pnl * pnl : 0.0);
-    const double s4 = warp_sum(active ? mtm : 0.0);
-    const double mx = warp_max(active ? pnl : neg_inf);
-    const double mn = warp_max(active ? -pnl : neg_inf);
+    const double s1 = warp_sum(active ? E.pnl : 0.0);
+    const double s2 = warp_sum(active ? E.pnl2 : 0.0);
+    const double s3 = warp_sum(active ? E.pnl * E.pnl : 0.0);
+    const double s4 = warp_sum(active ? E.mtm : 0.0);
+    const double mx = warp_max(active ? E.pnl : neg_inf);
+    const double mn = warp_max(active ? -E.pnl : neg_inf);
+    const unsigned n_over = __reduce_add_sync(0xffffffffu, active ? E.n_over : 0u);
+    const unsigned n_conf = __reduce_add_sync(0xffffffffu, active ? E.n_conf : 0u);
+    const unsigned n_ml = __reduce_add_sync(0xffffffffu, active ? E.n_ml : 0u);
     const unsigned n = __popc(__ballot_sync(0xffffffffu, active));
     if (lane == 0 && n) {
         atomicAdd(&S.d[D_SUM_PNL], s1); atomicAdd(&S.d[D_SUM_PNL2], s2);
         atomicAdd(&S.d[D_SUM_PATH2], s3); atomicAdd(&S.d[D_SUM_MTM], s4);
-        smem_max(&S.xmax, mx); smem_max(&S.xnegmin, mn);
+        atomic_max_f64(&S.xmax, mx); atomic_max_f64(&S.xnegmin, mn);
         smem_inc(&S.u[U_NPATHS], n);
+        if (n_over) smem_inc(&S.u[U_ENTRY + QMMX_LEVEL_OVERTOUCHED], n_over);
+        if (n_conf) smem_inc(&S.u[U_ENTRY + QMMX_CONF_LOW], n_conf);
+        if (n_ml) smem_inc(&S.u[U_ENTRY + QMMX_ML_CONF_LOW], n_ml);
     }
 }
 
@@ -360,13 +369,15 @@ __device__ inline void block_zero_agg(BlockShared& S) {
     if (threadIdx.x == 0) { S.xmax = neg_inf; S.xnegmin = neg_inf; }
 }
 
-// flush the block aggregate into the flat global buffer of `combo`; caller syncs before and after
+// flush the block aggregate into the flat global buffer of `combo`; caller syncs before
 __device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat, int combo, int steps) {
     unsigned long long* gu = flat + (size_t)combo * QMMX_AGG_SLOTS;
     double* gd = reinterpret_cast<double*>(gu + QMMX_AGG_NU);
     if (threadIdx.x == 0) {
-        // derived counters: n_steps, and the remainder code (TOO_FAR, or NOLEVELS without levels)
+        // derived counters: n_steps, OK entries (every opened position ends as a trade or as OPEN), and the
+        // remainder code (TOO_FAR, or NOLEVELS without levels)
         const unsigned long long nsteps = S.u[U_NPATHS] * (unsigned long long)steps;
+        S.u[U_ENTRY + QMMX_OK_ENTRY] = S.u[U_NTRADES] + S.u[U_NOPEN];
         unsigned long long others = 0;
         for (int c = 0; c < QMMX_N_ENTRY_CODES; ++c) others += S.u[U_ENTRY + c];
         S.u[U_NSTEPS] = nsteps;
@@ -379,23 +390,24 @@ __device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat,
     }
     if (threadIdx.x < QMMX_AGG_ND) { const double v = S.d[threadIdx.x]; if (v != 0.0) atomicAdd(&gd[threadIdx.x], v); }
     if (threadIdx.x == 0 && S.u[U_NPATHS]) {
-        global_max(&gd[QMMX_AGG_ND + 0], S.xmax);
-        global_max(&gd[QMMX_AGG_ND + 1], S.xnegmin);
+        atomic_max_f64(&gd[QMMX_AGG_ND + 0], S.xmax);
+        atomic_max_f64(&gd[QMMX_AGG_ND + 1], S.xnegmin);
     }
 }
 
-__device__ inline void block_load_tables(BlockShared& S, const DevTables* T) {
+__device__ inline void block_load_tables(BlockShared& S, const DevTables* __restrict__ T, const DevCombo* __restrict__ C) {
     if (threadIdx.x == 0) {
-        S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.glo = T->glo; S.inv_w = T->inv_w;
+        S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
+        S.combo = *C;
     }
-    for (int t = threadIdx.x; t < kMaxLevels; t += blockDim.x) {
-        S.price[t] = T->price[t]; S.solid[t] = T->solid[t]; S.confl06[t] = T->confl06[t];
-    }
+    const uint32_t* ls = reinterpret_cast<const uint32_t*>(T->lev);
+    uint32_t* ld = reinterpret_cast<uint32_t*>(S.lev);
+    for (int t = threadIdx.x; t < (int)(sizeof(DevLevel) * kMaxLevels / 4); t += blockDim.x) ld[t] = ls[t];
     for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) { S.zhi[t] = T->zhi[t]; S.zlev[t] = T->zlev[t]; }
-    const int n4 = (T->ncell + 3) / 4;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(T->cell);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(S.cell);
-    for (int t = threadIdx.x; t < n4; t += blockDim.x) dst[t] = src[t];
+    const int n16 = (T->ncell + 15) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(T->cell);
+    uint4* dst = reinterpret_cast<uint4*>(S.cell);
+    for (int t = threadIdx.x; t < n16; t += blockDim.x) dst[t] = src[t];
 }
 
 }  // namespace qmmx

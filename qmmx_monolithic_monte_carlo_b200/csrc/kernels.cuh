@@ -1,0 +1,386 @@
+// sm_100a kernels of libqmmx_mc: engine scan over resident bars, Philox path generators (GBM, block
+// bootstrap), fused generate+scan, batch logistic scoring and the reference jitter Monte Carlo.
+// Launch geometry: persistent CTAs (kBlocksPerSM per SM x 148 SMs) of 256 threads; each warp owns
+// 32 consecutive paths at a time, so one bar row is one coalesced 128-byte line per warp and step.
+#pragma once
+#include "engine.cuh"
+
+namespace qmmx {
+
+constexpr int kBlocksPerSM = 4;
+constexpr int kWarps = kThreads / 32;
+
+struct ScanArgs {
+    const float* close; const float* high; const float* low;   // [steps][pitch] fp32
+    int64_t pitch, paths;
+    int32_t steps, combo0, parity_combo;
+    const DevTables* tables; const DevCombo* combos;
+    unsigned long long* flat;
+    const uint32_t* mlmask; const double* mlprob;               // per combo: [n_days][64] / [n_days][64][2][16]
+    EngineGlobals G;
+};
+
+// ---- Philox4x32-10 (Salmon et al., SC'11) ---------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    return c;
+}
+
+// Box-Muller on two 32-bit draws (same operation order as oracle/qmmx_oracle.c; MUFU transcendentals)
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+    const float u1 = __fmul_rn(__fadd_rn(__uint2float_rn(a), 0.5f), 2.3283064365386963e-10f);
+    const float u2 = __fmul_rn(__fadd_rn(__uint2float_rn(b >> 8), 0.5f), 5.9604644775390625e-08f);
+    const float r = sqrtf(__fmul_rn(-2.0f, __logf(u1)));
+    const float ang = __fsub_rn(__fmul_rn(u2, 6.28318530717958648f), 3.14159265358979324f);
+    float s, c;
+    __sincosf(ang, &s, &c);
+    z0 = __fmul_rn(r, c); z1 = __fmul_rn(r, s);
+}
+
+struct GbmDev {
+    float s0, drift, vol;       // per sub-step log-drift and volatility
+    int32_t sub_steps, cents;
+    uint32_t k0, k1;
+    uint64_t path_offset;
+};
+
+__device__ __forceinline__ float round_cents(float s) { return __fdiv_rn(rintf(__fmul_rn(s, 100.0f)), 100.0f); }
+
+__device__ __forceinline__ void gbm_normals(const GbmDev& g, uint64_t gid, uint32_t group, float z[4]) {
+    const uint4 x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), group, 0u), g.k0, g.k1);
+    box_muller(x.x, x.y, z[0], z[1]);
+    box_muller(x.z, x.w, z[2], z[3]);
+}
+__device__ __forceinline__ float gbm_advance(const GbmDev& g, float S, float z) {
+    return __fmul_rn(S, __expf(__fadd_rn(g.drift, __fmul_rn(g.vol, z))));
+}
+
+// ---- engine scan over resident bars -------------------------------------------------------------------------
+template <bool HL, bool PARITY, bool TINY>
+__device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY>& E, const ScanArgs& A, int64_t path) {
+    constexpr int U = HL ? 2 : 4;
+    const size_t pitch = (size_t)A.pitch;
+    const float* pc = A.close + path;
+    const float* ph = HL ? A.high + path : nullptr;
+    const float* pl = HL ? A.low + path : nullptr;
+    const int steps = A.steps;
+    float c0[U], c1[U], h0[U], h1[U], l0[U], l1[U];
+    const int nfull = steps / (2 * U);
+    int i = 0;
+    if (nfull > 0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            c0[u] = __ldg(pc + (size_t)u * pitch);
+            if (HL) { h0[u] = __ldg(ph + (size_t)u * pitch); l0[u] = __ldg(pl + (size_t)u * pitch); }
+        }
+        for (int n = 0; n < nfull; ++n, i += 2 * U) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const size_t o = (size_t)(i + U + u) * pitch;
+                c1[u] = __ldg(pc + o);
+                if (HL) { h1[u] = __ldg(ph + o); l1[u] = __ldg(pl + o); }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) E.step(c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u);
+            if (n + 1 < nfull) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const size_t o = (size_t)(i + 2 * U + u) * pitch;
+                    c0[u] = __ldg(pc + o);
+                    if (HL) { h0[u] = __ldg(ph + o); l0[u] = __ldg(pl + o); }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) E.step(c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u);
+        }
+    }
+#pragma unroll 1
+    for (; i < steps; ++i) {
+        const size_t o = (size_t)i * pitch;
+        const float c = __ldg(pc + o);
+        E.step(c, HL ? __ldg(ph + o) : 0.f, HL ? __ldg(pl + o) : 0.f, i);
+    }
+}
+
+template <bool HL, bool PARITY, bool TINY>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) scan_kernel(const ScanArgs A) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    BlockShared& S = *reinterpret_cast<BlockShared*>(smem_raw);
+    const int combo = A.combo0 + blockIdx.y;
+    const DevCombo* C = A.combos + combo;
+    block_load_tables(S, A.tables + C->table, C);
+    block_zero_agg(S);
+    __syncthreads();
+    EngineGlobals G = A.G;
+    if (A.mlmask) G.mlmask = A.mlmask + (size_t)combo * G.n_days * kMaxLevels;
+    if (A.mlprob) G.mlprob = A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32;
+    if (!(S.combo.flags & (1u << 16))) G.mlmask = nullptr;
+    if (!(S.combo.flags & (1u << 17))) G.mlprob = nullptr;
+    if (PARITY && combo != A.parity_combo) { G.trades = nullptr; G.tcounts = nullptr; G.codes = nullptr; }
+    PathEngine<HL, PARITY, TINY> E(S, G, threadIdx.x);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t ntiles = (A.paths + 31) / 32;
+    for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kWarps) {
+        const int64_t path = tile * 32 + lane;
+        const bool active = path < A.paths;
+        E.reset(path);
+        if (active) { scan_path(E, A, path); E.finish(); }
+        __syncwarp();
+        warp_accumulate(S, active, E);
+    }
+    __syncthreads();
+    block_flush_agg(S, A.flat, combo, A.steps);
+}
+
+// ---- GBM generator (materialised bars) -------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) gen_gbm_kernel(float* __restrict__ close, float* __restrict__ high,
+                                                           float* __restrict__ low, int64_t pitch, int64_t paths,
+                                                           int32_t steps, const GbmDev g) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < paths; q += stride) {
+        const uint64_t gid = g.path_offset + (uint64_t)q;
+        float S = g.s0;
+        float z[4];
+        if (g.sub_steps == 1) {
+            for (int i = 0; i < steps; i += 4) {
+                gbm_normals(g, gid, (uint32_t)(i >> 2), z);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (i + u < steps) {
+                        S = gbm_advance(g, S, z[u]);
+                        __stcs(close + (size_t)(i + u) * pitch + q, g.cents ? round_cents(S) : S);
+                    }
+                }
+            }
+        } else {
+            for (int i = 0; i < steps; ++i) {
+                gbm_normals(g, gid, (uint32_t)i, z);
+                float hi = S, lo = S;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { S = gbm_advance(g, S, z[u]); hi = fmaxf(hi, S); lo = fminf(lo, S); }
+                const size_t o = (size_t)i * pitch + q;
+                __stcs(close + o, g.cents ? round_cents(S) : S);
+                if (high) __stcs(high + o, g.cents ? round_cents(hi) : hi);
+                if (low) __stcs(low + o, g.cents ? round_cents(lo) : lo);
+            }
+        }
+    }
+}
+
+// ---- fused GBM generate + scan: bars live in registers only -------------------------------------------------------
+template <bool HL>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const ScanArgs A, const GbmDev g) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    BlockShared& S = *reinterpret_cast<BlockShared*>(smem_raw);
+    const int combo = A.combo0 + blockIdx.y;
+    const DevCombo* C = A.combos + combo;
+    block_load_tables(S, A.tables + C->table, C);
+    block_zero_agg(S);
+    __syncthreads();
+    EngineGlobals G = A.G;
+    if (A.mlmask) G.mlmask = A.mlmask + (size_t)combo * G.n_days * kMaxLevels;
+    if (A.mlprob) G.mlprob = A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32;
+    if (!(S.combo.flags & (1u << 16))) G.mlmask = nullptr;
+    if (!(S.combo.flags & (1u << 17))) G.mlprob = nullptr;
+    PathEngine<HL, false, false> E(S, G, threadIdx.x);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t ntiles = (A.paths + 31) / 32;
+    const int steps = A.steps;
+    for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kWarps) {
+        const int64_t path = tile * 32 + lane;
+        const bool active = path < A.paths;
+        E.reset(path);
+        if (active) {
+            const uint64_t gid = g.path_offset + (uint64_t)path;
+            float P = g.s0;
+            float z[4];
+            if (!HL) {
+                for (int i = 0; i < steps; i += 4) {
+                    gbm_normals(g, gid, (uint32_t)(i >> 2), z);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (i + u < steps) {
+                            P = gbm_advance(g, P, z[u]);
+                            E.step(g.cents ? round_cents(P) : P, 0.f, 0.f, i + u);
+                        }
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int i = 0; i < steps; ++i) {
+                    gbm_normals(g, gid, (uint32_t)i, z);
+                    float hi = P, lo = P;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { P = gbm_advance(g, P, z[u]); hi = fmaxf(hi, P); lo = fminf(lo, P); }
+                    E.step(g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i);
+                }
+            }
+            E.finish();
+        }
+        __syncwarp();
+        warp_accumulate(S, active, E);
+    }
+    __syncthreads();
+    block_flush_agg(S, A.flat, combo, A.steps);
+}
+
+// ---- circular block bootstrap of a candle window ---------------------------------------------------------------
+constexpr int kMaxWindow = 1024;
+struct BootDev {
+    const float* ratios;        // [3][nret]: high, low, close of bar t over close of bar t-1
+    int32_t nret, block_len;
+    float s0;
+    uint32_t k0, k1;
+    uint64_t path_offset;
+};
+
+__global__ void __launch_bounds__(kThreads) gen_bootstrap_kernel(float* __restrict__ close, float* __restrict__ high,
+                                                                 float* __restrict__ low, int64_t pitch, int64_t paths,
+                                                                 int32_t steps, const BootDev g) {
+    __shared__ float rh[kMaxWindow], rl[kMaxWindow], rc[kMaxWindow];
+    for (int t = threadIdx.x; t < g.nret; t += blockDim.x) {
+        rh[t] = g.ratios[t]; rl[t] = g.ratios[g.nret + t]; rc[t] = g.ratios[2 * g.nret + t];
+    }
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < paths; q += stride) {
+        const uint64_t gid = g.path_offset + (uint64_t)q;
+        float S = g.s0;
+        uint4 x = make_uint4(0, 0, 0, 0);
+        int start = 0, off = 0, blk = 0;
+        for (int i = 0; i < steps; ++i) {
+            if (off == 0) {
+                if ((blk & 3) == 0) x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), (uint32_t)(blk >> 2), 1u), g.k0, g.k1);
+                const uint32_t r = (blk & 3) == 0 ? x.x : (blk & 3) == 1 ? x.y : (blk & 3) == 2 ? x.z : x.w;
+                start = (int)__umulhi(r, (uint32_t)g.nret);
+            }
+            int idx = start + off;
+            idx %= g.nret;
+            const size_t o = (size_t)i * pitch + q;
+            if (high) __stcs(high + o, __fmul_rn(S, rh[idx]));
+            if (low) __stcs(low + o, __fmul_rn(S, rl[idx]));
+            S = __fmul_rn(S, rc[idx]);
+            __stcs(close + o, S);
+            if (++off == g.block_len) { off = 0; ++blk; }
+        }
+    }
+}
+
+// ---- batch logistic scoring: out[i][h] = sigmoid(bias[h] + w[h] . x[i]), fp32 FMA (M:334-355, M:1463) -----------
+constexpr int kLrMaxDim = 32, kLrMaxHeads = 8;
+__global__ void __launch_bounds__(kThreads) lr_score_kernel(const float* __restrict__ x, int64_t n, int32_t dim,
+                                                            const float* __restrict__ w, const float* __restrict__ bias,
+                                                            int32_t heads, float* __restrict__ out) {
+    __shared__ float sw[kLrMaxHeads * kLrMaxDim], sb[kLrMaxHeads];
+    for (int t = threadIdx.x; t < heads * dim; t += blockDim.x) sw[t] = w[t];
+    for (int t = threadIdx.x; t < heads; t += blockDim.x) sb[t] = bias ? bias[t] : 0.f;
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float xr[kLrMaxDim];
+#pragma unroll 4
+        for (int j = 0; j < dim; ++j) xr[j] = __ldg(x + i * dim + j);
+        for (int h = 0; h < heads; ++h) {
+            float z = sb[h];
+            for (int j = 0; j < dim; ++j) z = __fmaf_rn(sw[h * dim + j], xr[j], z);
+            float s;
+            if (z < -50.f) s = 0.f; else if (z > 50.f) s = 1.f; else s = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-z)));
+            out[i * heads + h] = s;
+        }
+    }
+}
+
+// ---- reference jitter Monte Carlo (M:3449-3510): one thread = one trial, candidates walked in bar order -----------
+struct JitterArgs {
+    const double* high; const double* low; int32_t n_bars;
+    const int32_t* cand_bar; const uint8_t* cand_side; const double* cand_level; const double* cand_entry; int32_t n_cand;
+    double sp, tp, sig[4];
+    int64_t trials; uint64_t trial_offset; uint32_t k0, k1;
+    const double* replay_normals; const double* replay_uniforms;
+    double* out_total; double* out_dd; int32_t* out_wins; int32_t* out_losses; int32_t* out_opens;
+};
+
+__device__ __forceinline__ void box_muller_f64(uint32_t a, uint32_t b, double& z0, double& z1) {
+    const double u1 = ((double)a + 0.5) * 2.3283064365386963e-10;
+    const double u2 = ((double)b + 0.5) * 2.3283064365386963e-10;
+    const double r = sqrt(-2.0 * log(u1));
+    double s, c;
+    sincospi(2.0 * u2, &s, &c);
+    z0 = r * c; z1 = r * s;
+}
+
+__global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    double* sh = reinterpret_cast<double*>(smem_raw);
+    double* sl = sh + A.n_bars;
+    for (int t = threadIdx.x; t < A.n_bars; t += blockDim.x) { sh[t] = A.high[t]; sl[t] = A.low[t]; }
+    __syncthreads();
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < A.trials; t += stride) {
+        const uint64_t gt = A.trial_offset + (uint64_t)t;
+        double eq = 0.0, peak = 0.0, max_dd = 0.0;
+        int wins = 0, losses = 0, opens = 0;
+        for (int ci = 0; ci < A.n_cand; ++ci) {
+            double nz[4], uni;
+            if (A.replay_normals) {
+                const double* r = A.replay_normals + ((size_t)t * A.n_cand + ci) * 4;
+                nz[0] = r[0]; nz[1] = r[1]; nz[2] = r[2]; nz[3] = r[3];
+                uni = A.replay_uniforms[(size_t)t * A.n_cand + ci];
+            } else {
+                const uint4 x = philox4x32_10(make_uint4((uint32_t)gt, (uint32_t)(gt >> 32), (uint32_t)ci, 2u), A.k0, A.k1);
+                box_muller_f64(x.x, x.y, nz[0], nz[1]);
+                box_muller_f64(x.z, x.w, nz[2], nz[3]);
+                const uint4 y = philox4x32_10(make_uint4((uint32_t)gt, (uint32_t)(gt >> 32), (uint32_t)ci, 3u), A.k0, A.k1);
+                uni = ((double)y.x * 4294967296.0 + (double)y.y) * 5.421010862427522e-20;   // [0, 1)
+            }
+            const int side = A.cand_side[ci];
+            const double lvl_j = A.cand_level[ci] + nz[0] * A.sig[0];                    // M:3453
+            const double entry = A.cand_entry[ci] + nz[1] * A.sig[1];                    // M:3454
+            double stop, target;
+            if (side == 0) { stop = lvl_j - A.sp + nz[2] * A.sig[2]; target = lvl_j + A.tp + nz[3] * A.sig[3]; }
+            else { stop = lvl_j + A.sp + nz[2] * A.sig[2]; target = lvl_j - A.tp + nz[3] * A.sig[3]; }
+            double risk = fabs(entry - stop);
+            if (risk == 0.0) risk = 1e-9;                                                 // `or 1e-9`, M:3463
+            const double reward = fabs(target - entry);
+            double r = 0.0;
+            int outcome = 2;
+            for (int j = A.cand_bar[ci] + 1; j < A.n_bars; ++j) {
+                const double hh = sh[j], ll = sl[j];
+                const bool stop_hit = (side == 0) ? (ll <= stop) : (hh >= stop);
+                const bool target_hit = (side == 0) ? (hh >= target) : (ll <= target);
+                if (stop_hit && target_hit) {
+                    double up_span = hh - entry; if (!(up_span > 0.0)) up_span = 0.0;
+                    double down_span = entry - ll; if (!(down_span > 0.0)) down_span = 0.0;
+                    const double p_target_first = up_span / (up_span + down_span + 1e-9);
+                    if (uni < p_target_first) { r = reward / risk; outcome = 0; } else { r = -1.0; outcome = 1; }
+                    break;
+                } else if (target_hit) { r = reward / risk; outcome = 0; break; }
+                else if (stop_hit) { r = -1.0; outcome = 1; break; }
+            }
+            eq += r;
+            peak = peak > eq ? peak : eq;                                                 // max(peak, eq)
+            const double dd = eq - peak;
+            max_dd = dd < max_dd ? dd : max_dd;                                           // min(max_dd, eq - peak)
+            if (outcome == 0) ++wins; else if (outcome == 1) ++losses; else ++opens;
+        }
+        A.out_total[t] = eq; A.out_dd[t] = max_dd;
+        A.out_wins[t] = wins; A.out_losses[t] = losses; A.out_opens[t] = opens;
+    }
+}
+
+__global__ void init_flat_kernel(unsigned long long* flat, int n_combos) {
+    const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
+    const int n = n_combos * QMMX_AGG_SLOTS;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const int s = t % QMMX_AGG_SLOTS;
+        flat[t] = (s >= QMMX_AGG_NU + QMMX_AGG_ND) ? (unsigned long long)__double_as_longlong(neg_inf) : 0ull;
+    }
+}
+
+}  // namespace qmmx

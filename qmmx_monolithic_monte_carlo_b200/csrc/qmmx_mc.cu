@@ -1,0 +1,834 @@
+// libqmmx_mc.so — C ABI (include/qmmx_mc.h) over the sm_100a kernels in kernels.cuh.
+// One ctx = one GPU = one compute stream (+ one copy stream for the host-bar pipeline).  No CPU fallback.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "tables_host.h"
+
+using namespace qmmx;
+
+struct qmmx_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr, own_stream = nullptr, copy_stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    std::string err;
+    uint64_t launches = 0;
+    // host-side configuration
+    int L = 0;
+    double price[kMaxLevels];
+    uint8_t solid[kMaxLevels];
+    std::vector<qmmx_params> params;
+    std::vector<double> lr; int n_lr = 0;
+    std::vector<double> pol; int n_pol = 0;
+    double hist_lo = -8.0, hist_hi = 8.0;
+    double z_go = 0.0, z_skip = 0.0;
+    bool dirty = true;
+    // derived device state
+    DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
+    DevCombo* d_combos = nullptr;
+    uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
+    unsigned long long* d_flat = nullptr; int flat_combos = 0;
+    bool any_hl = false, any_tiny = false;
+    // resident bars
+    float *d_close = nullptr, *d_high = nullptr, *d_low = nullptr;
+    bool own_bars = false;
+    int64_t paths = 0, pitch = 0; int32_t steps = 0;
+    // staging for qmmx_run_scan_host
+    float* d_stage[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+    int64_t stage_elems = 0;
+    bool ran = false;
+};
+
+namespace {
+
+int fail(qmmx_ctx* c, int code, const std::string& msg) {
+    if (c) c->err = msg;
+    return code;
+}
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess)                                                                       \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? QMMX_E_NOMEM : QMMX_E_CUDA,           \
+                        std::string(#call) + ": " + cudaGetErrorString(e_));                         \
+    } while (0)
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+void free_bars(qmmx_ctx* c) {
+    if (c->own_bars) { cudaFree(c->d_close); cudaFree(c->d_high); cudaFree(c->d_low); }
+    c->d_close = c->d_high = c->d_low = nullptr;
+    c->own_bars = false; c->paths = 0; c->pitch = 0; c->steps = 0;
+}
+
+int alloc_bars(qmmx_ctx* ctx, int64_t paths, int32_t steps, bool hl) {
+    free_bars(ctx);
+    const int64_t pitch = round_up(std::max<int64_t>(paths, 1), 32);
+    const size_t bytes = (size_t)pitch * (size_t)std::max(steps, 1) * sizeof(float);
+    CK(cudaMalloc(&ctx->d_close, bytes));
+    ctx->own_bars = true;
+    if (hl) { CK(cudaMalloc(&ctx->d_high, bytes)); CK(cudaMalloc(&ctx->d_low, bytes)); }
+    ctx->paths = paths; ctx->pitch = pitch; ctx->steps = steps;
+    return QMMX_OK;
+}
+
+template <class T>
+int upload_vec(qmmx_ctx* ctx, T** dptr, const T* host, size_t n) {
+    if (*dptr) { cudaFree(*dptr); *dptr = nullptr; }
+    if (n == 0) return QMMX_OK;
+    CK(cudaMalloc(dptr, n * sizeof(T)));
+    CK(cudaMemcpyAsync(*dptr, host, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return QMMX_OK;
+}
+
+size_t scan_smem_bytes(const qmmx_ctx* c) {
+    return offsetof(BlockShared, cell) + (size_t)round_up(c->max_ncell, 16);
+}
+
+// (re)build every derived table after a configuration change
+int prepare(qmmx_ctx* ctx) {
+    if (!ctx->dirty) return QMMX_OK;
+    if (ctx->params.empty()) return fail(ctx, QMMX_E_STATE, "qmmx_set_params has not been called");
+    const int nc = (int)ctx->params.size();
+    std::vector<DevTables> tabs;
+    std::vector<std::pair<double, double>> keys;
+    std::vector<DevCombo> combos(nc);
+    ctx->any_hl = false; ctx->any_tiny = false;
+    bool any_prob = false;
+    for (int c = 0; c < nc; ++c) {
+        const qmmx_params& P = ctx->params[c];
+        int t = -1;
+        for (size_t i = 0; i < keys.size(); ++i)
+            if (std::memcmp(&keys[i].first, &P.contact_prox, 8) == 0 && std::memcmp(&keys[i].second, &P.q_min_prob, 8) == 0) t = (int)i;
+        if (t < 0) {
+            if ((int)keys.size() >= kMaxTables)
+                return fail(ctx, QMMX_E_UNSUPPORTED, "more than 8 distinct (contact_prox, q_min_prob) pairs in one run");
+            tabs.emplace_back();
+            std::string e;
+            if (build_tables(ctx->L, ctx->price, ctx->solid, P.contact_prox, P.q_min_prob, &tabs.back(), &e) != 0)
+                return fail(ctx, QMMX_E_UNSUPPORTED, e);
+            keys.emplace_back(P.contact_prox, P.q_min_prob);
+            t = (int)keys.size() - 1;
+        }
+        DevCombo& D = combos[c];
+        std::memset(&D, 0, sizeof(D));
+        D.sp = P.stop_padding; D.tp = P.tp_padding; D.qmin = P.q_min_prob; D.prox = P.contact_prox;
+        D.pmax = 0.0001 > P.contact_prox ? 0.0001 : P.contact_prox;
+        double wr = P.w_rules, wm = P.w_ml, s = wr + wm;                // M:1714-1719
+        if (s <= 0) { wr = 1.0; wm = 0.0; s = 1.0; }
+        D.wr = wr / s; D.wm = wm / s;
+        D.cool_steps = P.cooldown_s <= 0 ? 0 : (P.cooldown_s + 59) / 60;
+        D.overtouch = P.overtouch_limit; D.spd = P.steps_per_day; D.table = t;
+        D.flags = P.flags & 0xffffu;
+        const bool ml_on = !(P.flags & QMMX_F_DISABLE_ML_GATE) && ctx->n_lr > 0;
+        if (ml_on) D.flags |= 1u << 16;
+        if (ml_on && (P.flags & QMMX_F_USE_BLEND)) { D.flags |= 1u << 17; any_prob = true; }
+        if (P.flags & QMMX_F_EXIT_ON_HL) ctx->any_hl = true;
+        if (P.flags & QMMX_F_TINY_PRICES) ctx->any_tiny = true;
+    }
+    for (int c = 1; c < nc; ++c)
+        if (((ctx->params[c].flags ^ ctx->params[0].flags) & (QMMX_F_EXIT_ON_HL | QMMX_F_TINY_PRICES)) != 0)
+            return fail(ctx, QMMX_E_UNSUPPORTED, "EXIT_ON_HL / TINY_PRICES must be the same for all combos of a run");
+    ctx->n_tables = (int)tabs.size();
+    ctx->max_ncell = 1;
+    for (auto& t : tabs) ctx->max_ncell = std::max(ctx->max_ncell, t.ncell);
+    int rc;
+    if ((rc = upload_vec(ctx, &ctx->d_tables, tabs.data(), tabs.size())) != 0) return rc;
+    if ((rc = upload_vec(ctx, &ctx->d_combos, combos.data(), combos.size())) != 0) return rc;
+    // logistic gates
+    if (ctx->d_mlmask) { cudaFree(ctx->d_mlmask); ctx->d_mlmask = nullptr; }
+    if (ctx->d_mlprob) { cudaFree(ctx->d_mlprob); ctx->d_mlprob = nullptr; }
+    if (ctx->n_lr > 0) {
+        const size_t per_mask = (size_t)ctx->n_lr * kMaxLevels, per_prob = per_mask * 32;
+        if (any_prob && per_prob * nc * sizeof(double) > (size_t)512 << 20)
+            return fail(ctx, QMMX_E_UNSUPPORTED, "blend-mode probability table exceeds 512 MiB (combos x days)");
+        std::vector<uint32_t> mask(per_mask * nc, 0u);
+        std::vector<double> prob(any_prob ? per_prob * nc : 0);
+        for (int c = 0; c < nc; ++c) {
+            if (!(combos[c].flags & (1u << 16))) continue;
+            build_ml_tables(ctx->L, ctx->price, ctx->params[c].stop_padding, ctx->params[c].q_min_prob, ctx->lr.data(),
+                            ctx->n_lr, mask.data() + per_mask * c, any_prob ? prob.data() + per_prob * c : nullptr);
+        }
+        if ((rc = upload_vec(ctx, &ctx->d_mlmask, mask.data(), mask.size())) != 0) return rc;
+        if (any_prob && (rc = upload_vec(ctx, &ctx->d_mlprob, prob.data(), prob.size())) != 0) return rc;
+    }
+    if ((rc = upload_vec(ctx, &ctx->d_pol, ctx->pol.data(), ctx->pol.size())) != 0) return rc;
+    if (ctx->flat_combos < nc) {
+        if (ctx->d_flat) cudaFree(ctx->d_flat);
+        ctx->d_flat = nullptr;
+        CK(cudaMalloc(&ctx->d_flat, (size_t)nc * QMMX_AGG_SLOTS * 8));
+        ctx->flat_combos = nc;
+    }
+    ctx->dirty = false;
+    return QMMX_OK;
+}
+
+void fill_args(qmmx_ctx* ctx, ScanArgs& A, const float* c, const float* h, const float* l, int64_t pitch,
+               int64_t paths, int32_t steps) {
+    std::memset(&A, 0, sizeof(A));
+    A.close = c; A.high = h; A.low = l; A.pitch = pitch; A.paths = paths; A.steps = steps;
+    A.combo0 = 0; A.parity_combo = 0;
+    A.tables = ctx->d_tables; A.combos = ctx->d_combos; A.flat = ctx->d_flat;
+    A.mlmask = ctx->d_mlmask; A.mlprob = ctx->d_mlprob;
+    EngineGlobals& G = A.G;
+    G.mlmask = nullptr; G.mlprob = nullptr; G.n_days = ctx->n_lr;
+    G.pol = ctx->d_pol; G.n_pol = ctx->n_pol;
+    G.z_go = ctx->z_go; G.z_skip = ctx->z_skip;
+    G.hist_lo = ctx->hist_lo; G.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
+    G.steps = steps; G.trades = nullptr; G.tcounts = nullptr; G.max_trades = 0; G.codes = nullptr; G.paths = paths;
+}
+
+dim3 scan_grid(const qmmx_ctx* ctx, int64_t paths, int ncombos) {
+    const int64_t ntiles = (paths + 31) / 32;
+    const int64_t want = (ntiles + kWarps - 1) / kWarps;
+    const int64_t cap = (int64_t)ctx->sm_count * kBlocksPerSM;
+    return dim3((unsigned)std::max<int64_t>(1, std::min(want, cap)), (unsigned)ncombos, 1);
+}
+
+template <class K>
+int set_smem_attr(qmmx_ctx* ctx, K kernel, size_t bytes) {
+    CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return QMMX_OK;
+}
+
+int init_flat(qmmx_ctx* ctx) {
+    const int nc = (int)ctx->params.size();
+    init_flat_kernel<<<std::max(1, (nc * QMMX_AGG_SLOTS + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, nc);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    return QMMX_OK;
+}
+
+int launch_scan(qmmx_ctx* ctx, const ScanArgs& A, bool parity) {
+    const int nc = (int)ctx->params.size();
+    const size_t smem = scan_smem_bytes(ctx);
+    const dim3 grid = scan_grid(ctx, A.paths, nc);
+    const bool hl = ctx->any_hl, tiny = ctx->any_tiny;
+    if (hl && (!A.high || !A.low)) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs high/low bars");
+    if (A.paths <= 0 || A.steps <= 0) return QMMX_OK;
+    int rc = QMMX_OK;
+#define LAUNCH(HLv, PARv, TINYv)                                                              \
+    do {                                                                                      \
+        auto k = scan_kernel<HLv, PARv, TINYv>;                                               \
+        if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                               \
+        k<<<grid, kThreads, smem, ctx->stream>>>(A);                                          \
+    } while (0)
+    if (!parity) {
+        if (!hl && !tiny) LAUNCH(false, false, false);
+        else if (hl && !tiny) LAUNCH(true, false, false);
+        else if (!hl && tiny) LAUNCH(false, false, true);
+        else LAUNCH(true, false, true);
+    } else {
+        if (!hl && !tiny) LAUNCH(false, true, false);
+        else if (hl && !tiny) LAUNCH(true, true, false);
+        else if (!hl && tiny) LAUNCH(false, true, true);
+        else LAUNCH(true, true, true);
+    }
+#undef LAUNCH
+    ctx->launches++;
+    CK(cudaGetLastError());
+    return QMMX_OK;
+}
+
+void unpack_one(const qmmx_ctx* ctx, const unsigned long long* f, int combo, qmmx_agg* a) {
+    std::memset(a, 0, sizeof(*a));
+    a->struct_size = sizeof(*a); a->combo = (uint32_t)combo;
+    a->n_paths = f[U_NPATHS]; a->n_steps = f[U_NSTEPS]; a->n_trades = f[U_NTRADES]; a->n_wins = f[U_NWINS];
+    a->n_open = f[U_NOPEN]; a->n_trade_overflow = f[U_NOVERFLOW];
+    for (int c = 0; c < QMMX_N_ENTRY_CODES; ++c) a->entry_hist[c] = f[U_ENTRY + c];
+    for (int c = 0; c < QMMX_N_EXIT_CODES; ++c) a->exit_hist[c] = f[U_EXIT + c];
+    for (int c = 0; c < QMMX_PNL_HIST_BINS; ++c) a->pnl_hist[c] = f[U_HIST + c];
+    double d[QMMX_AGG_ND + QMMX_AGG_NX];
+    std::memcpy(d, f + QMMX_AGG_NU, sizeof(d));
+    a->sum_pnl = d[D_SUM_PNL]; a->sum_pnl2 = d[D_SUM_PNL2]; a->sum_path_pnl2 = d[D_SUM_PATH2]; a->sum_open_mtm = d[D_SUM_MTM];
+    a->max_path_pnl = d[QMMX_AGG_ND]; a->min_path_pnl = -d[QMMX_AGG_ND + 1];
+    a->pnl_hist_lo = ctx ? ctx->hist_lo : 0.0; a->pnl_hist_hi = ctx ? ctx->hist_hi : 0.0;
+}
+
+GbmDev make_gbm(const qmmx_gbm* g, uint64_t seed, uint64_t path_offset) {
+    GbmDev d;
+    d.s0 = g->s0;
+    d.drift = (float)(((double)g->mu_annual - 0.5 * (double)g->sigma_annual * (double)g->sigma_annual) *
+                      (double)g->dt_years / (double)g->sub_steps);
+    d.vol = (float)((double)g->sigma_annual * std::sqrt((double)g->dt_years / (double)g->sub_steps));
+    d.sub_steps = g->sub_steps; d.cents = (g->flags & QMMX_GBM_ROUND_CENTS) ? 1 : 0;
+    d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32); d.path_offset = path_offset;
+    return d;
+}
+
+int check_gbm(qmmx_ctx* ctx, const qmmx_gbm* g) {
+    if (!g || g->struct_size != sizeof(qmmx_gbm)) return fail(ctx, QMMX_E_BADARG, "qmmx_gbm.struct_size mismatch");
+    if (g->sub_steps != 1 && g->sub_steps != 4) return fail(ctx, QMMX_E_BADARG, "qmmx_gbm.sub_steps must be 1 or 4");
+    return QMMX_OK;
+}
+
+}  // namespace
+
+#define ENTER(c)                                                         \
+    if (!(c)) return QMMX_E_BADARG;                                      \
+    qmmx_ctx* ctx = (c);                                                 \
+    CK(cudaSetDevice(ctx->device))
+
+extern "C" {
+
+int qmmx_abi_version(void) { return QMMX_ABI_VERSION; }
+
+const char* qmmx_strerror(int status) {
+    switch (status) {
+        case QMMX_OK: return "ok";
+        case QMMX_E_BADARG: return "bad argument";
+        case QMMX_E_CUDA: return "CUDA error";
+        case QMMX_E_NOMEM: return "out of device memory";
+        case QMMX_E_STATE: return "call order: levels / params / bars not set";
+        case QMMX_E_UNSUPPORTED: return "unsupported configuration";
+        default: return "unknown status";
+    }
+}
+
+const char* qmmx_last_error(const qmmx_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int qmmx_create(int device, qmmx_ctx** out) {
+    if (!out) return QMMX_E_BADARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return QMMX_E_CUDA;
+    qmmx_ctx* ctx = new qmmx_ctx();
+    ctx->device = device;
+    auto bail = [&](int code) { delete ctx; return code; };
+    if (cudaSetDevice(device) != cudaSuccess) return bail(QMMX_E_CUDA);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(QMMX_E_CUDA);
+    if (prop.major < 10) return bail(QMMX_E_UNSUPPORTED);   // sm_100a cubin only
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
+    ctx->stream = ctx->own_stream;
+    cudaEventCreate(&ctx->ev0); cudaEventCreate(&ctx->ev1);
+    for (int i = 0; i < 2; ++i) {
+        cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming);
+    }
+    ctx->z_go = sigmoid_threshold(0.60);     // M:3083-3085
+    ctx->z_skip = sigmoid_threshold(0.55);
+    *out = ctx;
+    return QMMX_OK;
+}
+
+int qmmx_destroy(qmmx_ctx* ctx) {
+    if (!ctx) return QMMX_E_BADARG;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    free_bars(ctx);
+    for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
+    cudaFree(ctx->d_tables); cudaFree(ctx->d_combos); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
+    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat);
+    cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
+    for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
+    cudaStreamDestroy(ctx->own_stream); cudaStreamDestroy(ctx->copy_stream);
+    delete ctx;
+    return QMMX_OK;
+}
+
+int qmmx_set_stream(qmmx_ctx* c, void* cuda_stream) {
+    ENTER(c);
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return QMMX_OK;
+}
+
+int qmmx_set_levels(qmmx_ctx* c, const double* price, const uint8_t* solid, int n_levels) {
+    ENTER(c);
+    if (n_levels < 0 || n_levels > QMMX_MAX_LEVELS || (n_levels > 0 && (!price || !solid)))
+        return fail(ctx, QMMX_E_BADARG, "n_levels must be 0..64 with non-null arrays");
+    for (int j = 0; j < n_levels; ++j) {
+        if (!std::isfinite(price[j])) return fail(ctx, QMMX_E_BADARG, "level prices must be finite");
+        ctx->price[j] = price[j]; ctx->solid[j] = solid[j] ? 1 : 0;
+    }
+    ctx->L = n_levels; ctx->dirty = true;
+    return QMMX_OK;
+}
+
+int qmmx_set_params(qmmx_ctx* c, const qmmx_params* params, int n_combos) {
+    ENTER(c);
+    if (!params || n_combos < 1 || n_combos > QMMX_MAX_COMBOS) return fail(ctx, QMMX_E_BADARG, "n_combos must be 1..1024");
+    for (int i = 0; i < n_combos; ++i) {
+        const qmmx_params& P = params[i];
+        if (P.struct_size != sizeof(qmmx_params)) return fail(ctx, QMMX_E_BADARG, "qmmx_params.struct_size mismatch");
+        if (P.overtouch_limit < 1 || P.overtouch_limit > 15) return fail(ctx, QMMX_E_BADARG, "overtouch_limit must be 1..15");
+        if (P.steps_per_day < 1) return fail(ctx, QMMX_E_BADARG, "steps_per_day must be >= 1");
+        if (!(P.contact_prox == P.contact_prox) || !(P.q_min_prob == P.q_min_prob))
+            return fail(ctx, QMMX_E_BADARG, "contact_prox / q_min_prob must not be NaN");
+    }
+    ctx->params.assign(params, params + n_combos);
+    ctx->dirty = true;
+    return QMMX_OK;
+}
+
+int qmmx_set_lr(qmmx_ctx* c, const double* coef_intercept, int n_days) {
+    ENTER(c);
+    if (n_days < 0 || n_days > kMaxDays || (n_days > 0 && !coef_intercept)) return fail(ctx, QMMX_E_BADARG, "n_days must be 0..64");
+    ctx->lr.assign(coef_intercept, coef_intercept + (size_t)n_days * QMMX_LR_DIM);
+    ctx->n_lr = n_days; ctx->dirty = true;
+    return QMMX_OK;
+}
+
+int qmmx_set_policy(qmmx_ctx* c, const double* w, int n_days) {
+    ENTER(c);
+    if (n_days < 0 || n_days > kMaxDays || (n_days > 0 && !w)) return fail(ctx, QMMX_E_BADARG, "n_days must be 0..64");
+    ctx->pol.assign(w, w + (size_t)n_days * QMMX_POLICY_HEADS * QMMX_POLICY_DIM);
+    ctx->n_pol = n_days; ctx->dirty = true;
+    return QMMX_OK;
+}
+
+int qmmx_set_pnl_hist_range(qmmx_ctx* c, double lo, double hi) {
+    ENTER(c);
+    if (!(hi > lo)) return fail(ctx, QMMX_E_BADARG, "pnl histogram range must satisfy hi > lo");
+    ctx->hist_lo = lo; ctx->hist_hi = hi;
+    return QMMX_OK;
+}
+
+int qmmx_upload_bars(qmmx_ctx* c, const float* close, const float* high, const float* low, int64_t paths, int32_t steps) {
+    ENTER(c);
+    if (!close || paths < 0 || steps < 0 || ((high == nullptr) != (low == nullptr)))
+        return fail(ctx, QMMX_E_BADARG, "close must be non-null; high and low come together");
+    int rc = alloc_bars(ctx, paths, steps, high != nullptr);
+    if (rc != 0) return rc;
+    if (paths == 0 || steps == 0) return QMMX_OK;
+    const size_t w = (size_t)paths * 4, dp = (size_t)ctx->pitch * 4;
+    CK(cudaMemcpy2DAsync(ctx->d_close, dp, close, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
+    if (high) {
+        CK(cudaMemcpy2DAsync(ctx->d_high, dp, high, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpy2DAsync(ctx->d_low, dp, low, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    return QMMX_OK;
+}
+
+int qmmx_bind_device_bars(qmmx_ctx* c, const float* d_close, const float* d_high, const float* d_low,
+                          int64_t paths, int32_t steps, int64_t pitch) {
+    ENTER(c);
+    if (!d_close || paths < 0 || steps < 0 || pitch < paths || ((d_high == nullptr) != (d_low == nullptr)))
+        return fail(ctx, QMMX_E_BADARG, "bad device bar description");
+    free_bars(ctx);
+    ctx->d_close = const_cast<float*>(d_close); ctx->d_high = const_cast<float*>(d_high); ctx->d_low = const_cast<float*>(d_low);
+    ctx->own_bars = false; ctx->paths = paths; ctx->steps = steps; ctx->pitch = pitch;
+    return QMMX_OK;
+}
+
+int qmmx_device_bars(qmmx_ctx* c, float** d_close, float** d_high, float** d_low, int64_t* pitch) {
+    ENTER(c);
+    if (d_close) *d_close = ctx->d_close;
+    if (d_high) *d_high = ctx->d_high;
+    if (d_low) *d_low = ctx->d_low;
+    if (pitch) *pitch = ctx->pitch;
+    return QMMX_OK;
+}
+
+int qmmx_pin_host(qmmx_ctx* c, void* ptr, size_t bytes) {
+    ENTER(c);
+    if (!ptr || bytes == 0) return fail(ctx, QMMX_E_BADARG, "null host buffer");
+    CK(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    return QMMX_OK;
+}
+
+int qmmx_unpin_host(qmmx_ctx* c, void* ptr) {
+    ENTER(c);
+    CK(cudaHostUnregister(ptr));
+    return QMMX_OK;
+}
+
+int qmmx_download_bars(qmmx_ctx* c, float* close, float* high, float* low) {
+    ENTER(c);
+    if (!ctx->d_close) return fail(ctx, QMMX_E_STATE, "no resident bars");
+    if (ctx->paths == 0 || ctx->steps == 0) return QMMX_OK;
+    const size_t w = (size_t)ctx->paths * 4, dp = (size_t)ctx->pitch * 4;
+    if (close) CK(cudaMemcpy2DAsync(close, w, ctx->d_close, dp, w, ctx->steps, cudaMemcpyDeviceToHost, ctx->stream));
+    if (high) {
+        if (!ctx->d_high) return fail(ctx, QMMX_E_STATE, "resident bars have no high/low");
+        CK(cudaMemcpy2DAsync(high, w, ctx->d_high, dp, w, ctx->steps, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (low) {
+        if (!ctx->d_low) return fail(ctx, QMMX_E_STATE, "resident bars have no high/low");
+        CK(cudaMemcpy2DAsync(low, w, ctx->d_low, dp, w, ctx->steps, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    return QMMX_OK;
+}
+
+int qmmx_gen_gbm(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps, const qmmx_gbm* gbm) {
+    ENTER(c);
+    int rc = check_gbm(ctx, gbm);
+    if (rc != 0) return rc;
+    if (paths < 0 || steps < 0) return fail(ctx, QMMX_E_BADARG, "negative size");
+    if ((rc = alloc_bars(ctx, paths, steps, gbm->sub_steps == 4)) != 0) return rc;
+    if (paths == 0 || steps == 0) return QMMX_OK;
+    const GbmDev g = make_gbm(gbm, seed, path_offset);
+    const int64_t blocks = std::min<int64_t>((paths + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    gen_gbm_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, paths, steps, g);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                       const float* window_ohlc, int32_t window_len, int32_t block_len) {
+    ENTER(c);
+    const int nret = window_len - 1;
+    if (!window_ohlc || nret < 1 || nret > kMaxWindow || block_len < 1 || paths < 0 || steps < 0)
+        return fail(ctx, QMMX_E_BADARG, "window_len must be 2..1025, block_len >= 1");
+    int rc = alloc_bars(ctx, paths, steps, true);
+    if (rc != 0) return rc;
+    if (paths == 0 || steps == 0) return QMMX_OK;
+    std::vector<float> ratios(3 * (size_t)nret);
+    for (int t = 1; t < window_len; ++t) {
+        const float pc = window_ohlc[4 * (t - 1) + 3];
+        ratios[t - 1] = window_ohlc[4 * t + 1] / pc;
+        ratios[nret + t - 1] = window_ohlc[4 * t + 2] / pc;
+        ratios[2 * nret + t - 1] = window_ohlc[4 * t + 3] / pc;
+    }
+    float* d_r = nullptr;
+    CK(cudaMalloc(&d_r, ratios.size() * 4));
+    cudaError_t e = cudaMemcpyAsync(d_r, ratios.data(), ratios.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        BootDev g;
+        g.ratios = d_r; g.nret = nret; g.block_len = block_len; g.s0 = window_ohlc[4 * (window_len - 1) + 3];
+        g.k0 = (uint32_t)seed; g.k1 = (uint32_t)(seed >> 32); g.path_offset = path_offset;
+        const int64_t blocks = std::min<int64_t>((paths + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        gen_bootstrap_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, paths, steps, g);
+        ctx->launches++;
+        e = cudaGetLastError();
+        cudaEventRecord(ctx->ev1, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    }
+    cudaFree(d_r);
+    if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("gen_bootstrap: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_run_scan_async(qmmx_ctx* c) {
+    ENTER(c);
+    if (!ctx->d_close) return fail(ctx, QMMX_E_STATE, "no resident bars (qmmx_upload_bars / qmmx_gen_* first)");
+    int rc = prepare(ctx);
+    if (rc != 0) return rc;
+    ScanArgs A;
+    fill_args(ctx, A, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, ctx->paths, ctx->steps);
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((rc = init_flat(ctx)) != 0) return rc;
+    if ((rc = launch_scan(ctx, A, false)) != 0) return rc;
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_fetch_agg(qmmx_ctx* c, qmmx_agg* agg_out) {
+    ENTER(c);
+    if (!ctx->ran || !ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    const int nc = (int)ctx->params.size();
+    std::vector<unsigned long long> flat((size_t)nc * QMMX_AGG_SLOTS);
+    CK(cudaMemcpyAsync(flat.data(), ctx->d_flat, flat.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (agg_out) for (int i = 0; i < nc; ++i) unpack_one(ctx, flat.data() + (size_t)i * QMMX_AGG_SLOTS, i, agg_out + i);
+    return QMMX_OK;
+}
+
+int qmmx_run_scan(qmmx_ctx* c, qmmx_agg* agg_out, qmmx_trade* trades_out, int32_t* trade_counts_out,
+                  int32_t max_trades_per_path, uint8_t* codes_out) {
+    ENTER(c);
+    const bool parity = trades_out || trade_counts_out || codes_out;
+    if (!parity) {
+        int rc = qmmx_run_scan_async(ctx);
+        if (rc != 0) return rc;
+        return qmmx_fetch_agg(ctx, agg_out);
+    }
+    if (!ctx->d_close) return fail(ctx, QMMX_E_STATE, "no resident bars (qmmx_upload_bars / qmmx_gen_* first)");
+    if (trades_out && max_trades_per_path < 1) return fail(ctx, QMMX_E_BADARG, "max_trades_per_path must be >= 1");
+    int rc = prepare(ctx);
+    if (rc != 0) return rc;
+    const int64_t P = ctx->paths; const int32_t T = ctx->steps;
+    qmmx_trade* d_tr = nullptr; int32_t* d_cnt = nullptr; uint8_t* d_codes = nullptr;
+    cudaError_t e = cudaSuccess;
+    if (trades_out && P > 0) e = cudaMalloc(&d_tr, (size_t)P * max_trades_per_path * sizeof(qmmx_trade));
+    if (e == cudaSuccess && trades_out && P > 0) e = cudaMemsetAsync(d_tr, 0, (size_t)P * max_trades_per_path * sizeof(qmmx_trade), ctx->stream);
+    if (e == cudaSuccess && (trade_counts_out || trades_out) && P > 0) e = cudaMalloc(&d_cnt, (size_t)P * 4);
+    if (e == cudaSuccess && codes_out && P > 0 && T > 0) e = cudaMalloc(&d_codes, (size_t)P * T);
+    if (e == cudaSuccess) {
+        ScanArgs A;
+        fill_args(ctx, A, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, P, T);
+        A.G.trades = d_tr; A.G.tcounts = d_cnt; A.G.max_trades = trades_out ? max_trades_per_path : 0; A.G.codes = d_codes;
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        rc = init_flat(ctx);
+        if (rc == 0) rc = launch_scan(ctx, A, true);
+        cudaEventRecord(ctx->ev1, ctx->stream);
+        if (rc == 0) {
+            if (trades_out && d_tr) e = cudaMemcpyAsync(trades_out, d_tr, (size_t)P * max_trades_per_path * sizeof(qmmx_trade), cudaMemcpyDeviceToHost, ctx->stream);
+            if (e == cudaSuccess && trade_counts_out && d_cnt) e = cudaMemcpyAsync(trade_counts_out, d_cnt, (size_t)P * 4, cudaMemcpyDeviceToHost, ctx->stream);
+            if (e == cudaSuccess && codes_out && d_codes) e = cudaMemcpyAsync(codes_out, d_codes, (size_t)P * T, cudaMemcpyDeviceToHost, ctx->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        }
+    }
+    cudaFree(d_tr); cudaFree(d_cnt); cudaFree(d_codes);
+    if (rc != 0) return rc;
+    if (e != cudaSuccess) return fail(ctx, e == cudaErrorMemoryAllocation ? QMMX_E_NOMEM : QMMX_E_CUDA, std::string("run_scan: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return qmmx_fetch_agg(ctx, agg_out);
+}
+
+int qmmx_run_scan_host(qmmx_ctx* c, const float* close, const float* high, const float* low, int64_t paths,
+                       int32_t steps, int64_t chunk_paths, qmmx_agg* agg_out) {
+    ENTER(c);
+    if (!close || paths < 0 || steps < 0 || ((high == nullptr) != (low == nullptr)))
+        return fail(ctx, QMMX_E_BADARG, "close must be non-null; high and low come together");
+    int rc = prepare(ctx);
+    if (rc != 0) return rc;
+    if (ctx->any_hl && !high) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs high/low bars");
+    if (chunk_paths <= 0) chunk_paths = 1 << 17;
+    chunk_paths = round_up(std::min<int64_t>(chunk_paths, std::max<int64_t>(paths, 1)), 32);
+    const int nf = high ? 3 : 1;
+    const int64_t need = chunk_paths * std::max(steps, 1);
+    if (ctx->stage_elems < need || (nf == 3 && !ctx->d_stage[0][1])) {
+        for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) { cudaFree(ctx->d_stage[b][f]); ctx->d_stage[b][f] = nullptr; }
+        ctx->stage_elems = 0;
+        for (int b = 0; b < 2; ++b) for (int f = 0; f < nf; ++f) CK(cudaMalloc(&ctx->d_stage[b][f], (size_t)need * 4));
+        ctx->stage_elems = need;
+    }
+    const float* src[3] = {close, high, low};
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((rc = init_flat(ctx)) != 0) return rc;
+    int n = 0;
+    for (int64_t off = 0; off < paths; off += chunk_paths, ++n) {
+        const int b = n & 1;
+        const int64_t w = std::min(chunk_paths, paths - off);
+        if (n >= 2) CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_done[b], 0));
+        for (int f = 0; f < nf; ++f)
+            CK(cudaMemcpy2DAsync(ctx->d_stage[b][f], (size_t)chunk_paths * 4, src[f] + off, (size_t)paths * 4,
+                                 (size_t)w * 4, steps, cudaMemcpyHostToDevice, ctx->copy_stream));
+        CK(cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
+        ScanArgs A;
+        fill_args(ctx, A, ctx->d_stage[b][0], ctx->d_stage[b][1], ctx->d_stage[b][2], chunk_paths, w, steps);
+        if ((rc = launch_scan(ctx, A, false)) != 0) return rc;
+        CK(cudaEventRecord(ctx->ev_done[b], ctx->stream));
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ran = true;
+    return qmmx_fetch_agg(ctx, agg_out);
+}
+
+int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps, const qmmx_gbm* gbm) {
+    ENTER(c);
+    int rc = check_gbm(ctx, gbm);
+    if (rc != 0) return rc;
+    if (paths < 0 || steps < 0) return fail(ctx, QMMX_E_BADARG, "negative size");
+    if ((rc = prepare(ctx)) != 0) return rc;
+    if (ctx->any_tiny) return fail(ctx, QMMX_E_UNSUPPORTED, "TINY_PRICES is not available in the fused GBM kernel");
+    if (ctx->any_hl && gbm->sub_steps != 4) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs sub_steps = 4 (OHLC bars)");
+    ScanArgs A;
+    fill_args(ctx, A, nullptr, nullptr, nullptr, 0, paths, steps);
+    const GbmDev g = make_gbm(gbm, seed, path_offset);
+    const size_t smem = scan_smem_bytes(ctx);
+    const dim3 grid = scan_grid(ctx, paths, (int)ctx->params.size());
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((rc = init_flat(ctx)) != 0) return rc;
+    if (paths > 0 && steps > 0) {
+        if (gbm->sub_steps == 4) {
+            // OHLC recipe: 4 sub-steps per bar; the engine sees high/low only when EXIT_ON_HL is set
+            if (ctx->any_hl) {
+                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true>, smem)) != 0) return rc;
+                fused_gbm_kernel<true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+            } else {
+                return fail(ctx, QMMX_E_UNSUPPORTED, "fused GBM with sub_steps = 4 requires EXIT_ON_HL (use sub_steps = 1 for close-only)");
+            }
+        } else {
+            if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false>, smem)) != 0) return rc;
+            fused_gbm_kernel<false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+        }
+        ctx->launches++;
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_run_fused_gbm(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                       const qmmx_gbm* gbm, qmmx_agg* agg_out) {
+    int rc = qmmx_run_fused_gbm_async(c, seed, path_offset, paths, steps, gbm);
+    if (rc != 0) return rc;
+    return qmmx_fetch_agg(c, agg_out);
+}
+
+int qmmx_agg_device(qmmx_ctx* c, void** d_flat, size_t* bytes) {
+    ENTER(c);
+    if (!ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    if (d_flat) *d_flat = ctx->d_flat;
+    if (bytes) *bytes = ctx->params.size() * QMMX_AGG_SLOTS * 8;
+    return QMMX_OK;
+}
+
+int qmmx_agg_unpack(qmmx_ctx* ctx, const void* flat_host, int n_combos, qmmx_agg* out) {
+    if (!flat_host || !out || n_combos < 0) return QMMX_E_BADARG;
+    const unsigned long long* f = static_cast<const unsigned long long*>(flat_host);
+    for (int i = 0; i < n_combos; ++i) unpack_one(ctx, f + (size_t)i * QMMX_AGG_SLOTS, i, out + i);
+    return QMMX_OK;
+}
+
+int qmmx_lr_score(qmmx_ctx* c, const float* x, int64_t n, int32_t dim, const float* w, const float* bias,
+                  int32_t heads, float* out) {
+    ENTER(c);
+    if (!x || !w || !out || n < 0 || dim < 1 || dim > kLrMaxDim || heads < 1 || heads > kLrMaxHeads)
+        return fail(ctx, QMMX_E_BADARG, "lr_score: dim 1..32, heads 1..8");
+    if (n == 0) return QMMX_OK;
+    float *dx = nullptr, *dw = nullptr, *db = nullptr, *dout = nullptr;
+    cudaError_t e = cudaMalloc(&dx, (size_t)n * dim * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&dw, (size_t)heads * dim * 4);
+    if (e == cudaSuccess && bias) e = cudaMalloc(&db, (size_t)heads * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&dout, (size_t)n * heads * 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dx, x, (size_t)n * dim * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dw, w, (size_t)heads * dim * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && bias) e = cudaMemcpyAsync(db, bias, (size_t)heads * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        const int64_t blocks = std::min<int64_t>((n + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        lr_score_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(dx, n, dim, dw, db, heads, dout);
+        ctx->launches++;
+        e = cudaGetLastError();
+        cudaEventRecord(ctx->ev1, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout, (size_t)n * heads * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dx); cudaFree(dw); cudaFree(db); cudaFree(dout);
+    if (e != cudaSuccess) return fail(ctx, e == cudaErrorMemoryAllocation ? QMMX_E_NOMEM : QMMX_E_CUDA, std::string("lr_score: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_run_jitter(qmmx_ctx* c, const double* high, const double* low, int32_t n_bars, const int32_t* cand_bar,
+                    const uint8_t* cand_side, const double* cand_level, const double* cand_entry, int32_t n_cand,
+                    double stop_padding, double tp_padding, const double* sigmas, int64_t trials, uint64_t seed,
+                    uint64_t trial_offset, const double* replay_normals, const double* replay_uniforms,
+                    double* out_total_r, double* out_max_dd, int32_t* out_wins, int32_t* out_losses, int32_t* out_opens) {
+    ENTER(c);
+    if (!high || !low || n_bars < 1 || n_bars > 12000 || n_cand < 0 || trials < 0 || !sigmas ||
+        (n_cand > 0 && (!cand_bar || !cand_side || !cand_level || !cand_entry)) ||
+        ((replay_normals == nullptr) != (replay_uniforms == nullptr)) ||
+        !out_total_r || !out_max_dd || !out_wins || !out_losses || !out_opens)
+        return fail(ctx, QMMX_E_BADARG, "run_jitter: bad arguments (n_bars 1..12000)");
+    if (trials == 0) return QMMX_OK;
+    const size_t nb = (size_t)n_bars, nk = (size_t)n_cand, nt = (size_t)trials;
+    // one device arena: high, low, level, entry | replay normals, uniforms | outputs | int arrays
+    const size_t n_f64_in = 2 * nb + 2 * nk + (replay_normals ? nt * nk * 5 : 0);
+    const size_t n_f64 = n_f64_in + 2 * nt;
+    const size_t n_i32 = nk + 3 * nt;
+    uint8_t* arena = nullptr;
+    const size_t bytes = n_f64 * 8 + n_i32 * 4 + nk + 64;
+    CK(cudaMalloc(&arena, bytes));
+    double* d64 = reinterpret_cast<double*>(arena);
+    int32_t* i32 = reinterpret_cast<int32_t*>(arena + n_f64 * 8);
+    uint8_t* u8 = arena + n_f64 * 8 + n_i32 * 4;
+    JitterArgs A;
+    std::memset(&A, 0, sizeof(A));
+    double* p = d64;
+    cudaError_t e = cudaSuccess;
+    auto up = [&](const void* src, void* dst, size_t n) {
+        if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream);
+    };
+    A.high = p; up(high, p, nb * 8); p += nb;
+    A.low = p; up(low, p, nb * 8); p += nb;
+    A.cand_level = p; up(cand_level, p, nk * 8); p += nk;
+    A.cand_entry = p; up(cand_entry, p, nk * 8); p += nk;
+    if (replay_normals) {
+        A.replay_normals = p; up(replay_normals, p, nt * nk * 4 * 8); p += nt * nk * 4;
+        A.replay_uniforms = p; up(replay_uniforms, p, nt * nk * 8); p += nt * nk;
+    }
+    A.out_total = p; p += nt;
+    A.out_dd = p; p += nt;
+    A.cand_bar = i32; up(cand_bar, i32, nk * 4);
+    A.out_wins = i32 + nk; A.out_losses = i32 + nk + nt; A.out_opens = i32 + nk + 2 * nt;
+    A.cand_side = u8; up(cand_side, u8, nk);
+    A.n_bars = n_bars; A.n_cand = n_cand; A.sp = stop_padding; A.tp = tp_padding;
+    for (int q = 0; q < 4; ++q) A.sig[q] = sigmas[q];
+    A.trials = trials; A.trial_offset = trial_offset; A.k0 = (uint32_t)seed; A.k1 = (uint32_t)(seed >> 32);
+    const size_t smem = 2 * nb * 8;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(jitter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) {
+        const int64_t blocks = std::min<int64_t>((trials + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        jitter_kernel<<<(unsigned)blocks, kThreads, smem, ctx->stream>>>(A);
+        ctx->launches++;
+        e = cudaGetLastError();
+        cudaEventRecord(ctx->ev1, ctx->stream);
+    }
+    auto down = [&](void* dst, const void* src, size_t n) {
+        if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream);
+    };
+    down(out_total_r, A.out_total, nt * 8); down(out_max_dd, A.out_dd, nt * 8);
+    down(out_wins, A.out_wins, nt * 4); down(out_losses, A.out_losses, nt * 4); down(out_opens, A.out_opens, nt * 4);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(arena);
+    if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("run_jitter: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
+                        const float* p, int64_t n, int32_t* level_table, int32_t* level_brute,
+                        uint8_t* conf_mask, uint8_t* conf_brute, uint64_t* near_table, uint64_t* near_brute) {
+    if (n_levels < 0 || n_levels > QMMX_MAX_LEVELS || n < 0 || (n > 0 && !p)) return QMMX_E_BADARG;
+    std::vector<DevTables> T(1);
+    std::string e;
+    if (build_tables(n_levels, price, solid, prox, qmin, &T[0], &e) != 0) return QMMX_E_UNSUPPORTED;
+    for (int64_t i = 0; i < n; ++i) {
+        const float pf = p[i];
+        const int kt = classify_tables(&T[0], pf), kb = classify_bruteforce(n_levels, price, prox, pf);
+        if (level_table) level_table[i] = kt;
+        if (level_brute) level_brute[i] = kb;
+        uint8_t mt = 0, mb = 0;
+        if (kb >= 0) {
+            for (int b = 0; b < 3; ++b) {
+                if (kt >= 0 && pf >= T[0].lev[kt].cpass[b][0] && pf <= T[0].lev[kt].cpass[b][1]) mt |= 1u << b;
+                if (!(confidence_f64(std::fabs(price[kb] - (double)pf), solid[kb] != 0, b + 1, prox) < qmin)) mb |= 1u << b;
+            }
+        }
+        if (conf_mask) conf_mask[i] = mt;
+        if (conf_brute) conf_brute[i] = mb;
+        uint64_t nt = 0, nbm = 0;
+        for (int j = 0; j < n_levels; ++j) {
+            if (pf >= T[0].lev[j].wlo && pf <= T[0].lev[j].whi) nt |= 1ull << j;
+            if (!(std::fabs(price[j] - (double)pf) > prox)) nbm |= 1ull << j;
+        }
+        if (near_table) near_table[i] = nt;
+        if (near_brute) near_brute[i] = nbm;
+    }
+    return QMMX_OK;
+}
+
+int qmmx_last_timing(qmmx_ctx* c, float* ms) {
+    ENTER(c);
+    if (!ctx->ran || !ms) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    CK(cudaEventSynchronize(ctx->ev1));
+    CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return QMMX_OK;
+}
+
+int qmmx_launch_count(qmmx_ctx* c, uint64_t* n) {
+    if (!c || !n) return QMMX_E_BADARG;
+    *n = c->launches;
+    return QMMX_OK;
+}
+
+}  // extern "C"

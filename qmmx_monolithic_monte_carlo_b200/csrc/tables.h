@@ -1,64 +1,66 @@
 // Host/device table layouts shared by the table builder (host) and the kernels (device).
 //
-// The nearest-level search of the reference (`min(levels, key=|L.price - p|)`, first minimal element,
-// qmmx_monolithic.py:1543) and its proximity test (`dist > CONTACT_PROX`, M:1545) depend only on the
-// price p.  For fp32-representable p evaluated in float64 the answer is a piecewise-constant function of
-// p: the host builds that function EXACTLY (by bisection over the ordered set of fp32 values against the
-// brute-force float64 predicate) as a list of zones, plus a uniform grid over the price axis whose cells
-// say "every price in this cell is far from all levels" / "touches level k" / "mixed, consult the zones".
-// The kernels then classify a price with one shared-memory byte load instead of an O(L) float64 search.
+// Every per-tick decision of the reference's gate stack that depends only on the price p — which level is
+// nearest and whether it is within CONTACT_PROX (`min(levels, key=|L.price - p|)`, first minimal element,
+// qmmx_monolithic.py:1543-1545), whether p is still inside another level's contact window (latch release,
+// M:1572-1576), whether `compute_confidence(...) < Q_MIN_PROB` (M:1415-1427, M:1627-1641) — is, for an
+// fp32-representable p evaluated in float64, a monotone or piecewise-constant function of p.  The host
+// evaluates those float64 predicates EXACTLY (same IEEE operations as CPython, no FMA contraction) and
+// bisects over the ordered set of fp32 values, so the kernels replace the O(L) float64 work by fp32
+// compares against exact thresholds and one shared-memory byte lookup.
 #pragma once
 #include <cstdint>
 
 namespace qmmx {
 
-constexpr int kThreads = 256;           // threads per CTA = paths per tile
+constexpr int kThreads = 256;           // threads per CTA; one thread walks one path
 constexpr int kMaxLevels = 64;
-constexpr int kMaxCells = 16384;
-constexpr int kMaxZones = 256;
-constexpr int kMaxTables = 8;           // distinct CONTACT_PROX values across the combos of one run
+constexpr int kMaxCells = 32768;
+constexpr int kMaxZones = 272;
+constexpr int kMaxTables = 8;           // distinct (CONTACT_PROX, Q_MIN_PROB) pairs across the combos of one run
+constexpr int kMaxDays = 64;
 constexpr uint8_t kFar = 0xFF;
 constexpr uint8_t kMixed = 0xFE;
 
+constexpr uint32_t kLvSolid = 1u, kLvConfl06 = 2u, kLvConfl015 = 4u;
+
+struct DevLevel {                       // 64 bytes
+    double price;
+    float wlo, whi;                     // |price - p| <= CONTACT_PROX  <=>  wlo <= p <= whi       (fp32 p)
+    float cpass[3][2];                  // touch bucket b (tc<=1, tc==2, tc>=3): conf >= Q_MIN_PROB <=> [0] <= p <= [1]
+    uint32_t cand_lo, cand_hi;          // levels j != k whose contact window overlaps this level's window
+    uint32_t flags;                     // kLvSolid | kLvConfl06 (M:3069-3070) | kLvConfl015 (M:1885-1886)
+    uint32_t pad[3];
+};
+static_assert(sizeof(DevLevel) == 64, "DevLevel layout");
+
 struct DevTables {
-    int32_t L, Z, ncell, pad0;
-    float glo, inv_w, pad1, pad2;
-    double price[kMaxLevels];
-    uint8_t solid[kMaxLevels];
-    uint8_t confl06[kMaxLevels];    // #{j : |price_j - price_k| <= 0.6} > 1   (M:3069-3070)
-    uint8_t confl015[kMaxLevels];   // #{j : |price_j - price_k| <= 0.15} >= 2 (M:1885-1886)
-    float zhi[kMaxZones];           // inclusive fp32 upper bound of zone z; zone z = (zhi[z-1], zhi[z]]
-    uint8_t zlev[kMaxZones];        // level index touched in zone z, or kFar
-    uint8_t cell[kMaxCells];        // level index / kFar / kMixed per grid cell
+    int32_t L, Z, ncell, shift;         // cell = clamp((bits(p) - obase) >> shift, 0, ncell-1)
+    int32_t obase, pad0, pad1, pad2;
+    DevLevel lev[kMaxLevels];
+    float zhi[kMaxZones];               // inclusive fp32 upper bound of zone z; zone z = (zhi[z-1], zhi[z]]
+    uint8_t zlev[kMaxZones];            // level touched in zone z, or kFar
+    uint8_t cell[kMaxCells];            // level index / kFar / kMixed per grid cell
 };
 
-struct DevCombo {
-    double prox, pmax, sp, tp, qmin, wr, wm, vstrong, vprox;
-    int32_t cool_steps;             // ceil(cooldown_s / 60): now_ms < until_ms  <=>  step < exit_step + cool_steps
+struct DevCombo {                       // one parameter combination (qmmx_params, preprocessed)
+    double sp, tp, qmin, prox, pmax, wr, wm;
+    int32_t cool_steps;                 // ceil(cooldown_s / 60): now_ms < until_ms  <=>  step < exit_step + cool_steps
     int32_t overtouch;
-    int32_t spd;
+    int32_t spd;                        // steps per day
     int32_t table;
     uint32_t flags;
     uint32_t pad[3];
 };
 
-// grid cell of a price; identical IEEE single operations on host and device (no FMA contraction)
+// grid cell of a price: integer arithmetic on the IEEE bit pattern (monotone for p >= 0; negative p -> cell 0)
 #ifdef __CUDACC__
 __host__ __device__
 #endif
-inline int cell_of(float p, float glo, float inv_w, int ncell) {
-#ifdef __CUDA_ARCH__
-    const float t = __fmul_rn(__fsub_rn(p, glo), inv_w);
-    int c = __float2int_rd(t);
-    c = c < 0 ? 0 : c;
-    return c > ncell - 1 ? ncell - 1 : c;
-#else
-    const volatile float d = p - glo;
-    const volatile float t = d * inv_w;
-    if (!(t > 0.0f)) return 0;                       // also NaN
-    if (t >= (float)(ncell - 1)) return ncell - 1;
-    return (int)t;                                   // t > 0: truncation == floor
-#endif
+inline int cell_of_bits(int32_t bits, int32_t obase, int32_t shift, int32_t ncell) {
+    const int32_t o = bits > obase ? bits : obase;
+    const int32_t c = (o - obase) >> shift;
+    return c < ncell - 1 ? c : ncell - 1;
 }
 
 }  // namespace qmmx

@@ -1,25 +1,28 @@
-// Host-side builder of the exact price -> {far | level k} classification tables (see tables.h).
+// Host-side builder of the exact price-classification tables (see tables.h).
 // Compiled with -ffp-contract=off: every double/float operation below is a plain IEEE operation, i.e.
-// the same arithmetic CPython performs in qmmx_monolithic.py:1543-1545.
+// the same arithmetic CPython performs in qmmx_monolithic.py:1415-1427 and M:1543-1576.
 #include "tables_host.h"
 
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <functional>
 #include <vector>
 
 namespace qmmx {
 
 namespace {
 
-// monotone bijection between finite floats and int32 ordinals (-0.0 -> -1, +0.0 -> 0)
+// monotone bijection between finite floats and int32 ordinals (-0.0 -> -1, +0.0 -> 0); for p >= 0 the
+// ordinal is the IEEE bit pattern, which is what the kernels use
 inline int32_t f2o(float f) {
     int32_t i;
     std::memcpy(&i, &f, 4);
     return i ^ ((i >> 31) & 0x7fffffff);
 }
-inline float o2f(int32_t o) {
+inline float o2f(int64_t o64) {
+    const int32_t o = (int32_t)o64;
     int32_t i = o ^ ((o >> 31) & 0x7fffffff);
     float f;
     std::memcpy(&f, &i, 4);
@@ -51,30 +54,94 @@ void refine(const Classifier& z, int64_t lo, int zlo, int64_t hi, int zhi, std::
     if (zlo == zhi) return;
     if (hi == lo + 1) { out.push_back({(int32_t)lo, zlo}); return; }
     const int64_t mid = lo + (hi - lo) / 2;
-    const int zm = z(o2f((int32_t)mid));
+    const int zm = z(o2f(mid));
     refine(z, lo, zlo, mid, zm, out);
     refine(z, mid, zm, hi, zhi, out);
 }
 
+using Pred = std::function<bool(float)>;
+
+// The set {p fp32 : ok(p)} is an interval around `center` (ok is monotone on each side of it).
+// Returns false when it is empty.
+bool true_interval(const Pred& ok, double center, float* lo_out, float* hi_out) {
+    const int64_t omin = f2o(-FLT_MAX), omax = f2o(FLT_MAX);
+    if (!(std::fabs(center) < (double)FLT_MAX)) return false;
+    const int64_t oc0 = f2o((float)center);
+    int64_t oc = INT64_MIN;
+    for (int64_t d = -2; d <= 2; ++d) {
+        const int64_t q = oc0 + d;
+        if (q >= omin && q <= omax && ok(o2f(q))) { oc = q; break; }
+    }
+    if (oc == INT64_MIN) return false;
+    int64_t a = omin, b = oc;            // first true in [omin, oc]
+    while (a < b) {
+        const int64_t m = a + (b - a) / 2;
+        if (ok(o2f(m))) b = m; else a = m + 1;
+    }
+    *lo_out = o2f(a);
+    a = oc; b = omax;                    // last true in [oc, omax]
+    while (a < b) {
+        const int64_t m = a + (b - a + 1) / 2;
+        if (ok(o2f(m))) a = m; else b = m - 1;
+    }
+    *hi_out = o2f(a);
+    return true;
+}
+
 }  // namespace
 
-int build_tables(int L, const double* price, const uint8_t* solid, double prox, DevTables* T, std::string* err) {
+double confidence_f64(double dist, bool solid, int tc, double prox) {   // M:1415-1427
+    double base = 1.0 - (dist / (0.0001 > prox ? 0.0001 : prox));
+    if (!(base > 0.0)) base = 0.0;
+    base += solid ? 0.08 : 0.02;
+    if (tc <= 1) base += 0.10;
+    else if (tc == 2) base -= 0.08;
+    else base -= (0.08 * 2);
+    base += 0.03;
+    const double m = base < 1.0 ? base : 1.0;
+    return m > 0.0 ? m : 0.0;
+}
+
+int build_tables(int L, const double* price, const uint8_t* solid, double prox, double qmin, DevTables* T,
+                 std::string* err) {
     std::memset(T, 0, sizeof(*T));
     T->L = L;
+    const float finf = INFINITY;
     for (int j = 0; j < L; ++j) {
-        T->price[j] = price[j];
-        T->solid[j] = solid[j] ? 1 : 0;
+        DevLevel& D = T->lev[j];
+        D.price = price[j];
         int c06 = 0, c015 = 0;
         for (int i = 0; i < L; ++i) {
             if (std::fabs(price[i] - price[j]) <= 0.6) ++c06;
             if (std::fabs(price[i] - price[j]) <= 0.15) ++c015;
         }
-        T->confl06[j] = c06 > 1;
-        T->confl015[j] = c015 >= 2;
+        D.flags = (solid[j] ? kLvSolid : 0u) | (c06 > 1 ? kLvConfl06 : 0u) | (c015 >= 2 ? kLvConfl015 : 0u);
+        const double lp = price[j];
+        // contact window: a latched level stays latched while |lp - p| <= prox (M:1574 releases on >)
+        D.wlo = finf; D.whi = -finf;
+        true_interval([&](float pf) { return !(std::fabs(lp - (double)pf) > prox); }, lp, &D.wlo, &D.whi);
+        // confidence gate per touch bucket: pass <=> !(conf < qmin)  (M:1628)
+        for (int b = 0; b < 3; ++b) {
+            D.cpass[b][0] = finf; D.cpass[b][1] = -finf;
+            const bool sol = solid[j] != 0;
+            true_interval([&](float pf) {
+                return !(confidence_f64(std::fabs(lp - (double)pf), sol, b + 1, prox) < qmin);
+            }, lp, &D.cpass[b][0], &D.cpass[b][1]);
+        }
+    }
+    for (int k = 0; k < L; ++k) {
+        uint64_t cand = 0;
+        for (int j = 0; j < L; ++j) {
+            if (j == k) continue;
+            const DevLevel &A = T->lev[k], &B = T->lev[j];
+            if (A.wlo <= A.whi && B.wlo <= B.whi && B.wlo <= A.whi && A.wlo <= B.whi) cand |= 1ull << j;
+        }
+        T->lev[k].cand_lo = (uint32_t)cand;
+        T->lev[k].cand_hi = (uint32_t)(cand >> 32);
     }
     if (L == 0) {
-        T->Z = 1; T->zhi[0] = FLT_MAX; T->zlev[0] = kFar;
-        T->ncell = 1; T->glo = 0.0f; T->inv_w = 1.0f; T->cell[0] = kFar;
+        T->Z = 1; T->zhi[0] = finf; T->zlev[0] = kFar;
+        T->ncell = 1; T->shift = 0; T->obase = 0; T->cell[0] = kFar;
         return 0;
     }
     const Classifier z{L, price, prox};
@@ -99,16 +166,16 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
 
     std::vector<Zone> zones;
     int64_t lo = probes[0];
-    int zlo = z(o2f((int32_t)lo));
+    int zlo = z(o2f(lo));
     for (size_t i = 1; i < probes.size(); ++i) {
         const int64_t hi = probes[i];
-        const int zhi = z(o2f((int32_t)hi));
+        const int zhi = z(o2f(hi));
         refine(z, lo, zlo, hi, zhi, zones);
         lo = hi; zlo = zhi;
     }
     zones.push_back({(int32_t)omax, zlo});
     if ((int)zones.size() > kMaxZones) {
-        if (err) *err = "level set produces more than 256 price zones";
+        if (err) *err = "level set produces too many price zones";
         return -1;
     }
     T->Z = (int)zones.size();
@@ -116,19 +183,40 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
         T->zhi[i] = o2f(zones[i].hi);
         T->zlev[i] = zones[i].lev < 0 ? kFar : (uint8_t)zones[i].lev;
     }
-    // +inf and NaN never compare <= zhi: give the last zone an infinite bound so the device search ends
-    T->zhi[T->Z - 1] = INFINITY;
+    // +inf and NaN never compare <= a finite bound: the last zone is unbounded so the device search ends there
+    T->zhi[T->Z - 1] = finf;
 
-    // uniform grid over [min level - prox - margin, max level + prox + margin)
-    double pmin = price[0], pmax = price[0];
-    for (int j = 1; j < L; ++j) { pmin = std::min(pmin, price[j]); pmax = std::max(pmax, price[j]); }
-    const double target_w = 1.0 / 64.0;
-    const double glo = pmin - prox - 4 * target_w, ghi = pmax + prox + 4 * target_w;
-    int ncell = (int)std::ceil((ghi - glo) / target_w);
-    ncell = std::max(1, std::min(kMaxCells, ncell));
-    T->ncell = ncell;
-    T->glo = (float)glo;
-    T->inv_w = (float)((double)ncell / (ghi - glo));
+    // ---- grid over fp32 ordinals: full coverage of all windows when it fits at <= 64 ulps per cell,
+    //      else the densest cluster of levels at 16 ulps per cell (prices outside resolve through the zones)
+    std::vector<int> order(L);
+    for (int j = 0; j < L; ++j) order[j] = j;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return price[a] < price[b]; });
+    auto ord_of = [&](double x) -> int64_t {
+        if (x >= (double)FLT_MAX) return omax;
+        if (x <= 0.0) return 0;
+        return std::max<int64_t>(0, f2o((float)x));
+    };
+    const int64_t margin = 64;
+    int64_t o_lo = std::max<int64_t>(0, ord_of(price[order[0]] - prox) - margin);
+    int64_t o_hi = ord_of(price[order[L - 1]] + prox) + margin;
+    int shift = -1;
+    for (int s = 2; s <= 6; ++s)
+        if (((o_hi - o_lo) >> s) + 1 <= kMaxCells) { shift = s; break; }
+    if (shift < 0) {
+        shift = 4;
+        const int64_t cap = ((int64_t)kMaxCells << shift) - 2 * margin;
+        int best = 0, best_n = 0;
+        for (int i = 0; i < L; ++i) {
+            const int64_t a = ord_of(price[order[i]] - prox);
+            int n = 0;
+            for (int j = i; j < L; ++j) { if (ord_of(price[order[j]] + prox) - a <= cap) ++n; else break; }
+            if (n > best_n) { best_n = n; best = i; }
+        }
+        o_lo = std::max<int64_t>(0, ord_of(price[order[best]] - prox) - margin);
+        o_hi = std::min<int64_t>(o_lo + ((int64_t)kMaxCells << shift) - 1, omax);
+    }
+    const int ncell = (int)std::min<int64_t>(kMaxCells, ((o_hi - o_lo) >> shift) + 1);
+    T->ncell = ncell; T->shift = shift; T->obase = (int32_t)o_lo;
 
     auto zone_index = [&](int64_t o) {   // first zone whose upper ordinal >= o
         int a = 0, b = (int)zones.size() - 1;
@@ -138,25 +226,59 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
         }
         return a;
     };
-    int64_t cell_lo = omin;
     for (int c = 0; c < ncell; ++c) {
-        // last ordinal whose cell index is <= c (cell_of is monotone non-decreasing in p)
-        int64_t a = cell_lo, b = omax;
-        if (cell_of(o2f((int32_t)cell_lo), T->glo, T->inv_w, ncell) > c) { T->cell[c] = kMixed; continue; }  // empty
-        if (c == ncell - 1) a = omax;
-        else {
-            while (a < b) {
-                const int64_t m = a + (b - a + 1) / 2;
-                if (cell_of(o2f((int32_t)m), T->glo, T->inv_w, ncell) <= c) a = m; else b = m - 1;
-            }
-        }
-        const int64_t cell_hi = a;
-        const int z0 = zone_index(cell_lo), z1 = zone_index(cell_hi);
+        const int64_t c_lo = (c == 0) ? omin : o_lo + ((int64_t)c << shift);
+        const int64_t c_hi = (c == ncell - 1) ? omax : o_lo + (((int64_t)c + 1) << shift) - 1;
+        const int z0 = zone_index(std::min(c_lo, omax)), z1 = zone_index(std::min(c_hi, omax));
         T->cell[c] = (z0 == z1) ? T->zlev[z0] : kMixed;
-        cell_lo = cell_hi + 1;
-        if (cell_lo > omax) { for (int r = c + 1; r < ncell; ++r) T->cell[r] = kMixed; break; }
     }
     return 0;
+}
+
+// sklearn-form LR gate (M:1454-1466) evaluated on the host for every (day, level, side, touch count):
+// x = [lvl_type(=1), |level - stop|, touch_count, dir_up];  prob = 1 / (1 + exp(-(b + w.x))), accumulated left
+// to right in float64 exactly like oracle/headless.py:lr_prob.  mask bit (side*16 + tc) = gate FAILS.
+void build_ml_tables(int L, const double* price, double sp, double qmin, const double* lr, int n_lr,
+                     uint32_t* mask, double* prob) {
+    for (int day = 0; day < n_lr; ++day) {
+        const double* m = lr + 5 * day;
+        for (int k = 0; k < kMaxLevels; ++k) {
+            uint32_t bits = 0;
+            for (int side = 0; side < 2; ++side) {
+                for (int tc = 0; tc < 16; ++tc) {
+                    double pr = 0.0;
+                    if (k < L) {
+                        const double lp = price[k];
+                        const double stop = side == 0 ? lp - sp : lp + sp;      // M:1669-1674
+                        const double distf = std::fabs(lp - stop);
+                        double z = m[4];
+                        z = z + m[0] * 1.0;
+                        z = z + m[1] * distf;
+                        z = z + m[2] * (double)tc;
+                        z = z + m[3] * (side == 0 ? 1.0 : 0.0);
+                        pr = 1.0 / (1.0 + std::exp(-z));
+                        if (!(pr >= qmin)) bits |= 1u << (side * 16 + tc);
+                    }
+                    if (prob) prob[(((size_t)day * kMaxLevels + k) * 2 + side) * 16 + tc] = pr;
+                }
+            }
+            mask[(size_t)day * kMaxLevels + k] = bits;
+        }
+    }
+}
+
+// smallest float64 z with sigmoid_policy(z) >= target (M:20-26, libm exp as CPython uses it); 0 < target < 1
+double sigmoid_threshold(double target) {
+    auto sig = [](double x) { return 1.0 / (1.0 + std::exp(-x)); };
+    double lo = -50.0, hi = 50.0;              // sig(lo) < target <= sig(hi)
+    for (int it = 0; it < 200; ++it) {
+        const double mid = lo + (hi - lo) / 2;
+        if (mid <= lo || mid >= hi) break;
+        if (sig(mid) >= target) hi = mid; else lo = mid;
+    }
+    // walk to the exact boundary over adjacent doubles
+    while (sig(std::nextafter(hi, -INFINITY)) >= target) hi = std::nextafter(hi, -INFINITY);
+    return hi;
 }
 
 int classify_bruteforce(int L, const double* price, double prox, float p) {
@@ -165,11 +287,13 @@ int classify_bruteforce(int L, const double* price, double prox, float p) {
 }
 
 int classify_tables(const DevTables* T, float p) {
-    uint8_t v = T->cell[cell_of(p, T->glo, T->inv_w, T->ncell)];
+    int32_t bits;
+    std::memcpy(&bits, &p, 4);
+    uint8_t v = T->cell[cell_of_bits(bits, T->obase, T->shift, T->ncell)];
     if (v == kMixed) {
         int a = 0, b = T->Z - 1;
         while (a < b) {
-            const int m = (a + b) / 2;
+            const int m = (a + b) >> 1;
             if (p <= T->zhi[m]) b = m; else a = m + 1;
         }
         v = T->zlev[a];

@@ -4,10 +4,18 @@
 #include "tables.h"
 
 namespace qmmx {
-// Build the exact classification tables for one (level set, CONTACT_PROX). Returns 0 or -1 (+err text).
-int build_tables(int L, const double* price, const uint8_t* solid, double prox, DevTables* T, std::string* err);
+// Build the exact classification tables for one (level set, CONTACT_PROX, Q_MIN_PROB). Returns 0 or -1 (+err).
+int build_tables(int L, const double* price, const uint8_t* solid, double prox, double qmin, DevTables* T,
+                 std::string* err);
 // float64 brute force of qmmx_monolithic.py:1543-1545: level index, or -1 when too far / no levels
 int classify_bruteforce(int L, const double* price, double prox, float p);
 // the table lookup exactly as the kernels perform it (host mirror, for tests)
 int classify_tables(const DevTables* T, float p);
+// compute_confidence (M:1415-1427) with direction known, plain IEEE float64
+double confidence_f64(double dist, bool solid, int tc, double prox);
+// host-evaluated sklearn-form LR gate: mask [n_lr][kMaxLevels], prob [n_lr][kMaxLevels][2][16] (or null)
+void build_ml_tables(int L, const double* price, double sp, double qmin, const double* lr, int n_lr,
+                     uint32_t* mask, double* prob);
+// smallest float64 z with 1 / (1 + exp(-z)) >= target
+double sigmoid_threshold(double target);
 }  // namespace qmmx

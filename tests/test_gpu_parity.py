@@ -1,0 +1,366 @@
+"""GPU parity tests: libqmmx_mc.so (through its C ABI) against the oracle on the same inputs.
+
+Bar: bit-exact entry/exit bar indices, sides, level ids, reason codes, trade counts and every integer
+counter; per-trade PnL equal as fp32; fp64 sums within 1e-9 relative (the north-star asks 1e-6).
+"""
+import numpy as np
+import pytest
+
+from oracle import c_oracle as CO
+from oracle import headless as H
+from qmmx_monolithic_monte_carlo_b200 import abi
+from qmmx_monolithic_monte_carlo_b200 import engine as E
+from qmmx_monolithic_monte_carlo_b200 import fixtures as F
+from tests.golden_util import load_engine_cases, load_jitter_cases, levels_by_name
+from tests.test_c_oracle import c_inputs
+
+pytestmark = pytest.mark.gpu
+
+ENGINE_CASES = load_engine_cases()
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = E.MCEngine(0)
+    yield e
+    e.close()
+
+
+def assert_agg_equal(a, b, *, sums_rel=1e-9):
+    """a: abi.Agg from the GPU, b: abi.Agg from the oracle."""
+    for f in ("n_paths", "n_steps", "n_trades", "n_wins", "n_open", "n_trade_overflow"):
+        assert getattr(a, f) == getattr(b, f), f
+    assert list(a.entry_hist) == list(b.entry_hist)
+    assert list(a.exit_hist) == list(b.exit_hist)
+    assert list(a.pnl_hist) == list(b.pnl_hist)
+    for f in ("sum_pnl", "sum_pnl2", "sum_path_pnl2", "sum_open_mtm"):
+        x, y = getattr(a, f), getattr(b, f)
+        assert x == pytest.approx(y, rel=sums_rel, abs=1e-9), f
+    if b.n_paths:
+        assert a.max_path_pnl == b.max_path_pnl and a.min_path_pnl == b.min_path_pnl
+
+
+def assert_trades_equal(tr, cnt, otr, ocnt):
+    assert np.array_equal(cnt, ocnt)
+    for f in ("entry_bar", "exit_bar", "side", "reason", "level_id", "entry", "exit", "pnl"):
+        m = np.arange(tr.shape[1])[None, :] < np.minimum(cnt, tr.shape[1])[:, None]
+        assert np.array_equal(tr[f][m], otr[f][m]), f
+
+
+def configure(eng, lv_price, lv_solid, params, lr=None, pol=None):
+    eng.set_levels_raw(lv_price, lv_solid)
+    eng.set_params(params)
+    eng.set_lr(lr)
+    eng.set_policy(pol)
+
+
+@pytest.mark.parametrize("case", ENGINE_CASES, ids=[c["name"] for c in ENGINE_CASES])
+def test_gpu_matches_reference_golden(eng, case):
+    lv, params, lr_a, pol_a = c_inputs(case)
+    configure(eng, [l.price for l in lv], [l.solid for l in lv], params, lr_a, pol_a)
+    close = case["close"]
+    eng.upload_bars(close)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=close.shape)
+    assert np.array_equal(codes, case["codes"])
+    for j in range(case["paths"]):
+        gt = case["trades"][j]
+        assert cnt[j] == len(gt)
+        for g, t in zip(gt, tr[j]):
+            assert (g["entry_bar"], g["exit_bar"], g["side"], g["level"], g["reason"]) == \
+                   (t["entry_bar"], t["exit_bar"], t["side"], t["level_id"], t["reason"])
+            assert np.float32(g["pnl"]) == t["pnl"] and np.float32(g["entry"]) == t["entry"]
+    a = res[0].agg
+    assert list(a.entry_hist) == np.bincount(case["codes"].ravel(), minlength=20).tolist()
+
+
+PARAM_SETS = [
+    dict(contact_prox=0.1, cooldown_s=120),
+    dict(contact_prox=0.1, cooldown_s=8),
+    dict(contact_prox=0.05, cooldown_s=300, stop_padding=0.6, tp_padding=0.5),
+    dict(contact_prox=0.2, cooldown_s=0, q_min_prob=0.3, overtouch_limit=7),
+    dict(contact_prox=0.1, cooldown_s=61, q_min_prob=0.9),
+]
+
+
+@pytest.mark.parametrize("pi", range(len(PARAM_SETS)))
+@pytest.mark.parametrize("levels", ["fix30", "blue4"])
+def test_gpu_matches_oracle_random_paths(eng, pi, levels):
+    rows, price, solid = E.sort_levels(levels_by_name(levels))
+    params = abi.make_params(**PARAM_SETS[pi])
+    close = F.host_gbm_closes(5000 + 37 * pi, 390, seed=100 + pi, round_cents=(pi % 2 == 1))
+    configure(eng, price, solid, params)
+    eng.upload_bars(close)
+    res, tr, cnt, codes = eng.run_scan(trades=48, codes=True, paths_steps=close.shape)
+    o = CO.run_paths(close, price, solid, params, want_codes=True, max_trades=48, n_threads=4)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    # aggregate-only (production) kernel gives the same aggregates as the parity kernel
+    res2 = eng.run_scan()
+    assert_agg_equal(res2[0].agg, o["agg"])
+
+
+def _lr_tables(rng, days):
+    lr = np.column_stack([rng.normal(0, 0.5, days), rng.normal(0, 0.5, days), rng.normal(-0.3, 0.4, days),
+                          rng.normal(0, 0.8, days), rng.normal(0.6, 0.5, days)])
+    pol = rng.normal(0, 0.5, (days, 3, 7))
+    pol[:, 0, 0] += 1.0; pol[:, 1, 0] += 1.0; pol[:, 2, 0] -= 1.0
+    return lr, pol
+
+
+@pytest.mark.parametrize("mode", ["and", "blend", "policy", "and+policy", "ml_off"])
+def test_gpu_lr_gates_multi_day(eng, mode):
+    rng = np.random.default_rng(11)
+    days = 3
+    lr, pol = _lr_tables(rng, days)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    kw = dict(contact_prox=0.1, cooldown_s=120)
+    if mode == "blend":
+        kw.update(use_blend=True, w_rules=0.6, w_ml=0.4)
+    if "policy" in mode:
+        kw.update(disable_policy_gate=False)
+    if mode == "ml_off":
+        kw.update(disable_ml_gate=True)
+    params = abi.make_params(**kw)
+    close = F.host_gbm_closes(3000, 390 * days, seed=7, sigma=0.10)
+    use_lr = None if mode == "policy" else lr
+    use_pol = pol if "policy" in mode else None
+    configure(eng, price, solid, params, use_lr, use_pol)
+    eng.upload_bars(close)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=close.shape)
+    o = CO.run_paths(close, price, solid, params, lr=use_lr, policy=use_pol, want_codes=True, max_trades=64,
+                     n_threads=4)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    hist = res[0].entry_hist
+    if mode in ("and", "and+policy"):
+        assert hist["ML_CONF_LOW"] > 0
+    if mode == "blend":
+        assert hist["COMBINED_LOW"] > 0
+    if "policy" in mode:
+        assert hist["ONLINE_POLICY"] > 0
+    assert hist["OK"] > 0
+
+
+def test_gpu_hl_exit_mode(eng):
+    g = abi.make_gbm(sub_steps=4)
+    c, h, l = CO.gen_gbm(77, 0, 4000, 390, g, ohlc=True)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True)
+    configure(eng, price, solid, params)
+    eng.upload_bars(c, h, l)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=c.shape)
+    o = CO.run_paths(c, price, solid, params, high=h, low=l, want_codes=True, max_trades=64, n_threads=4)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+
+
+def test_gpu_edge_cases(eng):
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120)
+    # no levels: every step NOLEVELS
+    configure(eng, [], [], params)
+    close = F.host_gbm_closes(100, 50, seed=3)
+    eng.upload_bars(close)
+    r = eng.run_scan()[0]
+    assert r.entry_hist["NOLEVELS"] == 100 * 50 and r.n_trades == 0
+    # ragged path count (not a multiple of 32), 1 step, flat path, trade-record overflow
+    configure(eng, price, solid, params)
+    for paths, steps in [(1, 1), (33, 7), (257, 391), (31, 2)]:
+        close = F.host_gbm_closes(paths, steps, seed=paths)
+        eng.upload_bars(close)
+        res, tr, cnt, codes = eng.run_scan(trades=2, codes=True, paths_steps=close.shape)
+        o = CO.run_paths(close, price, solid, params, want_codes=True, max_trades=2)
+        assert np.array_equal(codes, o["codes"])
+        assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+        assert_agg_equal(res[0].agg, o["agg"])
+    flat = np.full((40, 64), 648.76, dtype=np.float32)
+    flat[20:, :32] = 648.80
+    eng.upload_bars(flat)
+    res, tr, cnt, codes = eng.run_scan(trades=4, codes=True, paths_steps=flat.shape)
+    o = CO.run_paths(flat, price, solid, params, want_codes=True, max_trades=4)
+    assert np.array_equal(codes, o["codes"]) and (codes == abi.ENTRY_CODES.index("DIR_UNKNOWN")).sum() >= 64 * 20
+    # empty input
+    eng.upload_bars(np.zeros((0, 0), dtype=np.float32))
+    r = eng.run_scan()[0]
+    assert r.n_paths == 0 and r.n_steps == 0
+
+
+def test_gpu_tiny_prices_flag(eng):
+    # prices around 0.01: the +-1e-9 guard band matters; QMMX_F_TINY_PRICES evaluates it in float64
+    rng = np.random.default_rng(5)
+    base = np.float32(0.01)
+    steps, paths = 200, 512
+    inc = rng.integers(-2, 3, size=(steps, paths)).astype(np.float32) * np.float32(9.3e-10)
+    close = (base + np.cumsum(inc, axis=0)).astype(np.float32)
+    price = np.array([0.01, 0.0100001]); solid = np.array([1, 0], dtype=np.uint8)
+    params = abi.make_params(contact_prox=1e-6, stop_padding=3e-8, tp_padding=3e-8, cooldown_s=60)
+    params.flags |= abi.F_TINY_PRICES
+    configure(eng, price, solid, params)
+    eng.upload_bars(close)
+    res, tr, cnt, codes = eng.run_scan(trades=32, codes=True, paths_steps=close.shape)
+    o = CO.run_paths(close, price, solid, params, want_codes=True, max_trades=32)
+    assert np.array_equal(codes, o["codes"])
+    assert_agg_equal(res[0].agg, o["agg"])
+
+
+def test_gpu_param_grid_sweep(eng):
+    rows, price, solid = E.sort_levels(F.levels_30())
+    grid = [abi.make_params(contact_prox=0.1, stop_padding=sp, tp_padding=tp, cooldown_s=cd)
+            for sp in (0.10, 0.35, 0.85) for tp in (0.15, 0.5) for cd in (0, 60, 900)]
+    grid.append(abi.make_params(contact_prox=0.05, q_min_prob=0.5, cooldown_s=120))   # second table
+    close = F.host_gbm_closes(4096, 390, seed=21)
+    configure(eng, price, solid, grid)
+    eng.upload_bars(close)
+    res = eng.run_scan()
+    assert len(res) == len(grid)
+    for p, r in zip(grid, res):
+        o = CO.run_paths(close, price, solid, p, n_threads=4)
+        assert_agg_equal(r.agg, o["agg"])
+
+
+def test_gpu_host_pipeline_equals_resident(eng):
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120)
+    close = F.host_gbm_closes(70001, 390, seed=9)
+    configure(eng, price, solid, params)
+    eng.upload_bars(close)
+    a = eng.run_scan()[0]
+    eng.pin(close)
+    try:
+        b = eng.run_scan_host(close, chunk_paths=16384)[0]
+    finally:
+        eng.unpin(close)
+    o = CO.run_paths(close, price, solid, params, n_threads=8)
+    assert_agg_equal(a.agg, o["agg"])
+    assert_agg_equal(b.agg, o["agg"])
+
+
+def test_gpu_philox_gbm_generator(eng):
+    g = abi.make_gbm()
+    paths, steps = 4096, 390
+    eng.gen_gbm(20250829, 1000, paths, steps, g)
+    c, _, _ = eng.download_bars(paths, steps)
+    oc, _, _ = CO.gen_gbm(20250829, 1000, paths, steps, g)
+    # same Philox stream and operation order; MUFU vs libm transcendentals differ in the last bits
+    assert np.allclose(c, oc, rtol=2e-5, atol=0)
+    lr = np.diff(np.log(np.vstack([np.full((1, paths), g.s0, dtype=np.float64), c.astype(np.float64)])), axis=0)
+    sd = 0.15 * np.sqrt(1 / (252 * 390))
+    assert abs(lr.std() / sd - 1) < 0.01 and abs(lr.mean()) < 5 * sd / np.sqrt(lr.size)
+    # sharding: path ids are global
+    eng.gen_gbm(20250829, 1000 + 96, 64, steps, g)
+    c2, _, _ = eng.download_bars(64, steps)
+    assert np.array_equal(c2, c[:, 96:160])
+    # OHLC recipe
+    g4 = abi.make_gbm(sub_steps=4, round_cents=True)
+    eng.gen_gbm(5, 0, 1000, 100, g4)
+    c4, h4, l4 = eng.download_bars(1000, 100, hl=True)
+    o4 = CO.gen_gbm(5, 0, 1000, 100, g4, ohlc=True)
+    assert np.all(h4 >= c4) and np.all(l4 <= c4)
+    assert np.mean(c4 == o4[0]) > 0.99 and np.allclose(c4, o4[0], atol=0.011)
+
+
+def test_gpu_fused_equals_generate_then_scan(eng):
+    rows, price, solid = E.sort_levels(F.levels_30())
+    rng = np.random.default_rng(2)
+    lr, _ = _lr_tables(rng, 1)
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120)
+    configure(eng, price, solid, params, lr)
+    g = abi.make_gbm()
+    paths, steps = 100_003, 390
+    fused = eng.run_fused_gbm(42, 7, paths, steps, g)[0]
+    eng.gen_gbm(42, 7, paths, steps, g)
+    scan = eng.run_scan()[0]
+    assert_agg_equal(fused.agg, scan.agg, sums_rel=1e-12)
+    # and the device-generated bars scanned by the oracle give the same aggregates again
+    c, _, _ = eng.download_bars(paths, steps)
+    o = CO.run_paths(c, price, solid, params, lr=lr, n_threads=8)
+    assert_agg_equal(scan.agg, o["agg"])
+    # statistical tier: oracle-generated (libm) paths vs device-generated paths, same seed
+    oc, _, _ = CO.gen_gbm(42, 7, 20000, steps, g)
+    oo = CO.run_paths(oc, price, solid, params, lr=lr, n_threads=8)["agg"]
+    eng.gen_gbm(42, 7, 20000, steps, g)
+    dd = eng.run_scan()[0].agg
+    assert abs(dd.n_trades - oo.n_trades) <= 5 * np.sqrt(oo.n_trades) * 0.05 + 20
+    # OHLC fused
+    p2 = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True)
+    configure(eng, price, solid, p2)
+    g4 = abi.make_gbm(sub_steps=4)
+    f4 = eng.run_fused_gbm(3, 0, 20011, 390, g4)[0]
+    eng.gen_gbm(3, 0, 20011, 390, g4)
+    s4 = eng.run_scan()[0]
+    assert_agg_equal(f4.agg, s4.agg, sums_rel=1e-12)
+
+
+def test_gpu_bootstrap_generator(eng):
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    paths, steps = 3000, 5 * 390
+    eng.gen_bootstrap(9, 11, paths, steps, window, 5)
+    c, h, l = eng.download_bars(paths, steps, hl=True)
+    oc, oh, ol = CO.gen_bootstrap(9, 11, paths, steps, window, 5)
+    assert np.array_equal(c, oc) and np.array_equal(h, oh) and np.array_equal(l, ol)   # integer draws + IEEE products
+    # config 5: multi-day paths, per-day LR weights, exits on high/low
+    rng = np.random.default_rng(4)
+    lr, pol = _lr_tables(rng, 5)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True)
+    configure(eng, price, solid, params, lr)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=c.shape)
+    o = CO.run_paths(c, price, solid, params, high=h, low=l, lr=lr, want_codes=True, max_trades=64, n_threads=8)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+
+
+def test_gpu_lr_score_matches_fp32_reference(eng):
+    import torch
+    rng = np.random.default_rng(0)
+    for dim, heads in [(7, 3), (4, 1), (32, 8)]:
+        x = rng.normal(0, 1, (10007, dim)).astype(np.float32)
+        w = rng.normal(0, 1, (heads, dim)).astype(np.float32)
+        b = rng.normal(0, 1, heads).astype(np.float32)
+        out = eng.lr_score(x, w, b)
+        ref = torch.sigmoid(torch.from_numpy(x) @ torch.from_numpy(w).T + torch.from_numpy(b)).numpy()
+        assert np.allclose(out, ref, atol=2e-6, rtol=0)     # fp32 FMA accumulation, tolerance 2e-6 absolute
+        out2 = eng.lr_score(x, w, None)
+        ref2 = torch.sigmoid(torch.from_numpy(x) @ torch.from_numpy(w).T).numpy()
+        assert np.allclose(out2, ref2, atol=2e-6, rtol=0)
+
+
+@pytest.mark.parametrize("case", load_jitter_cases()[:3], ids=lambda c: c["name"])
+def test_gpu_jitter_mc_replay_is_exact(eng, case):
+    lv = H.sort_levels(levels_by_name(case["levels"]))
+    P = H.Params(contact_prox=case["contact_prox"])
+    bars = case["bars"]
+    n = case["n"]
+    c, h, l = list(bars["c"])[-n:], list(bars["h"])[-n:], list(bars["l"])[-n:]
+    cands = H.find_candidates(c, lv, P, touch_limit=case["touch_limit"])
+    if not cands:
+        pytest.skip("no candidates")
+    trials = 2000
+    rng = np.random.default_rng(1)
+    normals = rng.standard_normal((trials, len(cands), 4))
+    uniforms = rng.random((trials, len(cands)))
+    sig = (0.02, 0.01, 0.005, 0.003)
+    ref = H.jitter_monte_carlo(bars, lv, P, n=n, touch_limit=case["touch_limit"], trials=trials,
+                               level_jitter_std=sig[0], entry_slip_std=sig[1], stop_slip_std=sig[2],
+                               target_slip_std=sig[3], draws=(normals, uniforms))
+    out = eng.run_jitter(h, l, cands, P.stop_padding, P.tp_padding, sig, trials, replay=(normals, uniforms))
+    assert np.array_equal(out["totals"], np.array(ref["totals"]))
+    assert np.array_equal(out["drawdowns"], np.array(ref["drawdowns"]))
+    s = H.mc_summary(list(out["totals"]), list(out["drawdowns"]), list(out["wins"]), list(out["losses"]),
+                     list(out["opens"]))
+    for k in ("mean", "median", "stdev", "best", "worst", "var05", "cvar05", "dd_mean", "dd_worst", "wins",
+              "losses", "opens"):
+        assert s[k] == ref[k], k
+    # statistical tier: device Philox draws vs the reference's Mersenne-Twister draws
+    big = 200_000
+    dev = eng.run_jitter(h, l, cands, P.stop_padding, P.tp_padding, (0.02, 0.01, 0.0, 0.0), big, seed=99)
+    refs = H.jitter_monte_carlo(bars, lv, P, n=n, touch_limit=case["touch_limit"], trials=4000, seed=5)
+    se = refs["stdev"] / np.sqrt(4000) + dev["totals"].std() / np.sqrt(big)
+    assert abs(dev["totals"].mean() - refs["mean"]) < 5 * se + 1e-9     # 5-sigma bound on the mean total R
