@@ -197,7 +197,8 @@ def main():
     close = F.host_gbm_closes(paths, STEPS_PER_PATH, seed=F.HOST_SEED + rank)   # weak scaling: own paths per rank
 
     eng = E.MCEngine(local_rank)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()           # non-default: its handle is non-NULL, so the ctx can adopt it
+    torch.cuda.set_stream(stream)
     eng.set_stream(stream.cuda_stream)
     eng.set_levels(wl["levels"])
     eng.set_params(params)

@@ -30,7 +30,8 @@ struct BlockShared {
     uint8_t zlev[kMaxZones];
     DevCombo combo;
     // block aggregate, flushed to the global reduction buffer with atomics
-    unsigned long long u[QMMX_AGG_NU];
+    unsigned long long u[U_HIST];
+    uint32_t hist[QMMX_PNL_HIST_BINS];           // per-path PnL histogram (32-bit: native shared-memory atomics)
     double d[QMMX_AGG_ND];
     double xmax, xnegmin;
     // per-thread touch counters: 4-bit saturating, 64 levels -> 8 words per thread, [word][thread]
@@ -98,8 +99,12 @@ struct PathEngine {
     float entry;
     int entry_bar;
     uint32_t latch_lo, latch_hi;
-    // per-path tallies of the frequent codes (everything else goes straight to shared-memory counters)
-    uint32_t n_over, n_conf, n_ml;
+    // per-path tallies, two 16-bit counters per register (steps per path <= 65535); reduced per warp at path end
+    uint32_t c_gate;       // LEVEL_OVERTOUCHED | CONF_LOW << 16
+    uint32_t c_ml;         // ML_CONF_LOW | winning trades << 16
+    uint32_t c_exit;       // STOP exits | TARGET exits << 16
+    uint32_t c_span;       // IN_POSITION steps | COOLDOWN steps << 16
+    uint32_t c_dir;        // DIR_UNKNOWN
     // per-path accumulators
     double pnl, pnl2, mtm;
     int ntr;
@@ -110,7 +115,7 @@ struct PathEngine {
         path = path_;
         prev = __int_as_float(0x7fc00000);
         last_dir = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
-        latch_lo = 0u; latch_hi = 0u; n_over = 0u; n_conf = 0u; n_ml = 0u;
+        latch_lo = 0u; latch_hi = 0u; c_gate = 0u; c_ml = 0u; c_exit = 0u; c_span = 0u; c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
 #pragma unroll
         for (int w = 0; w < 8; ++w) S.touch[w * kThreads + tid] = 0u;
@@ -192,16 +197,16 @@ struct PathEngine {
         const uint32_t word = tw;
         int tc = (word >> sh) & 15;
         if (isnew && tc < 15) { ++tc; tw = word + (1u << sh); }
-        if (tc >= C.overtouch) { ++n_over; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
+        if (tc >= C.overtouch) { c_gate += 1u; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
         const int b = (tc < 3 ? tc : 3) - 1;
-        if (!(pf >= Lk.cpass[b][0] && pf <= Lk.cpass[b][1])) { ++n_conf; return QMMX_CONF_LOW; }   // M:1628
+        if (!(pf >= Lk.cpass[b][0] && pf <= Lk.cpass[b][1])) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
         const int side = d - 1;                                              // M:1645: up -> long(0), down -> short(1)
         if (C.flags & QMMX_F_USE_BLEND) {                                    // M:1730-1742
             if (blend_fails(S, G, k, pf, tc, d, i / C.spd)) { smem_inc(&S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
         } else if (G.mlmask) {                                               // M:1454-1466, M:1745-1755
             int day = i / C.spd; day = day < G.n_days ? day : G.n_days - 1;
             const uint32_t m = __ldg(&G.mlmask[day * kMaxLevels + k]);
-            if ((m >> (side * 16 + tc)) & 1u) { ++n_ml; return QMMX_ML_CONF_LOW; }
+            if ((m >> (side * 16 + tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
         if (!(C.flags & QMMX_F_DISABLE_POLICY_GATE)) {
@@ -233,13 +238,11 @@ struct PathEngine {
         const double tp = (side == 0) ? (exit_px - e) : (e - exit_px);       // M:1926
         pnl += tp; pnl2 += tp * tp;
         cool_until = i + C.cool_steps;                                       // M:2982, M:269-270
-        smem_inc(&S.u[U_NTRADES]);
-        if (tp > 0) smem_inc(&S.u[U_NWINS]);                                 // label, M:1936
-        smem_inc(&S.u[U_EXIT + reason]);
-        smem_inc(&S.u[U_ENTRY + QMMX_IN_POSITION], (unsigned long long)(i - entry_bar));
+        if (tp > 0) c_ml += 1u << 16;                                        // label, M:1936
+        c_exit += (reason == QMMX_EXIT_STOP) ? 1u : (1u << 16);
         int cd = C.cool_steps < G.steps - i ? C.cool_steps : G.steps - i;
         cd -= 1;
-        if (cd > 0) smem_inc(&S.u[U_ENTRY + QMMX_COOLDOWN], (unsigned long long)cd);
+        c_span += (uint32_t)(i - entry_bar) + ((uint32_t)(cd > 0 ? cd : 0) << 16);
         record(entry_bar, i, side, reason, k, entry, (float)exit_px, (float)tp);
         pos = -1;
     }
@@ -285,7 +288,7 @@ struct PathEngine {
             code = QMMX_NOLEVELS;                                            // M:1524 (tallied as remainder)
         } else if (d == 0) {
             code = QMMX_DIR_UNKNOWN;                                         // M:1538
-            smem_inc(&S.u[U_ENTRY + QMMX_DIR_UNKNOWN]);
+            ++c_dir;
         } else {
             const uint32_t v = classify(pf);
             if (v != kFar) code = contact((int)v, pf, d, i);                 // else TOO_FAR, M:1545
@@ -302,15 +305,13 @@ struct PathEngine {
             const int k = pos & 0xff, side = pos >> 8;
             const double e = (double)entry, last = (double)prev;
             mtm = (side == 0) ? (last - e) : (e - last);
-            smem_inc(&S.u[U_NOPEN]);
-            smem_inc(&S.u[U_EXIT + QMMX_EXIT_OPEN]);
-            smem_inc(&S.u[U_ENTRY + QMMX_IN_POSITION], (unsigned long long)(G.steps - 1 - entry_bar));
+            c_span += (uint32_t)(G.steps - 1 - entry_bar);
             record(entry_bar, -1, side, QMMX_EXIT_OPEN, k, entry, prev, 0.0f);
         }
         if (PARITY && G.tcounts) G.tcounts[path] = ntr;
         double fb = floor((pnl - G.hist_lo) * G.hist_inv_w);
         const int bin = fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
-        smem_inc(&S.u[U_HIST + bin]);
+        atomicAdd(&S.hist[bin], 1u);
     }
 };
 
@@ -347,9 +348,14 @@ __device__ __forceinline__ void warp_accumulate(BlockShared& S, bool active, con
     const double s4 = warp_sum(active ? E.mtm : 0.0);
     const double mx = warp_max(active ? E.pnl : neg_inf);
     const double mn = warp_max(active ? -E.pnl : neg_inf);
-    const unsigned n_over = __reduce_add_sync(0xffffffffu, active ? E.n_over : 0u);
-    const unsigned n_conf = __reduce_add_sync(0xffffffffu, active ? E.n_conf : 0u);
-    const unsigned n_ml = __reduce_add_sync(0xffffffffu, active ? E.n_ml : 0u);
+    // 16-bit fields: a warp sum of 32 values < 65536 each fits 21 bits, so reduce the halves separately
+    const unsigned cg = active ? E.c_gate : 0u, cm = active ? E.c_ml : 0u, ce = active ? E.c_exit : 0u, cs = active ? E.c_span : 0u;
+    const unsigned n_over = __reduce_add_sync(0xffffffffu, cg & 0xffffu), n_conf = __reduce_add_sync(0xffffffffu, cg >> 16);
+    const unsigned n_ml = __reduce_add_sync(0xffffffffu, cm & 0xffffu), n_wins = __reduce_add_sync(0xffffffffu, cm >> 16);
+    const unsigned n_stop = __reduce_add_sync(0xffffffffu, ce & 0xffffu), n_tgt = __reduce_add_sync(0xffffffffu, ce >> 16);
+    const unsigned n_inpos = __reduce_add_sync(0xffffffffu, cs & 0xffffu), n_cool = __reduce_add_sync(0xffffffffu, cs >> 16);
+    const unsigned n_dir = __reduce_add_sync(0xffffffffu, active ? E.c_dir : 0u);
+    const unsigned n_open = __popc(__ballot_sync(0xffffffffu, active && E.pos >= 0));
     const unsigned n = __popc(__ballot_sync(0xffffffffu, active));
     if (lane == 0 && n) {
         atomicAdd(&S.d[D_SUM_PNL], s1); atomicAdd(&S.d[D_SUM_PNL2], s2);
@@ -359,12 +365,21 @@ __device__ __forceinline__ void warp_accumulate(BlockShared& S, bool active, con
         if (n_over) smem_inc(&S.u[U_ENTRY + QMMX_LEVEL_OVERTOUCHED], n_over);
         if (n_conf) smem_inc(&S.u[U_ENTRY + QMMX_CONF_LOW], n_conf);
         if (n_ml) smem_inc(&S.u[U_ENTRY + QMMX_ML_CONF_LOW], n_ml);
+        if (n_dir) smem_inc(&S.u[U_ENTRY + QMMX_DIR_UNKNOWN], n_dir);
+        if (n_wins) smem_inc(&S.u[U_NWINS], n_wins);
+        if (n_stop) smem_inc(&S.u[U_EXIT + QMMX_EXIT_STOP], n_stop);
+        if (n_tgt) smem_inc(&S.u[U_EXIT + QMMX_EXIT_TARGET], n_tgt);
+        if (n_stop + n_tgt) smem_inc(&S.u[U_NTRADES], n_stop + n_tgt);
+        if (n_inpos) smem_inc(&S.u[U_ENTRY + QMMX_IN_POSITION], n_inpos);
+        if (n_cool) smem_inc(&S.u[U_ENTRY + QMMX_COOLDOWN], n_cool);
+        if (n_open) { smem_inc(&S.u[U_NOPEN], n_open); smem_inc(&S.u[U_EXIT + QMMX_EXIT_OPEN], n_open); }
     }
 }
 
 __device__ inline void block_zero_agg(BlockShared& S) {
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
-    for (int t = threadIdx.x; t < QMMX_AGG_NU; t += blockDim.x) S.u[t] = 0ull;
+    for (int t = threadIdx.x; t < U_HIST; t += blockDim.x) S.u[t] = 0ull;
+    for (int t = threadIdx.x; t < QMMX_PNL_HIST_BINS; t += blockDim.x) S.hist[t] = 0u;
     if (threadIdx.x < QMMX_AGG_ND) S.d[threadIdx.x] = 0.0;
     if (threadIdx.x == 0) { S.xmax = neg_inf; S.xnegmin = neg_inf; }
 }
@@ -385,7 +400,7 @@ __device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat,
     }
     __syncthreads();
     for (int t = threadIdx.x; t < QMMX_AGG_NU; t += blockDim.x) {
-        const unsigned long long v = S.u[t];
+        const unsigned long long v = t < U_HIST ? S.u[t] : (unsigned long long)S.hist[t - U_HIST];
         if (v) atomicAdd(&gu[t], v);
     }
     if (threadIdx.x < QMMX_AGG_ND) { const double v = S.d[threadIdx.x]; if (v != 0.0) atomicAdd(&gd[threadIdx.x], v); }

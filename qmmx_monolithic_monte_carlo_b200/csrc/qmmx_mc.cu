@@ -216,6 +216,7 @@ int launch_scan(qmmx_ctx* ctx, const ScanArgs& A, bool parity) {
     const bool hl = ctx->any_hl, tiny = ctx->any_tiny;
     if (hl && (!A.high || !A.low)) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs high/low bars");
     if (A.paths <= 0 || A.steps <= 0) return QMMX_OK;
+    if (A.steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
     int rc = QMMX_OK;
 #define LAUNCH(HLv, PARv, TINYv)                                                              \
     do {                                                                                      \
@@ -644,6 +645,7 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     const dim3 grid = scan_grid(ctx, paths, (int)ctx->params.size());
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if ((rc = init_flat(ctx)) != 0) return rc;
+    if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
     if (paths > 0 && steps > 0) {
         if (gbm->sub_steps == 4) {
             // OHLC recipe: 4 sub-steps per bar; the engine sees high/low only when EXIT_ON_HL is set

@@ -97,6 +97,7 @@ def test_gpu_matches_oracle_random_paths(eng, pi, levels):
     assert_agg_equal(res[0].agg, o["agg"])
     # aggregate-only (production) kernel gives the same aggregates as the parity kernel
     res2 = eng.run_scan()
+    o["agg"].n_trade_overflow = 0            # only the parity-mode record buffer can overflow
     assert_agg_equal(res2[0].agg, o["agg"])
 
 
