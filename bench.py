@@ -166,6 +166,7 @@ def main():
     ap.add_argument("--paths", type=int, default=0, help="override paths per GPU (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--lib", default=None, help="alternate libqmmx_mc build (kernel tuning variants)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -196,7 +197,7 @@ def main():
     lr = lr_weights() if wl["lr"] else None
     close = F.host_gbm_closes(paths, STEPS_PER_PATH, seed=F.HOST_SEED + rank)   # weak scaling: own paths per rank
 
-    eng = E.MCEngine(local_rank)
+    eng = E.MCEngine(local_rank, args.lib)
     stream = torch.cuda.Stream()           # non-default: its handle is non-NULL, so the ctx can adopt it
     torch.cuda.set_stream(stream)
     eng.set_stream(stream.cuda_stream)

@@ -41,24 +41,26 @@ def is_stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/ into libqmmx_mc.so when sources are newer than the library."""
-    if not force and not is_stale():
+def build_library(force: bool = False, verbose: bool = False, out: str = None, defines=()) -> str:
+    """Compile csrc/ into libqmmx_mc.so when sources are newer than the library.
+    `out` / `defines` build a tuning variant (e.g. -DQMMX_BLOCKS_PER_SM=3) beside the product library."""
+    if out is None and not force and not is_stale():
         return LIB
     os.makedirs(_OBJ_DIR, exist_ok=True)
     obj = os.path.join(_OBJ_DIR, "tables_host.o")
     cxx = os.environ.get("CXX", "g++")
     cmd1 = [cxx] + CXX_FLAGS + ["-I", INCLUDE, "-c", os.path.join(CSRC, "tables_host.cpp"), "-o", obj]
-    cmd2 = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [
-        "-I", INCLUDE, "-shared", "-o", LIB + ".tmp", os.path.join(CSRC, "qmmx_mc.cu"), obj]
+    target = out or LIB
+    cmd2 = [_nvcc()] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + [
+        "-I", INCLUDE, "-shared", "-o", target + ".tmp", os.path.join(CSRC, "qmmx_mc.cu"), obj]
     for cmd in (cmd1, cmd2):
         r = subprocess.run(cmd, capture_output=True, text=True)
         if verbose:
             sys.stderr.write(r.stderr)
         if r.returncode != 0:
             raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
-    os.replace(LIB + ".tmp", LIB)
-    return LIB
+    os.replace(target + ".tmp", target)
+    return target
 
 
 if __name__ == "__main__":

@@ -8,6 +8,10 @@
 // float64 predicates (tables.h); the logistic gates use host-evaluated float64 probabilities (same libm as
 // CPython) and a float64 Neumaier dot product on the device.  The file is compiled with --fmad=false so no
 // multiply-add is ever contracted.
+//
+// Register discipline: the per-path state is a bag of scalars that never has its address taken (a single
+// address-taken member sends the whole struct to local memory); block-wide read-only data lives in shared
+// memory and is reached through smem() so the compiler keeps the shared address space.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -22,13 +26,42 @@ constexpr int U_NPATHS = 0, U_NSTEPS = 1, U_NTRADES = 2, U_NWINS = 3, U_NOPEN = 
 constexpr int U_ENTRY = 6, U_EXIT = U_ENTRY + QMMX_N_ENTRY_CODES, U_HIST = U_EXIT + QMMX_N_EXIT_CODES;
 constexpr int D_SUM_PNL = 0, D_SUM_PNL2 = 1, D_SUM_PATH2 = 2, D_SUM_MTM = 3;
 
+constexpr uint32_t kCbHasMl = 1u << 16, kCbHasProb = 1u << 17;   // internal DevCombo.flags bits
+
+struct EngineGlobals {            // read-only run description, copied into shared memory per CTA
+    const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit tc (dir up) / bit 16+tc (dir down) = ML gate FAILS; null = no model
+    const double* mlprob;         // [n_days][kMaxLevels][2][16] P(win) for blend mode; null when unused
+    const double* pol;            // [n_pol][3][7]
+    double z_go, z_skip;          // sigmoid(z) >= 0.60 <=> z >= z_go ; sigmoid(z) < 0.55 <=> z < z_skip
+    double hist_lo, hist_inv_w;
+    int64_t paths;                // row stride of codes
+    // parity-mode outputs (may be null)
+    qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
+    int32_t max_trades, n_days, n_pol, steps;
+};
+
 // ---- shared-memory block state -------------------------------------------------------------------------
+// per-level data on the contact path, 64 bytes, built per CTA from DevLevel + the CTA's combo
+struct HotLevel {
+    float2 thr[2];                      // [side] {lo_thr, hi_thr}: long {stop v, target ^}, short {target v, stop ^}
+    float2 cpass[3];                    // touch bucket: conf >= Q_MIN_PROB  <=>  x <= p <= y
+    uint32_t bit_lo, bit_hi, cand_lo, cand_hi;
+    uint32_t toff, tsh;                 // touch word byte offset (thread 0) and bit shift
+};
+static_assert(sizeof(HotLevel) == 64, "HotLevel layout");
+struct ColdLevel { double price; float wlo, whi; uint32_t flags, pad; };
+
+template <bool WIDE> struct LatchType { typedef uint32_t T; };
+template <> struct LatchType<true> { typedef unsigned long long T; };
+
 struct BlockShared {
     int32_t L, Z, ncell, shift, obase, pad0, pad1, pad2;
-    DevLevel lev[kMaxLevels];
+    alignas(16) HotLevel hot[kMaxLevels];
+    ColdLevel cold[kMaxLevels];
     float zhi[kMaxZones];
     uint8_t zlev[kMaxZones];
     DevCombo combo;
+    EngineGlobals G;
     // block aggregate, flushed to the global reduction buffer with atomics
     unsigned long long u[U_HIST];
     uint32_t hist[QMMX_PNL_HIST_BINS];           // per-path PnL histogram (32-bit: native shared-memory atomics)
@@ -40,29 +73,22 @@ struct BlockShared {
     alignas(16) uint8_t cell[16];
 };
 
-struct EngineGlobals {            // read-only, global memory
-    const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit tc (dir up) / bit 16+tc (dir down) = ML gate FAILS; null = no model
-    const double* mlprob;         // [n_days][kMaxLevels][2][16] P(win) for blend mode; null when unused
-    int32_t n_days;
-    const double* pol;            // [n_pol][3][7]
-    int32_t n_pol;
-    double z_go, z_skip;          // sigmoid(z) >= 0.60 <=> z >= z_go ; sigmoid(z) < 0.55 <=> z < z_skip
-    double hist_lo, hist_inv_w;
-    int32_t steps;
-    // parity-mode outputs (may be null)
-    qmmx_trade* trades; int32_t* tcounts; int32_t max_trades; uint8_t* codes;
-    int64_t paths;                // row stride of codes
-};
+__device__ __forceinline__ BlockShared& smem() {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    return *reinterpret_cast<BlockShared*>(smem_raw);
+}
 
 __device__ __forceinline__ void smem_inc(unsigned long long* p, unsigned long long v = 1ull) { atomicAdd(p, v); }
 
 // OnlinePolicy._dot under CPython >= 3.12 (Neumaier-compensated builtin sum), M:334-335
-__device__ __noinline__ double dot_py312(const double* __restrict__ w, const double* x) {
-    double f = 0.0 + w[0] * x[0];
+__device__ __noinline__ double dot_py312(const double* __restrict__ w, double x1, double x3, double x4, double x5, double x6) {
+    // x = [1, x1, 0, x3, x4, x5, x6]
+    double f = 0.0 + w[0] * 1.0;
     double c = 0.0;
-#pragma unroll 1
+#pragma unroll
     for (int i = 1; i < QMMX_POLICY_DIM; ++i) {
-        const double v = w[i] * x[i];
+        const double xi = i == 1 ? x1 : i == 2 ? 0.0 : i == 3 ? x3 : i == 4 ? x4 : i == 5 ? x5 : x6;
+        const double v = w[i] * xi;
         const double t = f + v;
         if (fabs(f) >= fabs(v)) c += (f - t) + v; else c += (v - t) + f;
         f = t;
@@ -83,22 +109,90 @@ __device__ __forceinline__ double compute_confidence(double dist, bool solid, in
     return m > 0.0 ? m : 0.0;
 }
 
+// rare: neighbouring levels are latched while level k is touched -> each stays latched only while p is still
+// inside its own contact window (M:1572-1576).  Returns the latch bits to keep.
+__device__ __noinline__ unsigned long long keep_neighbours(float pf, uint32_t klo, uint32_t khi) {
+    const BlockShared& S = smem();
+    uint32_t llo = 0u, lhi = 0u;
+    while (klo) {
+        const int j = __ffs((int)klo) - 1; klo &= klo - 1;
+        if (pf >= S.cold[j].wlo && pf <= S.cold[j].whi) llo |= 1u << j;
+    }
+    while (khi) {
+        const int j = __ffs((int)khi) - 1; khi &= khi - 1;
+        if (pf >= S.cold[32 + j].wlo && pf <= S.cold[32 + j].whi) lhi |= 1u << j;
+    }
+    return ((unsigned long long)lhi << 32) | llo;
+}
+
+// rare: blend gate (M:1711-1742) in float64; true when the blended score is below Q_MIN_PROB
+__device__ __noinline__ bool blend_fails(int k, float pf, int tc, int side, int day_off) {
+    const BlockShared& S = smem();
+    const DevCombo& C = S.combo;
+    const double lp = S.cold[k].price;
+    const double conf = compute_confidence(fabs(lp - (double)pf), (S.cold[k].flags & kLvSolid) != 0, tc, C.pmax);
+    double mlp = conf;
+    if (S.G.mlprob) mlp = S.G.mlprob[(((size_t)day_off + k) * 2 + side) * 16 + tc];
+    const double blended = C.wr * conf + C.wm * mlp;
+    return blended < C.qmin;
+}
+
+// rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
+__device__ __noinline__ bool policy_passes(int k, float pf, int side, int i) {
+    const BlockShared& S = smem();
+    const DevCombo& C = S.combo;
+    if (S.G.n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
+    const double lp = S.cold[k].price;
+    const double pa = fabs((double)pf - lp);
+    const double tod = (double)(i % C.spd) / 390.0;
+    const double x1 = pa < 1.0 ? pa : 1.0;
+    const double x3 = side == 1 ? 1.0 : 0.0, x4 = side == 0 ? 1.0 : 0.0;
+    const double x5 = (S.cold[k].flags & kLvConfl06) ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
+    const int day = i / C.spd;
+    const double* w = S.G.pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < S.G.n_pol ? day : S.G.n_pol - 1);
+    const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
+    const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x1, x3, x4, x5, x6);
+    return (z_side >= S.G.z_go) && (z_sk < S.G.z_skip);
+}
+
+// rare: the grid cell straddles a zone boundary -> exact binary search over the zone table
+__device__ __noinline__ uint32_t classify_zones(float pf) {
+    const BlockShared& S = smem();
+    int a = 0, b = S.Z - 1;
+    while (a < b) {
+        const int m = (a + b) >> 1;
+        if (pf <= S.zhi[m]) b = m; else a = m + 1;
+    }
+    return S.zlev[a];
+}
+
+// parity mode: one trade record
+__device__ __noinline__ void record_trade(int64_t path, int ntr, int entry_bar, int exit_bar, int side, int reason, int k,
+                                          float entry, float exit, float pnl) {
+    BlockShared& S = smem();
+    if (!S.G.trades) return;
+    if (ntr < S.G.max_trades) {
+        qmmx_trade t;
+        t.entry_bar = entry_bar; t.exit_bar = exit_bar; t.side = (uint8_t)side; t.reason = (uint8_t)reason;
+        t.level_id = (uint16_t)k; t.entry = entry; t.exit = exit; t.pnl = pnl;
+        S.G.trades[path * S.G.max_trades + ntr] = t;
+    } else smem_inc(&S.u[U_NOVERFLOW]);
+}
+
 // ---- per-path state machine ---------------------------------------------------------------------------
-template <bool HL, bool PARITY, bool TINY>
+// WIDE = more than 32 levels (64-bit contact latch).  PARITY adds per-step codes and trade records.
+template <bool HL, bool PARITY, bool TINY, bool WIDE>
 struct PathEngine {
-    BlockShared& S;
-    const EngineGlobals& G;
-    const int tid;
-    int64_t path;          // global index into the resident bars (parity outputs)
+    typedef typename LatchType<WIDE>::T latch_t;
+    int tid;
     // EngineState (M:259-270) + contact latch (M:1376)
     float prev;            // NaN until the first tick
-    int last_dir;          // 0 unknown, 1 up, 2 down
+    int d;                 // last_direction: 0 unknown, 1 up, 2 down
     int cool_until;        // first step index at which the cooldown is over
     int pos;               // -1 flat, else level | side << 8
     float lo_thr, hi_thr;  // exit when low <= lo_thr or high >= hi_thr (directed-rounded stop/target)
     float entry;
-    int entry_bar;
-    uint32_t latch_lo, latch_hi;
+    latch_t latch;
     // per-path tallies, two 16-bit counters per register (steps per path <= 65535); reduced per warp at path end
     uint32_t c_gate;       // LEVEL_OVERTOUCHED | CONF_LOW << 16
     uint32_t c_ml;         // ML_CONF_LOW | winning trades << 16
@@ -107,209 +201,160 @@ struct PathEngine {
     uint32_t c_dir;        // DIR_UNKNOWN
     // per-path accumulators
     double pnl, pnl2, mtm;
-    int ntr;
+    // parity mode only
+    int64_t path; int entry_bar; int ntr;
 
-    __device__ PathEngine(BlockShared& s, const EngineGlobals& g, int t) : S(s), G(g), tid(t) {}
-
-    __device__ __forceinline__ void reset(int64_t path_) {
-        path = path_;
+    __device__ __forceinline__ void reset(int tid_, int64_t path_) {
+        tid = tid_; path = path_;
         prev = __int_as_float(0x7fc00000);
-        last_dir = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
-        latch_lo = 0u; latch_hi = 0u; c_gate = 0u; c_ml = 0u; c_exit = 0u; c_span = 0u; c_dir = 0u;
+        d = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
+        latch = 0; c_gate = 0u; c_ml = 0u; c_exit = 0u; c_span = 0u; c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
+        BlockShared& S = smem();
 #pragma unroll
         for (int w = 0; w < 8; ++w) S.touch[w * kThreads + tid] = 0u;
     }
 
-    __device__ __forceinline__ void record(int entry_bar_, int exit_bar, int side, int reason, int k,
-                                           float entry_, float exit_, float pnl_) {
-        if (PARITY && G.trades) {
-            if (ntr < G.max_trades) {
-                qmmx_trade t;
-                t.entry_bar = entry_bar_; t.exit_bar = exit_bar; t.side = (uint8_t)side; t.reason = (uint8_t)reason;
-                t.level_id = (uint16_t)k; t.entry = entry_; t.exit = exit_; t.pnl = pnl_;
-                G.trades[path * G.max_trades + ntr] = t;
-            } else smem_inc(&S.u[U_NOVERFLOW]);
-        }
-        ++ntr;
-    }
-
-    // rare: a neighbouring level is latched while this one is touched -> keep it only while p is still inside
-    // that level's own contact window (M:1572-1576)
-    __device__ __noinline__ static void keep_neighbours(const BlockShared& S, float pf, uint32_t klo, uint32_t khi,
-                                                        uint32_t& llo, uint32_t& lhi) {
-        while (klo) {
-            const int j = __ffs((int)klo) - 1; klo &= klo - 1;
-            if (pf >= S.lev[j].wlo && pf <= S.lev[j].whi) llo |= 1u << j;
-        }
-        while (khi) {
-            const int j = __ffs((int)khi) - 1; khi &= khi - 1;
-            if (pf >= S.lev[32 + j].wlo && pf <= S.lev[32 + j].whi) lhi |= 1u << j;
-        }
-    }
-
-    // rare: blend gate (M:1711-1742) in float64; returns true when the blended score is below Q_MIN_PROB
-    __device__ __noinline__ static bool blend_fails(const BlockShared& S, const EngineGlobals& G, int k, float pf,
-                                                    int tc, int d, int day) {
-        const DevCombo& C = S.combo;
-        const double lp = S.lev[k].price;
-        const double conf = compute_confidence(fabs(lp - (double)pf), (S.lev[k].flags & kLvSolid) != 0, tc, C.pmax);
-        double mlp = conf;
-        if (G.mlprob) {
-            const int dd = day < G.n_days ? day : G.n_days - 1;
-            mlp = G.mlprob[(((size_t)dd * kMaxLevels + k) * 2 + (d - 1)) * 16 + tc];
-        }
-        const double blended = C.wr * conf + C.wm * mlp;
-        return blended < C.qmin;
-    }
-
-    // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
-    __device__ __noinline__ static bool policy_passes(const BlockShared& S, const EngineGlobals& G, int k, float pf,
-                                                      int side, int i) {
-        const DevCombo& C = S.combo;
-        if (G.n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
-        const double lp = S.lev[k].price;
-        double x[QMMX_POLICY_DIM];
-        const double pa = fabs((double)pf - lp);
-        const double tod = (double)(i % C.spd) / 390.0;
-        x[0] = 1.0; x[1] = pa < 1.0 ? pa : 1.0; x[2] = 0.0;
-        x[3] = side == 1 ? 1.0 : 0.0; x[4] = side == 0 ? 1.0 : 0.0;
-        x[5] = (S.lev[k].flags & kLvConfl06) ? 1.0 : 0.0; x[6] = tod < 1.0 ? tod : 1.0;
-        const int day = i / C.spd;
-        const double* w = G.pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < G.n_pol ? day : G.n_pol - 1);
-        const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x);
-        const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x);
-        return (z_side >= G.z_go) && (z_sk < G.z_skip);
-    }
-
     // contact path: price is nearest to, and within CONTACT_PROX of, level k
-    __device__ __forceinline__ int contact(int k, float pf, int d, int i) {
-        const DevCombo& C = S.combo;
-        const DevLevel& Lk = S.lev[k];
+    __device__ __forceinline__ int contact(int k, float pf, int dir, int i, int day_off) {
+        BlockShared& S = smem();
+        const HotLevel& Hk = S.hot[k];
         // latch + touch count (M:1562-1576)
-        const uint32_t blo = (k < 32) ? (1u << k) : 0u, bhi = (k < 32) ? 0u : (1u << (k - 32));
-        const bool isnew = ((latch_lo & blo) | (latch_hi & bhi)) == 0u;
-        const uint32_t klo = latch_lo & Lk.cand_lo, khi = latch_hi & Lk.cand_hi;
-        latch_lo = blo; latch_hi = bhi;
-        if (klo | khi) keep_neighbours(S, pf, klo, khi, latch_lo, latch_hi);
-        uint32_t& tw = S.touch[(k >> 3) * kThreads + tid];
-        const int sh = (k & 7) * 4;
-        const uint32_t word = tw;
-        int tc = (word >> sh) & 15;
-        if (isnew && tc < 15) { ++tc; tw = word + (1u << sh); }
-        if (tc >= C.overtouch) { c_gate += 1u; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
-        const int b = (tc < 3 ? tc : 3) - 1;
-        if (!(pf >= Lk.cpass[b][0] && pf <= Lk.cpass[b][1])) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
-        const int side = d - 1;                                              // M:1645: up -> long(0), down -> short(1)
-        if (C.flags & QMMX_F_USE_BLEND) {                                    // M:1730-1742
-            if (blend_fails(S, G, k, pf, tc, d, i / C.spd)) { smem_inc(&S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
-        } else if (G.mlmask) {                                               // M:1454-1466, M:1745-1755
-            int day = i / C.spd; day = day < G.n_days ? day : G.n_days - 1;
-            const uint32_t m = __ldg(&G.mlmask[day * kMaxLevels + k]);
+        latch_t bit, cand;
+        if (WIDE) {
+            const uint4 m = *reinterpret_cast<const uint4*>(&Hk.bit_lo);
+            bit = (latch_t)(((unsigned long long)m.y << 32) | m.x); cand = (latch_t)(((unsigned long long)m.w << 32) | m.z);
+        } else {
+            const uint2 m = *reinterpret_cast<const uint2*>(&Hk.bit_lo);   // levels < 32: low words only
+            bit = (latch_t)m.x; cand = (latch_t)Hk.cand_lo;
+        }
+        const bool isnew = (latch & bit) == 0;
+        const latch_t keep = latch & cand;
+        latch = bit;
+        if (keep) latch |= (latch_t)keep_neighbours(pf, (uint32_t)keep, WIDE ? (uint32_t)((unsigned long long)keep >> 32) : 0u);
+        const uint2 ts = *reinterpret_cast<const uint2*>(&Hk.toff);
+        uint32_t* tw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(S.touch) + ts.x) + tid;
+        const uint32_t word = *tw;
+        int tc = (word >> ts.y) & 15;
+        if (isnew && tc < 15) { ++tc; *tw = word + (1u << ts.y); }
+        if (tc >= S.combo.overtouch) { c_gate += 1u; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
+        const int b = min(tc, 3) - 1;
+        const float2 cp = Hk.cpass[b];
+        if (!(pf >= cp.x && pf <= cp.y)) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
+        const int side = dir - 1;                                            // M:1645: up -> long(0), down -> short(1)
+        const uint32_t cflags = S.combo.flags;
+        if (cflags & QMMX_F_USE_BLEND) {                                     // M:1730-1742
+            if (blend_fails(k, pf, tc, side, day_off)) { smem_inc(&S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
+        } else if (cflags & kCbHasMl) {                                      // M:1454-1466, M:1745-1755
+            const uint32_t m = __ldg(&S.G.mlmask[day_off + k]);
             if ((m >> (side * 16 + tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
-        if (!(C.flags & QMMX_F_DISABLE_POLICY_GATE)) {
-            if (!policy_passes(S, G, k, pf, side, i)) { smem_inc(&S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
+        if (!(cflags & QMMX_F_DISABLE_POLICY_GATE)) {
+            if (!policy_passes(k, pf, side, i)) { smem_inc(&S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
         }
         // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
+        // thresholds (M:1669-1674) were rounded per level at CTA setup:
         // p <= stop (float64, p fp32)  <=>  p <= round_down_fp32(stop);  p >= target  <=>  p >= round_up_fp32(target)
+        const float2 th = Hk.thr[side];
+        lo_thr = th.x; hi_thr = th.y;
         pos = k | (side << 8);
-        entry = pf; entry_bar = i;
-        const double lp = Lk.price;
-        if (side == 0) { lo_thr = __double2float_rd(lp - C.sp); hi_thr = __double2float_ru(lp + C.tp); }   // M:1669-1674
-        else { hi_thr = __double2float_ru(lp + C.sp); lo_thr = __double2float_rd(lp - C.tp); }
+        entry = pf;
+        if (PARITY) entry_bar = i;
         return QMMX_OK_ENTRY;
     }
 
     __device__ __forceinline__ void do_exit(float pf, bool hit_lo, bool hit_hi, int i) {
-        const DevCombo& C = S.combo;
-        const int k = pos & 0xff, side = pos >> 8;
+        BlockShared& S = smem();
+        const int side = pos >> 8;
         // long: stop below (tested first), target above; short: stop above (tested first), target below
-        const int reason = (side == 0) ? (hit_lo ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET)
-                                       : (hit_hi ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET);
-        double exit_px = (double)pf;
-        if (HL) {   // exit at the stop/target level itself (M:3636)
-            const double lp = S.lev[k].price;
-            if (side == 0) exit_px = (reason == QMMX_EXIT_STOP) ? lp - C.sp : lp + C.tp;
-            else exit_px = (reason == QMMX_EXIT_STOP) ? lp + C.sp : lp - C.tp;
+        const bool is_stop = (side == 0) ? hit_lo : hit_hi;
+        double tp;
+        float exit_f = pf;
+        if (!HL) {
+            // close exit (M:2979-3012): exit at the tick price; fp32 values, float64 difference (M:1926)
+            const double a = (double)pf, e = (double)entry;
+            tp = side == 0 ? a - e : e - a;
+        } else {    // exit at the stop/target level itself (M:3636)
+            const double lp = S.cold[pos & 0xff].price;
+            double exit_px;
+            if (side == 0) exit_px = is_stop ? lp - S.combo.sp : lp + S.combo.tp;
+            else exit_px = is_stop ? lp + S.combo.sp : lp - S.combo.tp;
+            const double e = (double)entry;
+            tp = (side == 0) ? (exit_px - e) : (e - exit_px);
+            exit_f = (float)exit_px;
         }
-        const double e = (double)entry;
-        const double tp = (side == 0) ? (exit_px - e) : (e - exit_px);       // M:1926
         pnl += tp; pnl2 += tp * tp;
-        cool_until = i + C.cool_steps;                                       // M:2982, M:269-270
+        cool_until = i + S.combo.cool_steps;                                 // M:2982, M:269-270
         if (tp > 0) c_ml += 1u << 16;                                        // label, M:1936
-        c_exit += (reason == QMMX_EXIT_STOP) ? 1u : (1u << 16);
-        int cd = C.cool_steps < G.steps - i ? C.cool_steps : G.steps - i;
-        cd -= 1;
-        c_span += (uint32_t)(i - entry_bar) + ((uint32_t)(cd > 0 ? cd : 0) << 16);
-        record(entry_bar, i, side, reason, k, entry, (float)exit_px, (float)tp);
+        c_exit += is_stop ? 1u : (1u << 16);
+        if (PARITY) record_trade(path, ntr, entry_bar, i, side, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET, pos & 0xff, entry, exit_f, (float)tp);
+        ++ntr;
         pos = -1;
     }
 
     // price -> level index touched, or kFar (exact: see tables.h)
     __device__ __forceinline__ uint32_t classify(float pf) const {
+        const BlockShared& S = smem();
         uint32_t v = S.cell[cell_of_bits(__float_as_int(pf), S.obase, S.shift, S.ncell)];
-        if (v == kMixed) {
-            int a = 0, b = S.Z - 1;
-            while (a < b) {
-                const int m = (a + b) >> 1;
-                if (pf <= S.zhi[m]) b = m; else a = m + 1;
-            }
-            v = S.zlev[a];
-        }
+        if (v == kMixed) v = classify_zones(pf);
         return v;
     }
 
-    // one tick: price pf = bar i's close (hh/ll = its high/low when HL)
-    __device__ __forceinline__ void step(float pf, float hh, float ll, int i) {
+    // one tick: price pf = bar i's close (hh/ll = its high/low when HL); day_off = min(day, n_days-1) * kMaxLevels
+    __device__ __forceinline__ void step(float pf, float hh, float ll, int i, int day_off) {
+        BlockShared& S = smem();
         int code = QMMX_TOO_FAR;
         // direction (M:1529-1537) and last_direction update (M:2954-2955)
-        int d;
+        int dir;
         if (!TINY) {
             // |p|,|prev| >= 2^-5 (QMMX_F_TINY_PRICES unset): fp32 spacing > 1.8e-9, so the +-1e-9 guard band of
-            // the reference cannot change any comparison and d doubles as the updated last_direction
-            d = (pf > prev) ? 1 : ((pf < prev) ? 2 : last_dir);
+            // the reference cannot change any comparison and dir doubles as the updated last_direction
+            dir = (pf > prev) ? 1 : ((pf < prev) ? 2 : d);
         } else {
-            d = 0;
+            dir = 0;
             if (prev == prev) {
                 const double p = (double)pf, q = (double)prev;
-                if (p > q + 1e-9) d = 1; else if (p < q - 1e-9) d = 2; else d = last_dir;
+                if (p > q + 1e-9) dir = 1; else if (p < q - 1e-9) dir = 2; else dir = d;
             }
         }
         if (pos >= 0) {
             code = QMMX_IN_POSITION;                                         // M:1508
+            c_span += 1u;
             const bool hit_lo = (HL ? ll : pf) <= lo_thr;
             const bool hit_hi = (HL ? hh : pf) >= hi_thr;
             if (hit_lo | hit_hi) do_exit(pf, hit_lo, hit_hi, i);
         } else if (i < cool_until) {
             code = QMMX_COOLDOWN;                                            // M:1516
-        } else if (S.L == 0) {
-            code = QMMX_NOLEVELS;                                            // M:1524 (tallied as remainder)
-        } else if (d == 0) {
-            code = QMMX_DIR_UNKNOWN;                                         // M:1538
+            c_span += 1u << 16;
+        } else if (dir == 0) {
+            code = QMMX_DIR_UNKNOWN;                                         // M:1538 (NOLEVELS when L == 0, fixed at flush)
             ++c_dir;
         } else {
             const uint32_t v = classify(pf);
-            if (v != kFar) code = contact((int)v, pf, d, i);                 // else TOO_FAR, M:1545
+            if (v != kFar) code = contact((int)v, pf, dir, i, day_off);      // else TOO_FAR (M:1545), or NOLEVELS (M:1524)
         }
-        if (!TINY) last_dir = d;
-        else if (prev == prev && pf != prev) last_dir = (pf > prev) ? 1 : 2;
+        if (!TINY) d = dir;
+        else if (prev == prev && pf != prev) d = (pf > prev) ? 1 : 2;
         prev = pf;
-        if (PARITY && G.codes) G.codes[(int64_t)i * G.paths + path] = (uint8_t)code;
+        if (PARITY && S.G.codes) {
+            if (S.L == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
+            S.G.codes[(int64_t)i * S.G.paths + path] = (uint8_t)code;
+        }
     }
 
     // end of path: open position => OPEN, realised 0, mark-to-market reported separately
     __device__ __forceinline__ void finish() {
+        BlockShared& S = smem();
         if (pos >= 0) {
-            const int k = pos & 0xff, side = pos >> 8;
+            const int side = pos >> 8;
             const double e = (double)entry, last = (double)prev;
             mtm = (side == 0) ? (last - e) : (e - last);
-            c_span += (uint32_t)(G.steps - 1 - entry_bar);
-            record(entry_bar, -1, side, QMMX_EXIT_OPEN, k, entry, prev, 0.0f);
+            if (PARITY) record_trade(path, ntr, entry_bar, -1, side, QMMX_EXIT_OPEN, pos & 0xff, entry, prev, 0.0f);
+            ++ntr;
         }
-        if (PARITY && G.tcounts) G.tcounts[path] = ntr;
-        double fb = floor((pnl - G.hist_lo) * G.hist_inv_w);
+        if (PARITY && S.G.tcounts) S.G.tcounts[path] = ntr;
+        double fb = floor((pnl - S.G.hist_lo) * S.G.hist_inv_w);
         const int bin = fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
         atomicAdd(&S.hist[bin], 1u);
     }
@@ -339,7 +384,8 @@ __device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
 
 // add one finished path per lane (inactive lanes contribute neutral values) to the block aggregate
 template <class Engine>
-__device__ __forceinline__ void warp_accumulate(BlockShared& S, bool active, const Engine& E) {
+__device__ __forceinline__ void warp_accumulate(bool active, const Engine& E) {
+    BlockShared& S = smem();
     const int lane = threadIdx.x & 31;
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
     const double s1 = warp_sum(active ? E.pnl : 0.0);
@@ -376,7 +422,8 @@ __device__ __forceinline__ void warp_accumulate(BlockShared& S, bool active, con
     }
 }
 
-__device__ inline void block_zero_agg(BlockShared& S) {
+__device__ inline void block_zero_agg() {
+    BlockShared& S = smem();
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
     for (int t = threadIdx.x; t < U_HIST; t += blockDim.x) S.u[t] = 0ull;
     for (int t = threadIdx.x; t < QMMX_PNL_HIST_BINS; t += blockDim.x) S.hist[t] = 0u;
@@ -385,7 +432,8 @@ __device__ inline void block_zero_agg(BlockShared& S) {
 }
 
 // flush the block aggregate into the flat global buffer of `combo`; caller syncs before
-__device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat, int combo, int steps) {
+__device__ inline void block_flush_agg(unsigned long long* flat, int combo, int steps) {
+    BlockShared& S = smem();
     unsigned long long* gu = flat + (size_t)combo * QMMX_AGG_SLOTS;
     double* gd = reinterpret_cast<double*>(gu + QMMX_AGG_NU);
     if (threadIdx.x == 0) {
@@ -396,6 +444,7 @@ __device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat,
         unsigned long long others = 0;
         for (int c = 0; c < QMMX_N_ENTRY_CODES; ++c) others += S.u[U_ENTRY + c];
         S.u[U_NSTEPS] = nsteps;
+        if (S.L == 0) { others -= S.u[U_ENTRY + QMMX_DIR_UNKNOWN]; S.u[U_ENTRY + QMMX_DIR_UNKNOWN] = 0ull; }   // NOLEVELS precedes DIR_UNKNOWN (M:1524)
         S.u[U_ENTRY + (S.L == 0 ? QMMX_NOLEVELS : QMMX_TOO_FAR)] += nsteps - others;
     }
     __syncthreads();
@@ -410,14 +459,28 @@ __device__ inline void block_flush_agg(BlockShared& S, unsigned long long* flat,
     }
 }
 
-__device__ inline void block_load_tables(BlockShared& S, const DevTables* __restrict__ T, const DevCombo* __restrict__ C) {
+__device__ inline void block_load_tables(const DevTables* __restrict__ T, const DevCombo* __restrict__ C) {
+    BlockShared& S = smem();
     if (threadIdx.x == 0) {
         S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
         S.combo = *C;
     }
-    const uint32_t* ls = reinterpret_cast<const uint32_t*>(T->lev);
-    uint32_t* ld = reinterpret_cast<uint32_t*>(S.lev);
-    for (int t = threadIdx.x; t < (int)(sizeof(DevLevel) * kMaxLevels / 4); t += blockDim.x) ld[t] = ls[t];
+    for (int k = threadIdx.x; k < kMaxLevels; k += blockDim.x) {
+        const DevLevel D = T->lev[k];
+        HotLevel H;
+        // M:1669-1674: long stop = L - SP, target = L + TP; short stop = L + SP, target = L - TP  (float64, then
+        // rounded toward the inside of the no-exit band so the fp32 compare equals the float64 compare)
+        H.thr[0] = make_float2(__double2float_rd(D.price - C->sp), __double2float_ru(D.price + C->tp));
+        H.thr[1] = make_float2(__double2float_rd(D.price - C->tp), __double2float_ru(D.price + C->sp));
+#pragma unroll
+        for (int b = 0; b < 3; ++b) H.cpass[b] = make_float2(D.cpass[b][0], D.cpass[b][1]);
+        H.bit_lo = k < 32 ? 1u << k : 0u; H.bit_hi = k < 32 ? 0u : 1u << (k - 32);
+        H.cand_lo = D.cand_lo; H.cand_hi = D.cand_hi;
+        H.toff = (uint32_t)((k >> 3) * kThreads * 4); H.tsh = (uint32_t)((k & 7) * 4);
+        S.hot[k] = H;
+        ColdLevel Cl; Cl.price = D.price; Cl.wlo = D.wlo; Cl.whi = D.whi; Cl.flags = D.flags; Cl.pad = 0u;
+        S.cold[k] = Cl;
+    }
     for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) { S.zhi[t] = T->zhi[t]; S.zlev[t] = T->zlev[t]; }
     const int n16 = (T->ncell + 15) / 16;
     const uint4* src = reinterpret_cast<const uint4*>(T->cell);

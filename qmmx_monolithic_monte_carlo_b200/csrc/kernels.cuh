@@ -7,7 +7,10 @@
 
 namespace qmmx {
 
-constexpr int kBlocksPerSM = 4;
+#ifndef QMMX_BLOCKS_PER_SM
+#define QMMX_BLOCKS_PER_SM 4
+#endif
+constexpr int kBlocksPerSM = QMMX_BLOCKS_PER_SM;
 constexpr int kWarps = kThreads / 32;
 
 struct ScanArgs {
@@ -61,9 +64,36 @@ __device__ __forceinline__ float gbm_advance(const GbmDev& g, float S, float z) 
     return __fmul_rn(S, __expf(__fadd_rn(g.drift, __fmul_rn(g.vol, z))));
 }
 
+// per-CTA setup: tables, combo and run description into shared memory
+__device__ __forceinline__ void block_setup(const ScanArgs& A, int combo, bool parity) {
+    const DevCombo* C = A.combos + combo;
+    block_load_tables(A.tables + C->table, C);
+    block_zero_agg();
+    if (threadIdx.x == 0) {
+        BlockShared& S = smem();
+        EngineGlobals G = A.G;
+        const uint32_t f = C->flags;
+        G.mlmask = (A.mlmask && (f & kCbHasMl)) ? A.mlmask + (size_t)combo * G.n_days * kMaxLevels : nullptr;
+        G.mlprob = (A.mlprob && (f & kCbHasProb)) ? A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32 : nullptr;
+        if (!parity || combo != A.parity_combo) { G.trades = nullptr; G.tcounts = nullptr; G.codes = nullptr; }
+        S.G = G;
+    }
+    __syncthreads();
+}
+
+// warp-uniform day counter: day_off = min(step / steps_per_day, n_days - 1) * kMaxLevels without a division per step
+struct DayTracker {
+    int next, off, spd, max_off;
+    __device__ __forceinline__ void init(int spd_, int n_days) { spd = spd_; next = spd_; off = 0; max_off = (n_days > 1 ? n_days - 1 : 0) * kMaxLevels; }
+    __device__ __forceinline__ int at(int i) {
+        if (i >= next) { next += spd; off = min(off + kMaxLevels, max_off); }
+        return off;
+    }
+};
+
 // ---- engine scan over resident bars -------------------------------------------------------------------------
-template <bool HL, bool PARITY, bool TINY>
-__device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY>& E, const ScanArgs& A, int64_t path) {
+template <bool HL, bool PARITY, bool TINY, bool WIDE>
+__device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY, WIDE>& E, const ScanArgs& A, int64_t path) {
     constexpr int U = HL ? 2 : 4;
     const size_t pitch = (size_t)A.pitch;
     const float* pc = A.close + path;
@@ -72,6 +102,8 @@ __device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY>& E, const
     const int steps = A.steps;
     float c0[U], c1[U], h0[U], h1[U], l0[U], l1[U];
     const int nfull = steps / (2 * U);
+    DayTracker day;
+    day.init(smem().combo.spd, A.G.n_days);
     int i = 0;
     if (nfull > 0) {
 #pragma unroll
@@ -87,7 +119,7 @@ __device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY>& E, const
                 if (HL) { h1[u] = __ldg(ph + o); l1[u] = __ldg(pl + o); }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u);
+            for (int u = 0; u < U; ++u) E.step(c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u, day.at(i + u));
             if (n + 1 < nfull) {
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
@@ -97,45 +129,34 @@ __device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY>& E, const
                 }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u);
+            for (int u = 0; u < U; ++u) E.step(c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u, day.at(i + U + u));
         }
     }
 #pragma unroll 1
     for (; i < steps; ++i) {
         const size_t o = (size_t)i * pitch;
         const float c = __ldg(pc + o);
-        E.step(c, HL ? __ldg(ph + o) : 0.f, HL ? __ldg(pl + o) : 0.f, i);
+        E.step(c, HL ? __ldg(ph + o) : 0.f, HL ? __ldg(pl + o) : 0.f, i, day.at(i));
     }
 }
 
-template <bool HL, bool PARITY, bool TINY>
+template <bool HL, bool PARITY, bool TINY, bool WIDE>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM) scan_kernel(const ScanArgs A) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    BlockShared& S = *reinterpret_cast<BlockShared*>(smem_raw);
     const int combo = A.combo0 + blockIdx.y;
-    const DevCombo* C = A.combos + combo;
-    block_load_tables(S, A.tables + C->table, C);
-    block_zero_agg(S);
-    __syncthreads();
-    EngineGlobals G = A.G;
-    if (A.mlmask) G.mlmask = A.mlmask + (size_t)combo * G.n_days * kMaxLevels;
-    if (A.mlprob) G.mlprob = A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32;
-    if (!(S.combo.flags & (1u << 16))) G.mlmask = nullptr;
-    if (!(S.combo.flags & (1u << 17))) G.mlprob = nullptr;
-    if (PARITY && combo != A.parity_combo) { G.trades = nullptr; G.tcounts = nullptr; G.codes = nullptr; }
-    PathEngine<HL, PARITY, TINY> E(S, G, threadIdx.x);
+    block_setup(A, combo, PARITY);
+    PathEngine<HL, PARITY, TINY, WIDE> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t ntiles = (A.paths + 31) / 32;
     for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kWarps) {
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
-        E.reset(path);
+        E.reset(threadIdx.x, path);
         if (active) { scan_path(E, A, path); E.finish(); }
         __syncwarp();
-        warp_accumulate(S, active, E);
+        warp_accumulate(active, E);
     }
     __syncthreads();
-    block_flush_agg(S, A.flat, combo, A.steps);
+    block_flush_agg(A.flat, combo, A.steps);
 }
 
 // ---- GBM generator (materialised bars) -------------------------------------------------------------------------
@@ -174,32 +195,24 @@ __global__ void __launch_bounds__(kThreads) gen_gbm_kernel(float* __restrict__ c
 }
 
 // ---- fused GBM generate + scan: bars live in registers only -------------------------------------------------------
-template <bool HL>
+template <bool HL, bool WIDE>
 __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const ScanArgs A, const GbmDev g) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    BlockShared& S = *reinterpret_cast<BlockShared*>(smem_raw);
     const int combo = A.combo0 + blockIdx.y;
-    const DevCombo* C = A.combos + combo;
-    block_load_tables(S, A.tables + C->table, C);
-    block_zero_agg(S);
-    __syncthreads();
-    EngineGlobals G = A.G;
-    if (A.mlmask) G.mlmask = A.mlmask + (size_t)combo * G.n_days * kMaxLevels;
-    if (A.mlprob) G.mlprob = A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32;
-    if (!(S.combo.flags & (1u << 16))) G.mlmask = nullptr;
-    if (!(S.combo.flags & (1u << 17))) G.mlprob = nullptr;
-    PathEngine<HL, false, false> E(S, G, threadIdx.x);
+    block_setup(A, combo, false);
+    PathEngine<HL, false, false, WIDE> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps;
     for (int64_t tile = (int64_t)blockIdx.x * kWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kWarps) {
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
-        E.reset(path);
+        E.reset(threadIdx.x, path);
         if (active) {
             const uint64_t gid = g.path_offset + (uint64_t)path;
             float P = g.s0;
             float z[4];
+            DayTracker day;
+            day.init(smem().combo.spd, A.G.n_days);
             if (!HL) {
                 for (int i = 0; i < steps; i += 4) {
                     gbm_normals(g, gid, (uint32_t)(i >> 2), z);
@@ -207,7 +220,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
                     for (int u = 0; u < 4; ++u) {
                         if (i + u < steps) {
                             P = gbm_advance(g, P, z[u]);
-                            E.step(g.cents ? round_cents(P) : P, 0.f, 0.f, i + u);
+                            E.step(g.cents ? round_cents(P) : P, 0.f, 0.f, i + u, day.at(i + u));
                         }
                     }
                 }
@@ -218,16 +231,16 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
                     float hi = P, lo = P;
 #pragma unroll
                     for (int u = 0; u < 4; ++u) { P = gbm_advance(g, P, z[u]); hi = fmaxf(hi, P); lo = fminf(lo, P); }
-                    E.step(g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i);
+                    E.step(g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i, day.at(i));
                 }
             }
             E.finish();
         }
         __syncwarp();
-        warp_accumulate(S, active, E);
+        warp_accumulate(active, E);
     }
     __syncthreads();
-    block_flush_agg(S, A.flat, combo, A.steps);
+    block_flush_agg(A.flat, combo, A.steps);
 }
 
 // ---- circular block bootstrap of a candle window ---------------------------------------------------------------

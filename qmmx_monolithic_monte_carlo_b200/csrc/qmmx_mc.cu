@@ -131,8 +131,8 @@ int prepare(qmmx_ctx* ctx) {
         D.overtouch = P.overtouch_limit; D.spd = P.steps_per_day; D.table = t;
         D.flags = P.flags & 0xffffu;
         const bool ml_on = !(P.flags & QMMX_F_DISABLE_ML_GATE) && ctx->n_lr > 0;
-        if (ml_on) D.flags |= 1u << 16;
-        if (ml_on && (P.flags & QMMX_F_USE_BLEND)) { D.flags |= 1u << 17; any_prob = true; }
+        if (ml_on) D.flags |= kCbHasMl;
+        if (ml_on && (P.flags & QMMX_F_USE_BLEND)) { D.flags |= kCbHasProb; any_prob = true; }
         if (P.flags & QMMX_F_EXIT_ON_HL) ctx->any_hl = true;
         if (P.flags & QMMX_F_TINY_PRICES) ctx->any_tiny = true;
     }
@@ -155,7 +155,7 @@ int prepare(qmmx_ctx* ctx) {
         std::vector<uint32_t> mask(per_mask * nc, 0u);
         std::vector<double> prob(any_prob ? per_prob * nc : 0);
         for (int c = 0; c < nc; ++c) {
-            if (!(combos[c].flags & (1u << 16))) continue;
+            if (!(combos[c].flags & kCbHasMl)) continue;
             build_ml_tables(ctx->L, ctx->price, ctx->params[c].stop_padding, ctx->params[c].q_min_prob, ctx->lr.data(),
                             ctx->n_lr, mask.data() + per_mask * c, any_prob ? prob.data() + per_prob * c : nullptr);
         }
@@ -220,10 +220,17 @@ int launch_scan(qmmx_ctx* ctx, const ScanArgs& A, bool parity) {
     int rc = QMMX_OK;
 #define LAUNCH(HLv, PARv, TINYv)                                                              \
     do {                                                                                      \
-        auto k = scan_kernel<HLv, PARv, TINYv>;                                               \
-        if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                               \
-        k<<<grid, kThreads, smem, ctx->stream>>>(A);                                          \
+        if (wide) {                                                                           \
+            auto k = scan_kernel<HLv, PARv, TINYv, true>;                                     \
+            if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                           \
+            k<<<grid, kThreads, smem, ctx->stream>>>(A);                                      \
+        } else {                                                                              \
+            auto k = scan_kernel<HLv, PARv, TINYv, false>;                                    \
+            if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                           \
+            k<<<grid, kThreads, smem, ctx->stream>>>(A);                                      \
+        }                                                                                     \
     } while (0)
+    const bool wide = ctx->L > 32;
     if (!parity) {
         if (!hl && !tiny) LAUNCH(false, false, false);
         else if (hl && !tiny) LAUNCH(true, false, false);
@@ -650,14 +657,24 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
         if (gbm->sub_steps == 4) {
             // OHLC recipe: 4 sub-steps per bar; the engine sees high/low only when EXIT_ON_HL is set
             if (ctx->any_hl) {
-                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true>, smem)) != 0) return rc;
-                fused_gbm_kernel<true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+                if (ctx->L > 32) {
+                    if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true, true>, smem)) != 0) return rc;
+                    fused_gbm_kernel<true, true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+                } else {
+                    if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true, false>, smem)) != 0) return rc;
+                    fused_gbm_kernel<true, false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+                }
             } else {
                 return fail(ctx, QMMX_E_UNSUPPORTED, "fused GBM with sub_steps = 4 requires EXIT_ON_HL (use sub_steps = 1 for close-only)");
             }
         } else {
-            if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false>, smem)) != 0) return rc;
-            fused_gbm_kernel<false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+            if (ctx->L > 32) {
+                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false, true>, smem)) != 0) return rc;
+                fused_gbm_kernel<false, true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+            } else {
+                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false, false>, smem)) != 0) return rc;
+                fused_gbm_kernel<false, false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
+            }
         }
         ctx->launches++;
         CK(cudaGetLastError());
