@@ -9,9 +9,12 @@
 // CPython) and a float64 Neumaier dot product on the device.  The file is compiled with --fmad=false so no
 // multiply-add is ever contracted.
 //
-// Register discipline: the per-path state is a bag of scalars that never has its address taken (a single
-// address-taken member sends the whole struct to local memory); block-wide read-only data lives in shared
-// memory and is reached through smem() so the compiler keeps the shared address space.
+// Performance discipline (measured with ncu, profiles/): a warp takes nearly every branch of the state
+// machine on every step (some lane enters, some lane exits, some lane touches a level), so the cost of a step
+// is the SUM of all branches.  Therefore: per-path state is a bag of scalars whose address is never taken (one
+// address-taken member sends the whole struct to local memory); run constants are kernel parameters (constant
+// bank operands, no loads); block tables are STATIC shared memory in structure-of-arrays form (absolute LDS
+// addresses, bank = level index); rare work sits in __noinline__ functions.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -28,55 +31,47 @@ constexpr int D_SUM_PNL = 0, D_SUM_PNL2 = 1, D_SUM_PATH2 = 2, D_SUM_MTM = 3;
 
 constexpr uint32_t kCbHasMl = 1u << 16, kCbHasProb = 1u << 17;   // internal DevCombo.flags bits
 
-struct EngineGlobals {            // read-only run description, copied into shared memory per CTA
-    const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit tc (dir up) / bit 16+tc (dir down) = ML gate FAILS; null = no model
+// Kernel parameters of one scan launch = one parameter combo over one set of paths (constant bank).
+struct ScanArgs {
+    const float* close; const float* high; const float* low;   // [steps][pitch] fp32
+    int64_t pitch, paths;
+    int32_t steps, combo_index;
+    const DevTables* tables;                                    // the table of this combo
+    unsigned long long* flat;                                   // reduction buffer of this combo
+    const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit side*16+tc = ML gate FAILS; null = gate off / no model
     const double* mlprob;         // [n_days][kMaxLevels][2][16] P(win) for blend mode; null when unused
     const double* pol;            // [n_pol][3][7]
     double z_go, z_skip;          // sigmoid(z) >= 0.60 <=> z >= z_go ; sigmoid(z) < 0.55 <=> z < z_skip
     double hist_lo, hist_inv_w;
-    int64_t paths;                // row stride of codes
     // parity-mode outputs (may be null)
     qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
-    int32_t max_trades, n_days, n_pol, steps;
+    int32_t max_trades, n_days, n_pol, pad;
+    DevCombo combo;
 };
 
-// ---- shared-memory block state -------------------------------------------------------------------------
-// per-level data on the contact path, 64 bytes, built per CTA from DevLevel + the CTA's combo
-struct HotLevel {
-    float2 thr[2];                      // [side] {lo_thr, hi_thr}: long {stop v, target ^}, short {target v, stop ^}
-    float2 cpass[3];                    // touch bucket: conf >= Q_MIN_PROB  <=>  x <= p <= y
-    uint32_t bit_lo, bit_hi, cand_lo, cand_hi;
-    uint32_t toff, tsh;                 // touch word byte offset (thread 0) and bit shift
-};
-static_assert(sizeof(HotLevel) == 64, "HotLevel layout");
+// ---- shared-memory block state (static; the grid-cell bytes are the only dynamic part) -------------------
 struct ColdLevel { double price; float wlo, whi; uint32_t flags, pad; };
 
-template <bool WIDE> struct LatchType { typedef uint32_t T; };
-template <> struct LatchType<true> { typedef unsigned long long T; };
-
 struct BlockShared {
-    int32_t L, Z, ncell, shift, obase, pad0, pad1, pad2;
-    alignas(16) HotLevel hot[kMaxLevels];
+    // contact path, structure of arrays indexed by level: bank = level (mod 32)
+    uint32_t cand_lo[kMaxLevels], cand_hi[kMaxLevels];   // levels whose contact window overlaps this level's
+    float2 cpass[3][kMaxLevels];        // touch bucket: conf >= Q_MIN_PROB  <=>  x <= p <= y
+    float2 thr[2][kMaxLevels];          // [side] {lo_thr, hi_thr}: long {stop v, target ^}, short {target v, stop ^}
     ColdLevel cold[kMaxLevels];
     float zhi[kMaxZones];
     uint8_t zlev[kMaxZones];
-    DevCombo combo;
-    EngineGlobals G;
+    int32_t L, Z, ncell, shift, obase, pad0;
     // block aggregate, flushed to the global reduction buffer with atomics
     unsigned long long u[U_HIST];
-    uint32_t hist[QMMX_PNL_HIST_BINS];           // per-path PnL histogram (32-bit: native shared-memory atomics)
+    uint32_t hist[QMMX_PNL_HIST_BINS];  // per-path PnL histogram (32-bit: native shared-memory atomics)
     double d[QMMX_AGG_ND];
     double xmax, xnegmin;
     // per-thread touch counters: 4-bit saturating, 64 levels -> 8 words per thread, [word][thread]
     uint32_t touch[8 * kThreads];
-    // grid cells follow (dynamic, ncell bytes rounded up to 16)
-    alignas(16) uint8_t cell[16];
 };
 
-__device__ __forceinline__ BlockShared& smem() {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    return *reinterpret_cast<BlockShared*>(smem_raw);
-}
+__shared__ BlockShared g_S;
+extern __shared__ __align__(16) uint8_t g_cell[];   // level index / kFar / kMixed per grid cell
 
 __device__ __forceinline__ void smem_inc(unsigned long long* p, unsigned long long v = 1ull) { atomicAdd(p, v); }
 
@@ -112,79 +107,76 @@ __device__ __forceinline__ double compute_confidence(double dist, bool solid, in
 // rare: neighbouring levels are latched while level k is touched -> each stays latched only while p is still
 // inside its own contact window (M:1572-1576).  Returns the latch bits to keep.
 __device__ __noinline__ unsigned long long keep_neighbours(float pf, uint32_t klo, uint32_t khi) {
-    const BlockShared& S = smem();
     uint32_t llo = 0u, lhi = 0u;
     while (klo) {
         const int j = __ffs((int)klo) - 1; klo &= klo - 1;
-        if (pf >= S.cold[j].wlo && pf <= S.cold[j].whi) llo |= 1u << j;
+        if (pf >= g_S.cold[j].wlo && pf <= g_S.cold[j].whi) llo |= 1u << j;
     }
     while (khi) {
         const int j = __ffs((int)khi) - 1; khi &= khi - 1;
-        if (pf >= S.cold[32 + j].wlo && pf <= S.cold[32 + j].whi) lhi |= 1u << j;
+        if (pf >= g_S.cold[32 + j].wlo && pf <= g_S.cold[32 + j].whi) lhi |= 1u << j;
     }
     return ((unsigned long long)lhi << 32) | llo;
 }
 
+// rare: the grid cell straddles a zone boundary -> exact binary search over the zone table
+__device__ __noinline__ uint32_t classify_zones(float pf) {
+    int a = 0, b = g_S.Z - 1;
+    while (a < b) {
+        const int m = (a + b) >> 1;
+        if (pf <= g_S.zhi[m]) b = m; else a = m + 1;
+    }
+    return g_S.zlev[a];
+}
+
 // rare: blend gate (M:1711-1742) in float64; true when the blended score is below Q_MIN_PROB
-__device__ __noinline__ bool blend_fails(int k, float pf, int tc, int side, int day_off) {
-    const BlockShared& S = smem();
-    const DevCombo& C = S.combo;
-    const double lp = S.cold[k].price;
-    const double conf = compute_confidence(fabs(lp - (double)pf), (S.cold[k].flags & kLvSolid) != 0, tc, C.pmax);
+__device__ __noinline__ bool blend_fails(const ScanArgs* A, int k, float pf, int tc, int side, int day_off) {
+    const double lp = g_S.cold[k].price;
+    const double conf = compute_confidence(fabs(lp - (double)pf), (g_S.cold[k].flags & kLvSolid) != 0, tc, A->combo.pmax);
     double mlp = conf;
-    if (S.G.mlprob) mlp = S.G.mlprob[(((size_t)day_off + k) * 2 + side) * 16 + tc];
-    const double blended = C.wr * conf + C.wm * mlp;
-    return blended < C.qmin;
+    if (A->mlprob) mlp = A->mlprob[(((size_t)day_off + k) * 2 + side) * 16 + tc];
+    const double blended = A->combo.wr * conf + A->combo.wm * mlp;
+    return blended < A->combo.qmin;
 }
 
 // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
-__device__ __noinline__ bool policy_passes(int k, float pf, int side, int i) {
-    const BlockShared& S = smem();
-    const DevCombo& C = S.combo;
-    if (S.G.n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
-    const double lp = S.cold[k].price;
+__device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i) {
+    if (A->n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
+    const int spd = A->combo.spd;
+    const double lp = g_S.cold[k].price;
     const double pa = fabs((double)pf - lp);
-    const double tod = (double)(i % C.spd) / 390.0;
+    const double tod = (double)(i % spd) / 390.0;
     const double x1 = pa < 1.0 ? pa : 1.0;
     const double x3 = side == 1 ? 1.0 : 0.0, x4 = side == 0 ? 1.0 : 0.0;
-    const double x5 = (S.cold[k].flags & kLvConfl06) ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
-    const int day = i / C.spd;
-    const double* w = S.G.pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < S.G.n_pol ? day : S.G.n_pol - 1);
+    const double x5 = (g_S.cold[k].flags & kLvConfl06) ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
+    const int day = i / spd;
+    const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < A->n_pol ? day : A->n_pol - 1);
     const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
     const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x1, x3, x4, x5, x6);
-    return (z_side >= S.G.z_go) && (z_sk < S.G.z_skip);
-}
-
-// rare: the grid cell straddles a zone boundary -> exact binary search over the zone table
-__device__ __noinline__ uint32_t classify_zones(float pf) {
-    const BlockShared& S = smem();
-    int a = 0, b = S.Z - 1;
-    while (a < b) {
-        const int m = (a + b) >> 1;
-        if (pf <= S.zhi[m]) b = m; else a = m + 1;
-    }
-    return S.zlev[a];
+    return (z_side >= A->z_go) && (z_sk < A->z_skip);
 }
 
 // parity mode: one trade record
-__device__ __noinline__ void record_trade(int64_t path, int ntr, int entry_bar, int exit_bar, int side, int reason, int k,
-                                          float entry, float exit, float pnl) {
-    BlockShared& S = smem();
-    if (!S.G.trades) return;
-    if (ntr < S.G.max_trades) {
+__device__ __noinline__ void record_trade(const ScanArgs* A, int64_t path, int ntr, int entry_bar, int exit_bar, int side,
+                                          int reason, int k, float entry, float exit, float pnl) {
+    if (!A->trades) return;
+    if (ntr < A->max_trades) {
         qmmx_trade t;
         t.entry_bar = entry_bar; t.exit_bar = exit_bar; t.side = (uint8_t)side; t.reason = (uint8_t)reason;
         t.level_id = (uint16_t)k; t.entry = entry; t.exit = exit; t.pnl = pnl;
-        S.G.trades[path * S.G.max_trades + ntr] = t;
-    } else smem_inc(&S.u[U_NOVERFLOW]);
+        A->trades[path * A->max_trades + ntr] = t;
+    } else smem_inc(&g_S.u[U_NOVERFLOW]);
 }
+
+template <bool WIDE> struct LatchType { typedef uint32_t T; };
+template <> struct LatchType<true> { typedef unsigned long long T; };
 
 // ---- per-path state machine ---------------------------------------------------------------------------
 // WIDE = more than 32 levels (64-bit contact latch).  PARITY adds per-step codes and trade records.
 template <bool HL, bool PARITY, bool TINY, bool WIDE>
 struct PathEngine {
     typedef typename LatchType<WIDE>::T latch_t;
-    int tid;
+    uint32_t* tptr;        // &g_S.touch[tid]: this thread's column of touch counters
     // EngineState (M:259-270) + contact latch (M:1376)
     float prev;            // NaN until the first tick
     int d;                 // last_direction: 0 unknown, 1 up, 2 down
@@ -204,59 +196,54 @@ struct PathEngine {
     // parity mode only
     int64_t path; int entry_bar; int ntr;
 
-    __device__ __forceinline__ void reset(int tid_, int64_t path_) {
-        tid = tid_; path = path_;
+    __device__ __forceinline__ void reset(int tid, int64_t path_) {
+        tptr = &g_S.touch[tid]; path = path_;
         prev = __int_as_float(0x7fc00000);
         d = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
         latch = 0; c_gate = 0u; c_ml = 0u; c_exit = 0u; c_span = 0u; c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
-        BlockShared& S = smem();
 #pragma unroll
-        for (int w = 0; w < 8; ++w) S.touch[w * kThreads + tid] = 0u;
+        for (int w = 0; w < 8; ++w) tptr[w * kThreads] = 0u;
     }
 
     // contact path: price is nearest to, and within CONTACT_PROX of, level k
-    __device__ __forceinline__ int contact(int k, float pf, int dir, int i, int day_off) {
-        BlockShared& S = smem();
-        const HotLevel& Hk = S.hot[k];
+    __device__ __forceinline__ int contact(const ScanArgs& A, int k, float pf, int dir, int i, int day_off) {
         // latch + touch count (M:1562-1576)
         latch_t bit, cand;
         if (WIDE) {
-            const uint4 m = *reinterpret_cast<const uint4*>(&Hk.bit_lo);
-            bit = (latch_t)(((unsigned long long)m.y << 32) | m.x); cand = (latch_t)(((unsigned long long)m.w << 32) | m.z);
+            bit = (latch_t)(1ull << k);
+            cand = (latch_t)(((unsigned long long)g_S.cand_hi[k] << 32) | g_S.cand_lo[k]);
         } else {
-            const uint2 m = *reinterpret_cast<const uint2*>(&Hk.bit_lo);   // levels < 32: low words only
-            bit = (latch_t)m.x; cand = (latch_t)Hk.cand_lo;
+            bit = (latch_t)(1u << k);
+            cand = (latch_t)g_S.cand_lo[k];
         }
         const bool isnew = (latch & bit) == 0;
         const latch_t keep = latch & cand;
         latch = bit;
         if (keep) latch |= (latch_t)keep_neighbours(pf, (uint32_t)keep, WIDE ? (uint32_t)((unsigned long long)keep >> 32) : 0u);
-        const uint2 ts = *reinterpret_cast<const uint2*>(&Hk.toff);
-        uint32_t* tw = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(S.touch) + ts.x) + tid;
+        uint32_t* tw = tptr + (k >> 3) * kThreads;
+        const int sh = (k & 7) * 4;
         const uint32_t word = *tw;
-        int tc = (word >> ts.y) & 15;
-        if (isnew && tc < 15) { ++tc; *tw = word + (1u << ts.y); }
-        if (tc >= S.combo.overtouch) { c_gate += 1u; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
-        const int b = min(tc, 3) - 1;
-        const float2 cp = Hk.cpass[b];
+        int tc = (word >> sh) & 15;
+        if (isnew && tc < 15) { ++tc; *tw = word + (1u << sh); }
+        if (tc >= A.combo.overtouch) { c_gate += 1u; return QMMX_LEVEL_OVERTOUCHED; }     // M:1579
+        const float2 cp = g_S.cpass[min(tc, 3) - 1][k];
         if (!(pf >= cp.x && pf <= cp.y)) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
         const int side = dir - 1;                                            // M:1645: up -> long(0), down -> short(1)
-        const uint32_t cflags = S.combo.flags;
-        if (cflags & QMMX_F_USE_BLEND) {                                     // M:1730-1742
-            if (blend_fails(k, pf, tc, side, day_off)) { smem_inc(&S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
-        } else if (cflags & kCbHasMl) {                                      // M:1454-1466, M:1745-1755
-            const uint32_t m = __ldg(&S.G.mlmask[day_off + k]);
+        if (A.combo.flags & QMMX_F_USE_BLEND) {                              // M:1730-1742
+            if (blend_fails(&A, k, pf, tc, side, day_off)) { smem_inc(&g_S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
+        } else if (A.mlmask) {                                               // M:1454-1466, M:1745-1755
+            const uint32_t m = __ldg(&A.mlmask[day_off + k]);
             if ((m >> (side * 16 + tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
-        if (!(cflags & QMMX_F_DISABLE_POLICY_GATE)) {
-            if (!policy_passes(k, pf, side, i)) { smem_inc(&S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
+        if (!(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {
+            if (!policy_passes(&A, k, pf, side, i)) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
         }
         // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
         // thresholds (M:1669-1674) were rounded per level at CTA setup:
         // p <= stop (float64, p fp32)  <=>  p <= round_down_fp32(stop);  p >= target  <=>  p >= round_up_fp32(target)
-        const float2 th = Hk.thr[side];
+        const float2 th = g_S.thr[side][k];
         lo_thr = th.x; hi_thr = th.y;
         pos = k | (side << 8);
         entry = pf;
@@ -264,8 +251,7 @@ struct PathEngine {
         return QMMX_OK_ENTRY;
     }
 
-    __device__ __forceinline__ void do_exit(float pf, bool hit_lo, bool hit_hi, int i) {
-        BlockShared& S = smem();
+    __device__ __forceinline__ void do_exit(const ScanArgs& A, float pf, bool hit_lo, bool hit_hi, int i) {
         const int side = pos >> 8;
         // long: stop below (tested first), target above; short: stop above (tested first), target below
         const bool is_stop = (side == 0) ? hit_lo : hit_hi;
@@ -273,44 +259,43 @@ struct PathEngine {
         float exit_f = pf;
         if (!HL) {
             // close exit (M:2979-3012): exit at the tick price; fp32 values, float64 difference (M:1926)
-            const double a = (double)pf, e = (double)entry;
-            tp = side == 0 ? a - e : e - a;
+            const double diff = (double)pf - (double)entry;
+            tp = side == 0 ? diff : -diff;       // e - a == -(a - e) exactly
         } else {    // exit at the stop/target level itself (M:3636)
-            const double lp = S.cold[pos & 0xff].price;
+            const double lp = g_S.cold[pos & 0xff].price;
             double exit_px;
-            if (side == 0) exit_px = is_stop ? lp - S.combo.sp : lp + S.combo.tp;
-            else exit_px = is_stop ? lp + S.combo.sp : lp - S.combo.tp;
+            if (side == 0) exit_px = is_stop ? lp - A.combo.sp : lp + A.combo.tp;
+            else exit_px = is_stop ? lp + A.combo.sp : lp - A.combo.tp;
             const double e = (double)entry;
             tp = (side == 0) ? (exit_px - e) : (e - exit_px);
             exit_f = (float)exit_px;
         }
         pnl += tp; pnl2 += tp * tp;
-        cool_until = i + S.combo.cool_steps;                                 // M:2982, M:269-270
+        cool_until = i + A.combo.cool_steps;                                 // M:2982, M:269-270
         if (tp > 0) c_ml += 1u << 16;                                        // label, M:1936
         c_exit += is_stop ? 1u : (1u << 16);
-        if (PARITY) record_trade(path, ntr, entry_bar, i, side, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET, pos & 0xff, entry, exit_f, (float)tp);
+        if (PARITY) record_trade(&A, path, ntr, entry_bar, i, side, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET, pos & 0xff, entry, exit_f, (float)tp);
         ++ntr;
         pos = -1;
     }
 
     // price -> level index touched, or kFar (exact: see tables.h)
     __device__ __forceinline__ uint32_t classify(float pf) const {
-        const BlockShared& S = smem();
-        uint32_t v = S.cell[cell_of_bits(__float_as_int(pf), S.obase, S.shift, S.ncell)];
+        uint32_t v = g_cell[cell_of_bits(__float_as_int(pf), g_S.obase, g_S.shift, g_S.ncell)];
         if (v == kMixed) v = classify_zones(pf);
         return v;
     }
 
     // one tick: price pf = bar i's close (hh/ll = its high/low when HL); day_off = min(day, n_days-1) * kMaxLevels
-    __device__ __forceinline__ void step(float pf, float hh, float ll, int i, int day_off) {
-        BlockShared& S = smem();
+    __device__ __forceinline__ void step(const ScanArgs& A, float pf, float hh, float ll, int i, int day_off) {
         int code = QMMX_TOO_FAR;
         // direction (M:1529-1537) and last_direction update (M:2954-2955)
-        int dir;
+        int dir = d;
         if (!TINY) {
             // |p|,|prev| >= 2^-5 (QMMX_F_TINY_PRICES unset): fp32 spacing > 1.8e-9, so the +-1e-9 guard band of
             // the reference cannot change any comparison and dir doubles as the updated last_direction
-            dir = (pf > prev) ? 1 : ((pf < prev) ? 2 : d);
+            if (pf < prev) dir = 2;
+            if (pf > prev) dir = 1;
         } else {
             dir = 0;
             if (prev == prev) {
@@ -323,7 +308,7 @@ struct PathEngine {
             c_span += 1u;
             const bool hit_lo = (HL ? ll : pf) <= lo_thr;
             const bool hit_hi = (HL ? hh : pf) >= hi_thr;
-            if (hit_lo | hit_hi) do_exit(pf, hit_lo, hit_hi, i);
+            if (hit_lo | hit_hi) do_exit(A, pf, hit_lo, hit_hi, i);
         } else if (i < cool_until) {
             code = QMMX_COOLDOWN;                                            // M:1516
             c_span += 1u << 16;
@@ -332,31 +317,30 @@ struct PathEngine {
             ++c_dir;
         } else {
             const uint32_t v = classify(pf);
-            if (v != kFar) code = contact((int)v, pf, dir, i, day_off);      // else TOO_FAR (M:1545), or NOLEVELS (M:1524)
+            if (v != kFar) code = contact(A, (int)v, pf, dir, i, day_off);   // else TOO_FAR (M:1545), or NOLEVELS (M:1524)
         }
         if (!TINY) d = dir;
         else if (prev == prev && pf != prev) d = (pf > prev) ? 1 : 2;
         prev = pf;
-        if (PARITY && S.G.codes) {
-            if (S.L == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
-            S.G.codes[(int64_t)i * S.G.paths + path] = (uint8_t)code;
+        if (PARITY && A.codes) {
+            if (g_S.L == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
+            A.codes[(int64_t)i * A.paths + path] = (uint8_t)code;
         }
     }
 
     // end of path: open position => OPEN, realised 0, mark-to-market reported separately
-    __device__ __forceinline__ void finish() {
-        BlockShared& S = smem();
+    __device__ __forceinline__ void finish(const ScanArgs& A) {
         if (pos >= 0) {
             const int side = pos >> 8;
             const double e = (double)entry, last = (double)prev;
             mtm = (side == 0) ? (last - e) : (e - last);
-            if (PARITY) record_trade(path, ntr, entry_bar, -1, side, QMMX_EXIT_OPEN, pos & 0xff, entry, prev, 0.0f);
+            if (PARITY) record_trade(&A, path, ntr, entry_bar, -1, side, QMMX_EXIT_OPEN, pos & 0xff, entry, prev, 0.0f);
             ++ntr;
         }
-        if (PARITY && S.G.tcounts) S.G.tcounts[path] = ntr;
-        double fb = floor((pnl - S.G.hist_lo) * S.G.hist_inv_w);
+        if (PARITY && A.tcounts) A.tcounts[path] = ntr;
+        double fb = floor((pnl - A.hist_lo) * A.hist_inv_w);
         const int bin = fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
-        atomicAdd(&S.hist[bin], 1u);
+        atomicAdd(&g_S.hist[bin], 1u);
     }
 };
 
@@ -383,25 +367,25 @@ __device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
 }
 
 // add one finished path per lane (inactive lanes contribute neutral values) to the block aggregate
-template <class Engine>
-__device__ __forceinline__ void warp_accumulate(bool active, const Engine& E) {
-    BlockShared& S = smem();
+__device__ __noinline__ void warp_accumulate(bool active, double pnl, double pnl2, double mtm, uint32_t cg, uint32_t cm,
+                                             uint32_t ce, uint32_t cs, uint32_t cd, bool open) {
+    BlockShared& S = g_S;
     const int lane = threadIdx.x & 31;
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
-    const double s1 = warp_sum(active ? E.pnl : 0.0);
-    const double s2 = warp_sum(active ? E.pnl2 : 0.0);
-    const double s3 = warp_sum(active ? E.pnl * E.pnl : 0.0);
-    const double s4 = warp_sum(active ? E.mtm : 0.0);
-    const double mx = warp_max(active ? E.pnl : neg_inf);
-    const double mn = warp_max(active ? -E.pnl : neg_inf);
+    if (!active) { pnl = 0.0; pnl2 = 0.0; mtm = 0.0; cg = cm = ce = cs = cd = 0u; open = false; }
+    const double s1 = warp_sum(pnl);
+    const double s2 = warp_sum(pnl2);
+    const double s3 = warp_sum(pnl * pnl);
+    const double s4 = warp_sum(mtm);
+    const double mx = warp_max(active ? pnl : neg_inf);
+    const double mn = warp_max(active ? -pnl : neg_inf);
     // 16-bit fields: a warp sum of 32 values < 65536 each fits 21 bits, so reduce the halves separately
-    const unsigned cg = active ? E.c_gate : 0u, cm = active ? E.c_ml : 0u, ce = active ? E.c_exit : 0u, cs = active ? E.c_span : 0u;
     const unsigned n_over = __reduce_add_sync(0xffffffffu, cg & 0xffffu), n_conf = __reduce_add_sync(0xffffffffu, cg >> 16);
     const unsigned n_ml = __reduce_add_sync(0xffffffffu, cm & 0xffffu), n_wins = __reduce_add_sync(0xffffffffu, cm >> 16);
     const unsigned n_stop = __reduce_add_sync(0xffffffffu, ce & 0xffffu), n_tgt = __reduce_add_sync(0xffffffffu, ce >> 16);
     const unsigned n_inpos = __reduce_add_sync(0xffffffffu, cs & 0xffffu), n_cool = __reduce_add_sync(0xffffffffu, cs >> 16);
-    const unsigned n_dir = __reduce_add_sync(0xffffffffu, active ? E.c_dir : 0u);
-    const unsigned n_open = __popc(__ballot_sync(0xffffffffu, active && E.pos >= 0));
+    const unsigned n_dir = __reduce_add_sync(0xffffffffu, cd);
+    const unsigned n_open = __popc(__ballot_sync(0xffffffffu, open));
     const unsigned n = __popc(__ballot_sync(0xffffffffu, active));
     if (lane == 0 && n) {
         atomicAdd(&S.d[D_SUM_PNL], s1); atomicAdd(&S.d[D_SUM_PNL2], s2);
@@ -422,29 +406,51 @@ __device__ __forceinline__ void warp_accumulate(bool active, const Engine& E) {
     }
 }
 
-__device__ inline void block_zero_agg() {
-    BlockShared& S = smem();
+// per-CTA setup: zero the aggregate and build the shared tables from DevTables + this launch's combo
+__device__ inline void block_setup(const ScanArgs& A) {
+    BlockShared& S = g_S;
+    const DevTables* __restrict__ T = A.tables;
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
     for (int t = threadIdx.x; t < U_HIST; t += blockDim.x) S.u[t] = 0ull;
     for (int t = threadIdx.x; t < QMMX_PNL_HIST_BINS; t += blockDim.x) S.hist[t] = 0u;
     if (threadIdx.x < QMMX_AGG_ND) S.d[threadIdx.x] = 0.0;
-    if (threadIdx.x == 0) { S.xmax = neg_inf; S.xnegmin = neg_inf; }
+    if (threadIdx.x == 0) {
+        S.xmax = neg_inf; S.xnegmin = neg_inf;
+        S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
+    }
+    for (int k = threadIdx.x; k < kMaxLevels; k += blockDim.x) {
+        const DevLevel D = T->lev[k];
+        // M:1669-1674: long stop = L - SP, target = L + TP; short stop = L + SP, target = L - TP  (float64, then
+        // rounded toward the inside of the no-exit band so the fp32 compare equals the float64 compare)
+        S.thr[0][k] = make_float2(__double2float_rd(D.price - A.combo.sp), __double2float_ru(D.price + A.combo.tp));
+        S.thr[1][k] = make_float2(__double2float_rd(D.price - A.combo.tp), __double2float_ru(D.price + A.combo.sp));
+#pragma unroll
+        for (int b = 0; b < 3; ++b) S.cpass[b][k] = make_float2(D.cpass[b][0], D.cpass[b][1]);
+        S.cand_lo[k] = D.cand_lo; S.cand_hi[k] = D.cand_hi;
+        ColdLevel Cl; Cl.price = D.price; Cl.wlo = D.wlo; Cl.whi = D.whi; Cl.flags = D.flags; Cl.pad = 0u;
+        S.cold[k] = Cl;
+    }
+    for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) { S.zhi[t] = T->zhi[t]; S.zlev[t] = T->zlev[t]; }
+    const int n16 = (T->ncell + 15) / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(T->cell);
+    uint4* dst = reinterpret_cast<uint4*>(g_cell);
+    for (int t = threadIdx.x; t < n16; t += blockDim.x) dst[t] = src[t];
+    __syncthreads();
 }
 
-// flush the block aggregate into the flat global buffer of `combo`; caller syncs before
-__device__ inline void block_flush_agg(unsigned long long* flat, int combo, int steps) {
-    BlockShared& S = smem();
-    unsigned long long* gu = flat + (size_t)combo * QMMX_AGG_SLOTS;
+// flush the block aggregate into the flat global buffer of this launch's combo; caller syncs before
+__device__ inline void block_flush_agg(unsigned long long* gu, int steps) {
+    BlockShared& S = g_S;
     double* gd = reinterpret_cast<double*>(gu + QMMX_AGG_NU);
     if (threadIdx.x == 0) {
         // derived counters: n_steps, OK entries (every opened position ends as a trade or as OPEN), and the
         // remainder code (TOO_FAR, or NOLEVELS without levels)
         const unsigned long long nsteps = S.u[U_NPATHS] * (unsigned long long)steps;
         S.u[U_ENTRY + QMMX_OK_ENTRY] = S.u[U_NTRADES] + S.u[U_NOPEN];
+        if (S.L == 0) S.u[U_ENTRY + QMMX_DIR_UNKNOWN] = 0ull;      // NOLEVELS precedes DIR_UNKNOWN (M:1524)
         unsigned long long others = 0;
         for (int c = 0; c < QMMX_N_ENTRY_CODES; ++c) others += S.u[U_ENTRY + c];
         S.u[U_NSTEPS] = nsteps;
-        if (S.L == 0) { others -= S.u[U_ENTRY + QMMX_DIR_UNKNOWN]; S.u[U_ENTRY + QMMX_DIR_UNKNOWN] = 0ull; }   // NOLEVELS precedes DIR_UNKNOWN (M:1524)
         S.u[U_ENTRY + (S.L == 0 ? QMMX_NOLEVELS : QMMX_TOO_FAR)] += nsteps - others;
     }
     __syncthreads();
@@ -457,35 +463,6 @@ __device__ inline void block_flush_agg(unsigned long long* flat, int combo, int 
         atomic_max_f64(&gd[QMMX_AGG_ND + 0], S.xmax);
         atomic_max_f64(&gd[QMMX_AGG_ND + 1], S.xnegmin);
     }
-}
-
-__device__ inline void block_load_tables(const DevTables* __restrict__ T, const DevCombo* __restrict__ C) {
-    BlockShared& S = smem();
-    if (threadIdx.x == 0) {
-        S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
-        S.combo = *C;
-    }
-    for (int k = threadIdx.x; k < kMaxLevels; k += blockDim.x) {
-        const DevLevel D = T->lev[k];
-        HotLevel H;
-        // M:1669-1674: long stop = L - SP, target = L + TP; short stop = L + SP, target = L - TP  (float64, then
-        // rounded toward the inside of the no-exit band so the fp32 compare equals the float64 compare)
-        H.thr[0] = make_float2(__double2float_rd(D.price - C->sp), __double2float_ru(D.price + C->tp));
-        H.thr[1] = make_float2(__double2float_rd(D.price - C->tp), __double2float_ru(D.price + C->sp));
-#pragma unroll
-        for (int b = 0; b < 3; ++b) H.cpass[b] = make_float2(D.cpass[b][0], D.cpass[b][1]);
-        H.bit_lo = k < 32 ? 1u << k : 0u; H.bit_hi = k < 32 ? 0u : 1u << (k - 32);
-        H.cand_lo = D.cand_lo; H.cand_hi = D.cand_hi;
-        H.toff = (uint32_t)((k >> 3) * kThreads * 4); H.tsh = (uint32_t)((k & 7) * 4);
-        S.hot[k] = H;
-        ColdLevel Cl; Cl.price = D.price; Cl.wlo = D.wlo; Cl.whi = D.whi; Cl.flags = D.flags; Cl.pad = 0u;
-        S.cold[k] = Cl;
-    }
-    for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) { S.zhi[t] = T->zhi[t]; S.zlev[t] = T->zlev[t]; }
-    const int n16 = (T->ncell + 15) / 16;
-    const uint4* src = reinterpret_cast<const uint4*>(T->cell);
-    uint4* dst = reinterpret_cast<uint4*>(S.cell);
-    for (int t = threadIdx.x; t < n16; t += blockDim.x) dst[t] = src[t];
 }
 
 }  // namespace qmmx

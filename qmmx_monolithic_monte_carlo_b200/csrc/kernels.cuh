@@ -13,16 +13,6 @@ namespace qmmx {
 constexpr int kBlocksPerSM = QMMX_BLOCKS_PER_SM;
 constexpr int kWarps = kThreads / 32;
 
-struct ScanArgs {
-    const float* close; const float* high; const float* low;   // [steps][pitch] fp32
-    int64_t pitch, paths;
-    int32_t steps, combo0, parity_combo;
-    const DevTables* tables; const DevCombo* combos;
-    unsigned long long* flat;
-    const uint32_t* mlmask; const double* mlprob;               // per combo: [n_days][64] / [n_days][64][2][16]
-    EngineGlobals G;
-};
-
 // ---- Philox4x32-10 (Salmon et al., SC'11) ---------------------------------------------------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
 #pragma unroll
@@ -64,37 +54,24 @@ __device__ __forceinline__ float gbm_advance(const GbmDev& g, float S, float z) 
     return __fmul_rn(S, __expf(__fadd_rn(g.drift, __fmul_rn(g.vol, z))));
 }
 
-// per-CTA setup: tables, combo and run description into shared memory
-__device__ __forceinline__ void block_setup(const ScanArgs& A, int combo, bool parity) {
-    const DevCombo* C = A.combos + combo;
-    block_load_tables(A.tables + C->table, C);
-    block_zero_agg();
-    if (threadIdx.x == 0) {
-        BlockShared& S = smem();
-        EngineGlobals G = A.G;
-        const uint32_t f = C->flags;
-        G.mlmask = (A.mlmask && (f & kCbHasMl)) ? A.mlmask + (size_t)combo * G.n_days * kMaxLevels : nullptr;
-        G.mlprob = (A.mlprob && (f & kCbHasProb)) ? A.mlprob + (size_t)combo * G.n_days * kMaxLevels * 32 : nullptr;
-        if (!parity || combo != A.parity_combo) { G.trades = nullptr; G.tcounts = nullptr; G.codes = nullptr; }
-        S.G = G;
-    }
-    __syncthreads();
-}
-
 // warp-uniform day counter: day_off = min(step / steps_per_day, n_days - 1) * kMaxLevels without a division per step
+template <bool MULTIDAY>
 struct DayTracker {
-    int next, off, spd, max_off;
-    __device__ __forceinline__ void init(int spd_, int n_days) { spd = spd_; next = spd_; off = 0; max_off = (n_days > 1 ? n_days - 1 : 0) * kMaxLevels; }
-    __device__ __forceinline__ int at(int i) {
-        if (i >= next) { next += spd; off = min(off + kMaxLevels, max_off); }
+    int next, off;
+    __device__ __forceinline__ void init(const ScanArgs& A) { next = A.combo.spd; off = 0; }
+    __device__ __forceinline__ int at(const ScanArgs& A, int i) {
+        if (!MULTIDAY) return 0;
+        if (i == next) { next += A.combo.spd; off = min(off + kMaxLevels, (A.n_days - 1) * kMaxLevels); }
         return off;
     }
 };
 
 // ---- engine scan over resident bars -------------------------------------------------------------------------
-template <bool HL, bool PARITY, bool TINY, bool WIDE>
+// Bars are [step][pitch]: at one step the 32 lanes of a warp read one coalesced 128-byte line.  Each thread keeps
+// 2U loads in flight (register double buffer) so HBM latency is covered at 1024 threads per SM.
+template <bool MULTIDAY, bool HL, bool PARITY, bool TINY, bool WIDE>
 __device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY, WIDE>& E, const ScanArgs& A, int64_t path) {
-    constexpr int U = HL ? 2 : 4;
+    constexpr int U = 2;       // 2U loads in flight per thread: a warp revisits a step every ~1 us at 32 warps/SM
     const size_t pitch = (size_t)A.pitch;
     const float* pc = A.close + path;
     const float* ph = HL ? A.high + path : nullptr;
@@ -102,48 +79,51 @@ __device__ __forceinline__ void scan_path(PathEngine<HL, PARITY, TINY, WIDE>& E,
     const int steps = A.steps;
     float c0[U], c1[U], h0[U], h1[U], l0[U], l1[U];
     const int nfull = steps / (2 * U);
-    DayTracker day;
-    day.init(smem().combo.spd, A.G.n_days);
+    DayTracker<MULTIDAY> day;
+    day.init(A);
     int i = 0;
     if (nfull > 0) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            c0[u] = __ldg(pc + (size_t)u * pitch);
-            if (HL) { h0[u] = __ldg(ph + (size_t)u * pitch); l0[u] = __ldg(pl + (size_t)u * pitch); }
+            c0[u] = __ldg(pc); pc += pitch;
+            if (HL) { h0[u] = __ldg(ph); l0[u] = __ldg(pl); ph += pitch; pl += pitch; }
         }
         for (int n = 0; n < nfull; ++n, i += 2 * U) {
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const size_t o = (size_t)(i + U + u) * pitch;
-                c1[u] = __ldg(pc + o);
-                if (HL) { h1[u] = __ldg(ph + o); l1[u] = __ldg(pl + o); }
+                c1[u] = __ldg(pc); pc += pitch;
+                if (HL) { h1[u] = __ldg(ph); l1[u] = __ldg(pl); ph += pitch; pl += pitch; }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u, day.at(i + u));
+            for (int u = 0; u < U; ++u) E.step(A, c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u, day.at(A, i + u));
             if (n + 1 < nfull) {
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
-                    const size_t o = (size_t)(i + 2 * U + u) * pitch;
-                    c0[u] = __ldg(pc + o);
-                    if (HL) { h0[u] = __ldg(ph + o); l0[u] = __ldg(pl + o); }
+                    c0[u] = __ldg(pc); pc += pitch;
+                    if (HL) { h0[u] = __ldg(ph); l0[u] = __ldg(pl); ph += pitch; pl += pitch; }
                 }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u, day.at(i + U + u));
+            for (int u = 0; u < U; ++u) E.step(A, c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u, day.at(A, i + U + u));
         }
     }
 #pragma unroll 1
     for (; i < steps; ++i) {
-        const size_t o = (size_t)i * pitch;
-        const float c = __ldg(pc + o);
-        E.step(c, HL ? __ldg(ph + o) : 0.f, HL ? __ldg(pl + o) : 0.f, i, day.at(i));
+        const float c = __ldg(pc); pc += pitch;
+        float h = 0.f, l = 0.f;
+        if (HL) { h = __ldg(ph); l = __ldg(pl); ph += pitch; pl += pitch; }
+        E.step(A, c, h, l, i, day.at(A, i));
     }
 }
 
-template <bool HL, bool PARITY, bool TINY, bool WIDE>
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM) scan_kernel(const ScanArgs A) {
-    const int combo = A.combo0 + blockIdx.y;
-    block_setup(A, combo, PARITY);
+template <class Engine>
+__device__ __forceinline__ void accumulate_path(bool active, const Engine& E) {
+    warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.pos >= 0);
+}
+
+template <bool MULTIDAY, bool HL, bool PARITY, bool TINY, bool WIDE>
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) scan_kernel(const __grid_constant__ ScanArgs A) {
+    block_setup(A);
     PathEngine<HL, PARITY, TINY, WIDE> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t ntiles = (A.paths + 31) / 32;
@@ -151,12 +131,12 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) scan_kernel(const Scan
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(threadIdx.x, path);
-        if (active) { scan_path(E, A, path); E.finish(); }
+        if (active) { scan_path<MULTIDAY>(E, A, path); E.finish(A); }
         __syncwarp();
-        warp_accumulate(active, E);
+        accumulate_path(active, E);
     }
     __syncthreads();
-    block_flush_agg(A.flat, combo, A.steps);
+    block_flush_agg(A.flat, A.steps);
 }
 
 // ---- GBM generator (materialised bars) -------------------------------------------------------------------------
@@ -196,9 +176,8 @@ __global__ void __launch_bounds__(kThreads) gen_gbm_kernel(float* __restrict__ c
 
 // ---- fused GBM generate + scan: bars live in registers only -------------------------------------------------------
 template <bool HL, bool WIDE>
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const ScanArgs A, const GbmDev g) {
-    const int combo = A.combo0 + blockIdx.y;
-    block_setup(A, combo, false);
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
+    block_setup(A);
     PathEngine<HL, false, false, WIDE> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t ntiles = (A.paths + 31) / 32;
@@ -211,8 +190,8 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
             const uint64_t gid = g.path_offset + (uint64_t)path;
             float P = g.s0;
             float z[4];
-            DayTracker day;
-            day.init(smem().combo.spd, A.G.n_days);
+            DayTracker<true> day;
+            day.init(A);
             if (!HL) {
                 for (int i = 0; i < steps; i += 4) {
                     gbm_normals(g, gid, (uint32_t)(i >> 2), z);
@@ -220,7 +199,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
                     for (int u = 0; u < 4; ++u) {
                         if (i + u < steps) {
                             P = gbm_advance(g, P, z[u]);
-                            E.step(g.cents ? round_cents(P) : P, 0.f, 0.f, i + u, day.at(i + u));
+                            E.step(A, g.cents ? round_cents(P) : P, 0.f, 0.f, i + u, day.at(A, i + u));
                         }
                     }
                 }
@@ -231,16 +210,16 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
                     float hi = P, lo = P;
 #pragma unroll
                     for (int u = 0; u < 4; ++u) { P = gbm_advance(g, P, z[u]); hi = fmaxf(hi, P); lo = fminf(lo, P); }
-                    E.step(g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i, day.at(i));
+                    E.step(A, g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i, day.at(A, i));
                 }
             }
-            E.finish();
+            E.finish(A);
         }
         __syncwarp();
-        warp_accumulate(active, E);
+        accumulate_path(active, E);
     }
     __syncthreads();
-    block_flush_agg(A.flat, combo, A.steps);
+    block_flush_agg(A.flat, A.steps);
 }
 
 // ---- circular block bootstrap of a candle window ---------------------------------------------------------------

@@ -33,7 +33,7 @@ struct qmmx_ctx {
     bool dirty = true;
     // derived device state
     DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
-    DevCombo* d_combos = nullptr;
+    std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
     unsigned long long* d_flat = nullptr; int flat_combos = 0;
     bool any_hl = false, any_tiny = false;
@@ -91,8 +91,8 @@ int upload_vec(qmmx_ctx* ctx, T** dptr, const T* host, size_t n) {
     return QMMX_OK;
 }
 
-size_t scan_smem_bytes(const qmmx_ctx* c) {
-    return offsetof(BlockShared, cell) + (size_t)round_up(c->max_ncell, 16);
+size_t scan_smem_bytes(const qmmx_ctx* c) {      // dynamic part only: the grid-cell bytes
+    return (size_t)round_up(c->max_ncell, 16);
 }
 
 // (re)build every derived table after a configuration change
@@ -144,7 +144,7 @@ int prepare(qmmx_ctx* ctx) {
     for (auto& t : tabs) ctx->max_ncell = std::max(ctx->max_ncell, t.ncell);
     int rc;
     if ((rc = upload_vec(ctx, &ctx->d_tables, tabs.data(), tabs.size())) != 0) return rc;
-    if ((rc = upload_vec(ctx, &ctx->d_combos, combos.data(), combos.size())) != 0) return rc;
+    ctx->h_combos = combos;
     // logistic gates
     if (ctx->d_mlmask) { cudaFree(ctx->d_mlmask); ctx->d_mlmask = nullptr; }
     if (ctx->d_mlprob) { cudaFree(ctx->d_mlprob); ctx->d_mlprob = nullptr; }
@@ -173,26 +173,28 @@ int prepare(qmmx_ctx* ctx) {
     return QMMX_OK;
 }
 
-void fill_args(qmmx_ctx* ctx, ScanArgs& A, const float* c, const float* h, const float* l, int64_t pitch,
+// kernel parameters of one launch: combo `c` over the given bars (parity outputs are set by the caller)
+void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* h, const float* l, int64_t pitch,
                int64_t paths, int32_t steps) {
     std::memset(&A, 0, sizeof(A));
-    A.close = c; A.high = h; A.low = l; A.pitch = pitch; A.paths = paths; A.steps = steps;
-    A.combo0 = 0; A.parity_combo = 0;
-    A.tables = ctx->d_tables; A.combos = ctx->d_combos; A.flat = ctx->d_flat;
-    A.mlmask = ctx->d_mlmask; A.mlprob = ctx->d_mlprob;
-    EngineGlobals& G = A.G;
-    G.mlmask = nullptr; G.mlprob = nullptr; G.n_days = ctx->n_lr;
-    G.pol = ctx->d_pol; G.n_pol = ctx->n_pol;
-    G.z_go = ctx->z_go; G.z_skip = ctx->z_skip;
-    G.hist_lo = ctx->hist_lo; G.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
-    G.steps = steps; G.trades = nullptr; G.tcounts = nullptr; G.max_trades = 0; G.codes = nullptr; G.paths = paths;
+    const DevCombo& D = ctx->h_combos[c];
+    A.close = cl; A.high = h; A.low = l; A.pitch = pitch; A.paths = paths; A.steps = steps; A.combo_index = c;
+    A.tables = ctx->d_tables + D.table;
+    A.flat = ctx->d_flat + (size_t)c * QMMX_AGG_SLOTS;
+    const size_t per_mask = (size_t)ctx->n_lr * kMaxLevels;
+    A.mlmask = (ctx->d_mlmask && (D.flags & kCbHasMl)) ? ctx->d_mlmask + per_mask * c : nullptr;
+    A.mlprob = (ctx->d_mlprob && (D.flags & kCbHasProb)) ? ctx->d_mlprob + per_mask * 32 * c : nullptr;
+    A.pol = ctx->d_pol; A.n_pol = ctx->n_pol; A.n_days = ctx->n_lr;
+    A.z_go = ctx->z_go; A.z_skip = ctx->z_skip;
+    A.hist_lo = ctx->hist_lo; A.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
+    A.combo = D;
 }
 
-dim3 scan_grid(const qmmx_ctx* ctx, int64_t paths, int ncombos) {
+dim3 scan_grid(const qmmx_ctx* ctx, int64_t paths) {
     const int64_t ntiles = (paths + 31) / 32;
     const int64_t want = (ntiles + kWarps - 1) / kWarps;
     const int64_t cap = (int64_t)ctx->sm_count * kBlocksPerSM;
-    return dim3((unsigned)std::max<int64_t>(1, std::min(want, cap)), (unsigned)ncombos, 1);
+    return dim3((unsigned)std::max<int64_t>(1, std::min(want, cap)), 1, 1);
 }
 
 template <class K>
@@ -209,42 +211,53 @@ int init_flat(qmmx_ctx* ctx) {
     return QMMX_OK;
 }
 
-int launch_scan(qmmx_ctx* ctx, const ScanArgs& A, bool parity) {
+struct ParityOut { qmmx_trade* trades = nullptr; int32_t* tcounts = nullptr; uint8_t* codes = nullptr; int32_t max_trades = 0; };
+
+// one launch per parameter combo (run constants travel as kernel parameters); parity outputs belong to combo 0
+int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, int64_t pitch, int64_t paths,
+                int32_t steps, const ParityOut* par) {
     const int nc = (int)ctx->params.size();
     const size_t smem = scan_smem_bytes(ctx);
-    const dim3 grid = scan_grid(ctx, A.paths, nc);
+    const dim3 grid = scan_grid(ctx, paths);
     const bool hl = ctx->any_hl, tiny = ctx->any_tiny;
-    if (hl && (!A.high || !A.low)) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs high/low bars");
-    if (A.paths <= 0 || A.steps <= 0) return QMMX_OK;
-    if (A.steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
+    if (hl && (!h || !l)) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs high/low bars");
+    if (paths <= 0 || steps <= 0) return QMMX_OK;
+    if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
     int rc = QMMX_OK;
+#define LAUNCH2(MDv, HLv, PARv, TINYv, Wv)                                                    \
+    do {                                                                                      \
+        auto k = scan_kernel<MDv, HLv, PARv, TINYv, Wv>;                                      \
+        if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                               \
+        k<<<grid, kThreads, smem, ctx->stream>>>(A);                                          \
+    } while (0)
 #define LAUNCH(HLv, PARv, TINYv)                                                              \
     do {                                                                                      \
-        if (wide) {                                                                           \
-            auto k = scan_kernel<HLv, PARv, TINYv, true>;                                     \
-            if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                           \
-            k<<<grid, kThreads, smem, ctx->stream>>>(A);                                      \
-        } else {                                                                              \
-            auto k = scan_kernel<HLv, PARv, TINYv, false>;                                    \
-            if ((rc = set_smem_attr(ctx, k, smem)) != 0) return rc;                           \
-            k<<<grid, kThreads, smem, ctx->stream>>>(A);                                      \
-        }                                                                                     \
+        if (multiday) { if (wide) LAUNCH2(true, HLv, PARv, TINYv, true); else LAUNCH2(true, HLv, PARv, TINYv, false); } \
+        else { if (wide) LAUNCH2(false, HLv, PARv, TINYv, true); else LAUNCH2(false, HLv, PARv, TINYv, false); }        \
     } while (0)
+    const bool multiday = ctx->n_lr > 1;
     const bool wide = ctx->L > 32;
-    if (!parity) {
-        if (!hl && !tiny) LAUNCH(false, false, false);
-        else if (hl && !tiny) LAUNCH(true, false, false);
-        else if (!hl && tiny) LAUNCH(false, false, true);
-        else LAUNCH(true, false, true);
-    } else {
-        if (!hl && !tiny) LAUNCH(false, true, false);
-        else if (hl && !tiny) LAUNCH(true, true, false);
-        else if (!hl && tiny) LAUNCH(false, true, true);
-        else LAUNCH(true, true, true);
+    for (int c = 0; c < nc; ++c) {
+        ScanArgs A;
+        fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
+        const bool parity = par && c == 0;
+        if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
+        if (!parity) {
+            if (!hl && !tiny) LAUNCH(false, false, false);
+            else if (hl && !tiny) LAUNCH(true, false, false);
+            else if (!hl && tiny) LAUNCH(false, false, true);
+            else LAUNCH(true, false, true);
+        } else {
+            if (!hl && !tiny) LAUNCH(false, true, false);
+            else if (hl && !tiny) LAUNCH(true, true, false);
+            else if (!hl && tiny) LAUNCH(false, true, true);
+            else LAUNCH(true, true, true);
+        }
+        ctx->launches++;
+        CK(cudaGetLastError());
     }
 #undef LAUNCH
-    ctx->launches++;
-    CK(cudaGetLastError());
+#undef LAUNCH2
     return QMMX_OK;
 }
 
@@ -338,7 +351,7 @@ int qmmx_destroy(qmmx_ctx* ctx) {
     cudaDeviceSynchronize();
     free_bars(ctx);
     for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
-    cudaFree(ctx->d_tables); cudaFree(ctx->d_combos); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
+    cudaFree(ctx->d_tables); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
     cudaFree(ctx->d_pol); cudaFree(ctx->d_flat);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
@@ -533,11 +546,9 @@ int qmmx_run_scan_async(qmmx_ctx* c) {
     if (!ctx->d_close) return fail(ctx, QMMX_E_STATE, "no resident bars (qmmx_upload_bars / qmmx_gen_* first)");
     int rc = prepare(ctx);
     if (rc != 0) return rc;
-    ScanArgs A;
-    fill_args(ctx, A, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, ctx->paths, ctx->steps);
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if ((rc = init_flat(ctx)) != 0) return rc;
-    if ((rc = launch_scan(ctx, A, false)) != 0) return rc;
+    if ((rc = launch_scan(ctx, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, ctx->paths, ctx->steps, nullptr)) != 0) return rc;
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->ran = true;
     return QMMX_OK;
@@ -575,12 +586,11 @@ int qmmx_run_scan(qmmx_ctx* c, qmmx_agg* agg_out, qmmx_trade* trades_out, int32_
     if (e == cudaSuccess && (trade_counts_out || trades_out) && P > 0) e = cudaMalloc(&d_cnt, (size_t)P * 4);
     if (e == cudaSuccess && codes_out && P > 0 && T > 0) e = cudaMalloc(&d_codes, (size_t)P * T);
     if (e == cudaSuccess) {
-        ScanArgs A;
-        fill_args(ctx, A, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, P, T);
-        A.G.trades = d_tr; A.G.tcounts = d_cnt; A.G.max_trades = trades_out ? max_trades_per_path : 0; A.G.codes = d_codes;
+        ParityOut par;
+        par.trades = d_tr; par.tcounts = d_cnt; par.max_trades = trades_out ? max_trades_per_path : 0; par.codes = d_codes;
         cudaEventRecord(ctx->ev0, ctx->stream);
         rc = init_flat(ctx);
-        if (rc == 0) rc = launch_scan(ctx, A, true);
+        if (rc == 0) rc = launch_scan(ctx, ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, P, T, &par);
         cudaEventRecord(ctx->ev1, ctx->stream);
         if (rc == 0) {
             if (trades_out && d_tr) e = cudaMemcpyAsync(trades_out, d_tr, (size_t)P * max_trades_per_path * sizeof(qmmx_trade), cudaMemcpyDeviceToHost, ctx->stream);
@@ -627,9 +637,7 @@ int qmmx_run_scan_host(qmmx_ctx* c, const float* close, const float* high, const
                                  (size_t)w * 4, steps, cudaMemcpyHostToDevice, ctx->copy_stream));
         CK(cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
         CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
-        ScanArgs A;
-        fill_args(ctx, A, ctx->d_stage[b][0], ctx->d_stage[b][1], ctx->d_stage[b][2], chunk_paths, w, steps);
-        if ((rc = launch_scan(ctx, A, false)) != 0) return rc;
+        if ((rc = launch_scan(ctx, ctx->d_stage[b][0], ctx->d_stage[b][1], ctx->d_stage[b][2], chunk_paths, w, steps, nullptr)) != 0) return rc;
         CK(cudaEventRecord(ctx->ev_done[b], ctx->stream));
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
@@ -645,37 +653,26 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     if ((rc = prepare(ctx)) != 0) return rc;
     if (ctx->any_tiny) return fail(ctx, QMMX_E_UNSUPPORTED, "TINY_PRICES is not available in the fused GBM kernel");
     if (ctx->any_hl && gbm->sub_steps != 4) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs sub_steps = 4 (OHLC bars)");
-    ScanArgs A;
-    fill_args(ctx, A, nullptr, nullptr, nullptr, 0, paths, steps);
     const GbmDev g = make_gbm(gbm, seed, path_offset);
     const size_t smem = scan_smem_bytes(ctx);
-    const dim3 grid = scan_grid(ctx, paths, (int)ctx->params.size());
+    const dim3 grid = scan_grid(ctx, paths);
+    if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
+    if (gbm->sub_steps == 4 && !ctx->any_hl)
+        return fail(ctx, QMMX_E_UNSUPPORTED, "fused GBM with sub_steps = 4 requires EXIT_ON_HL (use sub_steps = 1 for close-only)");
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if ((rc = init_flat(ctx)) != 0) return rc;
-    if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
-    if (paths > 0 && steps > 0) {
-        if (gbm->sub_steps == 4) {
-            // OHLC recipe: 4 sub-steps per bar; the engine sees high/low only when EXIT_ON_HL is set
-            if (ctx->any_hl) {
-                if (ctx->L > 32) {
-                    if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true, true>, smem)) != 0) return rc;
-                    fused_gbm_kernel<true, true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
-                } else {
-                    if ((rc = set_smem_attr(ctx, fused_gbm_kernel<true, false>, smem)) != 0) return rc;
-                    fused_gbm_kernel<true, false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
-                }
-            } else {
-                return fail(ctx, QMMX_E_UNSUPPORTED, "fused GBM with sub_steps = 4 requires EXIT_ON_HL (use sub_steps = 1 for close-only)");
-            }
-        } else {
-            if (ctx->L > 32) {
-                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false, true>, smem)) != 0) return rc;
-                fused_gbm_kernel<false, true><<<grid, kThreads, smem, ctx->stream>>>(A, g);
-            } else {
-                if ((rc = set_smem_attr(ctx, fused_gbm_kernel<false, false>, smem)) != 0) return rc;
-                fused_gbm_kernel<false, false><<<grid, kThreads, smem, ctx->stream>>>(A, g);
-            }
-        }
+    const bool wide = ctx->L > 32, hl = gbm->sub_steps == 4;
+    for (int c = 0; c < (int)ctx->params.size() && paths > 0 && steps > 0; ++c) {
+        ScanArgs A;
+        fill_args(ctx, A, c, nullptr, nullptr, nullptr, 0, paths, steps);
+#define FUSED(HLv, Wv)                                                                        \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, fused_gbm_kernel<HLv, Wv>, smem)) != 0) return rc;   \
+            fused_gbm_kernel<HLv, Wv><<<grid, kThreads, smem, ctx->stream>>>(A, g);           \
+        } while (0)
+        if (hl) { if (wide) FUSED(true, true); else FUSED(true, false); }
+        else { if (wide) FUSED(false, true); else FUSED(false, false); }
+#undef FUSED
         ctx->launches++;
         CK(cudaGetLastError());
     }
