@@ -43,11 +43,10 @@ def workload(name: str):
 
 
 def lr_weights():
-    """Synthetic sklearn-form LR (no trained model ships with the reference): seeded N(0, .5^2)."""
-    rng = np.random.default_rng(20250829)
-    w = rng.normal(0.0, 0.5, 5)
-    w[4] += 1.0
-    return w.reshape(1, 5)
+    """Synthetic sklearn-form LR (no trained model ships with the reference):
+    x = [lvl_type(=1), |level - stop|, touch_count, dir_up] (M:1457-1461).  Chosen so that the gate is active:
+    first touches pass both ways, second touches pass only with the trend up, third touches fail."""
+    return np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])     # coef[4] + intercept
 
 
 def engine_params():
@@ -206,29 +205,12 @@ def main():
     eng.set_lr(lr)
     eng.upload_bars(close)
 
-    flat_ptr, flat_bytes = None, None
-
-    def flat_tensors():
-        nonlocal flat_ptr, flat_bytes
-        flat_ptr, flat_bytes = eng.agg_device()
-
-        class _Mem:
-            __cuda_array_interface__ = {"shape": (flat_bytes // 8,), "typestr": "<i8", "data": (flat_ptr, False),
-                                        "version": 3}
-        t = torch.as_tensor(_Mem(), device=f"cuda:{local_rank}")
-        nu, nd = abi.AGG_NU, abi.AGG_ND
-        t2 = t.view(-1, abi.AGG_SLOTS)
-        return t2[:, :nu], t2[:, nu:nu + nd].view(torch.float64), t2[:, nu + nd:].view(torch.float64)
+    from qmmx_monolithic_monte_carlo_b200 import distributed as D
 
     def step():
         eng.run_scan_async()
-        if world > 1:
-            u, d, x = flat_tensors()
-            uc, dc, xc = u.contiguous(), d.contiguous(), x.contiguous()
-            dist.all_reduce(uc, op=dist.ReduceOp.SUM)
-            dist.all_reduce(dc, op=dist.ReduceOp.SUM)
-            dist.all_reduce(xc, op=dist.ReduceOp.MAX)
-            u.copy_(uc); d.copy_(dc); x.copy_(xc)
+        if world > 1:   # the device reduction buffer is all-reduced in place over NCCL, on the same stream order
+            D.allreduce_flat_(D.device_flat_tensor(eng, local_rank))
 
     for _ in range(args.warmup):
         step()
