@@ -1,0 +1,120 @@
+"""Drop-in call shapes of the reference's simulators, running on the GPU library.
+
+`monte_carlo(...)`  ~ `QMMXApp.simulate_monte_carlo` (qmmx_monolithic.py:3353-3538): candidate pass on the host
+                      (O(n L), cheap), trials x candidates walk-forward on the device (`qmmx_run_jitter`),
+                      summary with the reference's index rules and message text.
+`run_paths(...)`    ~ the live engine (`evaluate_entry` + exit block) over many price paths.
+
+`levels` is the reference's list of dicts {color, type, index, price}; `bars` is the reference's list of
+{t, o, h, l, c} dicts (M:220-240) or a dict of arrays.  This module never touches oracle/.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from statistics import mean, median, pstdev
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import abi
+from .engine import MCEngine, sort_levels
+
+
+def _bar_arrays(bars, n):
+    if isinstance(bars, dict):
+        c, h, l = (np.asarray(bars[k], dtype=np.float64) for k in ("c", "h", "l"))
+    else:
+        c = np.array([float(b["c"]) for b in bars]); h = np.array([float(b["h"]) for b in bars])
+        l = np.array([float(b["l"]) for b in bars])
+    return c[-n:], h[-n:], l[-n:]
+
+
+def find_candidates(closes, level_prices, contact_prox, stop_padding, tp_padding, touch_limit):
+    """Candidate pass with_gates=False (M:3385-3442): nearest level to the close (first minimum wins), within
+    CONTACT_PROX, side by close-to-close move (flat => short), per-level touch limit keyed on round(level, 4)."""
+    out, seen, prev = [], {}, None
+    lp = [float(x) for x in level_prices]
+    for i, c in enumerate(closes):
+        c = float(c)
+        if prev is not None:
+            k = min(range(len(lp)), key=lambda j: abs(lp[j] - c))
+            dist = abs(lp[k] - c)
+            if dist <= contact_prox:
+                side = 0 if c > prev else 1
+                key = round(lp[k], 4)
+                tc = seen.get(key, 0) + 1
+                if tc <= touch_limit:
+                    seen[key] = tc
+                    out.append(dict(i=i, side=side, k=k, lvl=lp[k], entry=c, prox=dist, tc=tc,
+                                    stop=lp[k] - stop_padding if side == 0 else lp[k] + stop_padding,
+                                    target=lp[k] + tp_padding if side == 0 else lp[k] - tp_padding))
+        prev = c
+    return out
+
+
+@dataclass
+class MCSummary:
+    """Fields of the reference's MC/SUMMARY message (M:3513-3526)."""
+    candidates: int
+    trials: int
+    mean: float
+    median: float
+    stdev: float
+    best: float
+    worst: float
+    var05: float
+    cvar05: float
+    dd_mean: float
+    dd_worst: float
+    wins: float
+    losses: float
+    opens: float
+    totals: np.ndarray = field(repr=False, default=None)
+    drawdowns: np.ndarray = field(repr=False, default=None)
+
+    def message(self) -> str:
+        return (f"Candidates: {self.candidates} | Trials: {self.trials}\n"
+                f"Total R — mean {self.mean:+.2f}, median {self.median:+.2f}, stdev {self.stdev:.2f}\n"
+                f"Best {self.best:+.2f} | Worst {self.worst:+.2f}\n"
+                f"VaR(5%) {self.var05:+.2f} | CVaR(5%) {self.cvar05:+.2f}\n"
+                f"Max drawdown (R) — mean {self.dd_mean:+.2f}, worst {self.dd_worst:+.2f}\n"
+                f"Avg counts — wins {self.wins:.1f}, losses {self.losses:.1f}, open {self.opens:.1f}")
+
+
+def summarize(totals, drawdowns, wins, losses, opens, n_cand) -> MCSummary:
+    """M:3513-3526: p05 index = max(0, int(0.05 N) - 1); CVaR = mean of the sorted totals up to that index."""
+    t = [float(x) for x in totals]
+    dd = [float(x) for x in drawdowns]
+    ts = sorted(t)
+    p05 = max(0, int(0.05 * len(ts)) - 1)
+    return MCSummary(n_cand, len(t), mean(t), median(t), pstdev(t), max(t), min(t), ts[p05], mean(ts[:p05 + 1]),
+                     mean(dd), min(dd), mean(int(x) for x in wins), mean(int(x) for x in losses),
+                     mean(int(x) for x in opens), np.asarray(totals), np.asarray(drawdowns))
+
+
+def monte_carlo(eng: MCEngine, bars, levels: Sequence[dict], *, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25,
+                n=600, touch_limit=1, trials=500, entry_slip_std=0.01, level_jitter_std=0.02, stop_slip_std=0.0,
+                target_slip_std=0.0, seed: Optional[int] = None, replay=None) -> Optional[MCSummary]:
+    """Same arguments and defaults as `simulate_monte_carlo` (M:3353-3355) with with_gates=False.  The random
+    source is the device's Philox stream (key = seed), or `replay` = (normals[trials][K][4], uniforms[trials][K])
+    to reproduce host-drawn numbers exactly.  Returns None when no candidate is found (the reference shows
+    "No candidates found", M:3444-3446)."""
+    rows, price, _ = sort_levels(levels)
+    c, h, l = _bar_arrays(bars, n)
+    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit)
+    if not cands:
+        return None
+    out = eng.run_jitter(h, l, cands, stop_padding, tp_padding,
+                         (level_jitter_std, entry_slip_std, stop_slip_std, target_slip_std), trials,
+                         seed=0 if seed is None else int(seed), replay=replay)
+    return summarize(out["totals"], out["drawdowns"], out["wins"], out["losses"], out["opens"], len(cands))
+
+
+def run_paths(eng: MCEngine, close, levels: Sequence[dict], params, *, high=None, low=None, lr=None, policy=None):
+    """Engine over host price paths `[steps][paths]` (fp32): configure, upload, scan; one MCResult per combo."""
+    eng.set_levels(levels)
+    eng.set_params(params)
+    eng.set_lr(lr)
+    eng.set_policy(policy)
+    eng.upload_bars(close, high, low)
+    return eng.run_scan()

@@ -367,3 +367,51 @@ def test_gpu_jitter_mc_replay_is_exact(eng, case):
     refs = H.jitter_monte_carlo(bars, lv, P, n=n, touch_limit=case["touch_limit"], trials=4000, seed=5)
     se = refs["stdev"] / np.sqrt(4000) + dev["totals"].std() / np.sqrt(big)
     assert abs(dev["totals"].mean() - refs["mean"]) < 5 * se + 1e-9     # 5-sigma bound on the mean total R
+
+
+def test_gpu_monte_carlo_dropin_message(eng):
+    """`montecarlo.monte_carlo` (reference call shape) with replayed draws gives the oracle's summary text."""
+    from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    from tests.golden_util import format_mc_message
+    case = load_jitter_cases()[0]
+    lv = H.sort_levels(levels_by_name(case["levels"]))
+    P = H.Params(contact_prox=case["contact_prox"])
+    n, trials = case["n"], 500
+    cands = H.find_candidates(list(case["bars"]["c"])[-n:], lv, P, touch_limit=case["touch_limit"])
+    rng = np.random.default_rng(3)
+    normals = rng.standard_normal((trials, len(cands), 4)); uniforms = rng.random((trials, len(cands)))
+    ref = H.jitter_monte_carlo(case["bars"], lv, P, n=n, touch_limit=case["touch_limit"], trials=trials,
+                               draws=(normals, uniforms))
+    got = MC.monte_carlo(eng, case["bars"], levels_by_name(case["levels"]), contact_prox=case["contact_prox"], n=n,
+                         touch_limit=case["touch_limit"], trials=trials, replay=(normals, uniforms))
+    assert got.message() == format_mc_message(ref)
+    assert got.candidates == ref["candidates"]
+
+
+def test_gpu_full_size_properties(eng):
+    """BASELINE config sizes through size-independent properties: counters partition the steps, the histogram
+    counts every path, shards add up to the whole (linearity), and the run is idempotent."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120)
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    configure(eng, price, solid, params, lr)
+    g = abi.make_gbm()
+    P, T = 1_000_000, 390
+    whole = eng.run_fused_gbm(11, 0, P, T, g)[0]
+    a = whole.agg
+    assert a.n_paths == P and a.n_steps == P * T == sum(a.entry_hist)
+    assert sum(a.pnl_hist) == P and a.n_trades == a.exit_hist[0] + a.exit_hist[1] and a.n_open == a.exit_hist[3]
+    assert a.entry_hist[0] == a.n_trades + a.n_open and 0 < a.n_wins < a.n_trades
+    parts = [eng.run_fused_gbm(11, lo, hi - lo, T, g)[0].agg for lo, hi in [(0, 300_001), (300_001, 1_000_000)]]
+    for f in ("n_paths", "n_steps", "n_trades", "n_wins", "n_open"):
+        assert getattr(a, f) == sum(getattr(p, f) for p in parts), f
+    assert list(a.entry_hist) == [x + y for x, y in zip(parts[0].entry_hist, parts[1].entry_hist)]
+    assert list(a.pnl_hist) == [x + y for x, y in zip(parts[0].pnl_hist, parts[1].pnl_hist)]
+    assert a.sum_pnl == pytest.approx(parts[0].sum_pnl + parts[1].sum_pnl, rel=1e-9)
+    assert a.max_path_pnl == max(p.max_path_pnl for p in parts) and a.min_path_pnl == min(p.min_path_pnl for p in parts)
+    again = eng.run_fused_gbm(11, 0, P, T, g)[0].agg
+    assert list(again.entry_hist) == list(a.entry_hist) and again.n_wins == a.n_wins
+    # resident-bar scan of the same generated paths agrees with the fused kernel
+    eng.gen_gbm(11, 0, P, T, g)
+    scan = eng.run_scan()[0].agg
+    assert list(scan.entry_hist) == list(a.entry_hist) and list(scan.pnl_hist) == list(a.pnl_hist)
