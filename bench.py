@@ -56,7 +56,7 @@ def engine_params():
 class ClockSampler(threading.Thread):
     """nvidia-smi style clock / throttle-reason sampling (NVML) during the timed region."""
 
-    def __init__(self, index: int, period_s: float = 0.05):
+    def __init__(self, index: int, period_s: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.period, self.samples, self.reasons, self.max_mhz = index, period_s, [], set(), None
         self._stop_evt = threading.Event()
