@@ -207,10 +207,12 @@ def main():
 
     from qmmx_monolithic_monte_carlo_b200 import distributed as D
 
+    scratch = [None]
+
     def step():
         eng.run_scan_async()
-        if world > 1:   # the device reduction buffer is all-reduced in place over NCCL, on the same stream order
-            D.allreduce_flat_(D.device_flat_tensor(eng, local_rank))
+        if world > 1:   # one NCCL all-gather of the aggregate vector + the library's merge kernel, same stream order
+            scratch[0] = D.allgather_merge_(eng, local_rank, scratch=scratch[0])
 
     for _ in range(args.warmup):
         step()

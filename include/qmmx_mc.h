@@ -225,6 +225,10 @@ int  qmmx_fetch_agg(qmmx_ctx* ctx, qmmx_agg* agg_out /* [n_combos] */);
  * caller's collective (torch.distributed / NCCL all-reduce); unpack turns a flat HOST copy into structs */
 int  qmmx_agg_device(qmmx_ctx* ctx, void** d_flat, size_t* bytes);
 int  qmmx_agg_unpack(qmmx_ctx* ctx, const void* flat_host, int n_combos, qmmx_agg* out);
+/* multi-GPU merge with ONE collective: all-gather every rank's flat buffer into d_parts
+ * ([n_parts][n_combos * QMMX_AGG_SLOTS] 8-byte slots, device memory), then this call reduces them into the ctx's
+ * own buffer on the ctx stream (SUM counters, SUM sums, MAX extrema).  Asynchronous; qmmx_fetch_agg reads it. */
+int  qmmx_merge_flat(qmmx_ctx* ctx, const void* d_parts, int n_parts);
 
 /* batch logistic scoring, fp32 FMA: out[i][h] = sigmoid(w[h] . x[i]) (+ bias[h] if bias != NULL) */
 int  qmmx_lr_score(qmmx_ctx* ctx, const float* x /* [n][dim] */, int64_t n, int32_t dim,

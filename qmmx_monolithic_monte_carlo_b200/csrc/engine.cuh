@@ -45,7 +45,8 @@ struct ScanArgs {
     double hist_lo, hist_inv_w;
     // parity-mode outputs (may be null)
     qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
-    int32_t max_trades, n_days, n_pol, pad;
+    int32_t max_trades, n_days, n_pol, n_levels;
+    int32_t cell_obase, cell_shift, cell_ncell, pad;   // grid of the table (tables.h cell_of_bits), as constants
     DevCombo combo;
 };
 
@@ -136,12 +137,14 @@ __device__ __noinline__ bool blend_fails(const ScanArgs* A, int k, float pf, int
     double mlp = conf;
     if (A->mlprob) mlp = A->mlprob[(((size_t)day_off + k) * 2 + side) * 16 + tc];
     const double blended = A->combo.wr * conf + A->combo.wm * mlp;
-    return blended < A->combo.qmin;
+    const bool fails = blended < A->combo.qmin;
+    if (fails) smem_inc(&g_S.u[U_ENTRY + QMMX_COMBINED_LOW]);
+    return fails;
 }
 
 // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
 __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i) {
-    if (A->n_pol <= 0) return false;      // zero weights: sigmoid(0) = 0.5 < 0.60
+    if (A->n_pol <= 0) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return false; }   // zero weights: sigmoid(0) = 0.5 < 0.60
     const int spd = A->combo.spd;
     const double lp = g_S.cold[k].price;
     const double pa = fabs((double)pf - lp);
@@ -153,7 +156,9 @@ __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, i
     const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < A->n_pol ? day : A->n_pol - 1);
     const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
     const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x1, x3, x4, x5, x6);
-    return (z_side >= A->z_go) && (z_sk < A->z_skip);
+    const bool pass = (z_side >= A->z_go) && (z_sk < A->z_skip);
+    if (!pass) smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]);
+    return pass;
 }
 
 // parity mode: one trade record
@@ -231,14 +236,14 @@ struct PathEngine {
         if (!(pf >= cp.x && pf <= cp.y)) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
         const int side = dir - 1;                                            // M:1645: up -> long(0), down -> short(1)
         if (A.combo.flags & QMMX_F_USE_BLEND) {                              // M:1730-1742
-            if (blend_fails(&A, k, pf, tc, side, day_off)) { smem_inc(&g_S.u[U_ENTRY + QMMX_COMBINED_LOW]); return QMMX_COMBINED_LOW; }
+            if (blend_fails(&A, k, pf, tc, side, day_off)) return QMMX_COMBINED_LOW;
         } else if (A.mlmask) {                                               // M:1454-1466, M:1745-1755
             const uint32_t m = __ldg(&A.mlmask[day_off + k]);
             if ((m >> (side * 16 + tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
         if (!(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {
-            if (!policy_passes(&A, k, pf, side, i)) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return QMMX_ONLINE_POLICY; }
+            if (!policy_passes(&A, k, pf, side, i)) return QMMX_ONLINE_POLICY;
         }
         // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
         // thresholds (M:1669-1674) were rounded per level at CTA setup:
@@ -280,8 +285,8 @@ struct PathEngine {
     }
 
     // price -> level index touched, or kFar (exact: see tables.h)
-    __device__ __forceinline__ uint32_t classify(float pf) const {
-        uint32_t v = g_cell[cell_of_bits(__float_as_int(pf), g_S.obase, g_S.shift, g_S.ncell)];
+    __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
+        uint32_t v = g_cell[cell_of_bits(__float_as_int(pf), A.cell_obase, A.cell_shift, A.cell_ncell)];
         if (v == kMixed) v = classify_zones(pf);
         return v;
     }
@@ -316,14 +321,14 @@ struct PathEngine {
             code = QMMX_DIR_UNKNOWN;                                         // M:1538 (NOLEVELS when L == 0, fixed at flush)
             ++c_dir;
         } else {
-            const uint32_t v = classify(pf);
+            const uint32_t v = classify(A, pf);
             if (v != kFar) code = contact(A, (int)v, pf, dir, i, day_off);   // else TOO_FAR (M:1545), or NOLEVELS (M:1524)
         }
         if (!TINY) d = dir;
         else if (prev == prev && pf != prev) d = (pf > prev) ? 1 : 2;
         prev = pf;
         if (PARITY && A.codes) {
-            if (g_S.L == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
+            if (A.n_levels == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
             A.codes[(int64_t)i * A.paths + path] = (uint8_t)code;
         }
     }

@@ -366,6 +366,27 @@ __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
     }
 }
 
+// merge the all-gathered reduction buffers of n_parts ranks: SUM u64 counters, SUM f64 sums, MAX extrema
+__global__ void merge_flat_kernel(unsigned long long* __restrict__ flat, const unsigned long long* __restrict__ parts,
+                                  int n_parts, int n_slots_total) {
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n_slots_total; t += gridDim.x * blockDim.x) {
+        const int s = t % QMMX_AGG_SLOTS;
+        if (s < QMMX_AGG_NU) {
+            unsigned long long acc = 0ull;
+            for (int p = 0; p < n_parts; ++p) acc += parts[(size_t)p * n_slots_total + t];
+            flat[t] = acc;
+        } else if (s < QMMX_AGG_NU + QMMX_AGG_ND) {
+            double acc = 0.0;
+            for (int p = 0; p < n_parts; ++p) acc += __longlong_as_double((long long)parts[(size_t)p * n_slots_total + t]);
+            flat[t] = (unsigned long long)__double_as_longlong(acc);
+        } else {
+            double acc = __longlong_as_double((long long)parts[t]);
+            for (int p = 1; p < n_parts; ++p) { const double v = __longlong_as_double((long long)parts[(size_t)p * n_slots_total + t]); acc = v > acc ? v : acc; }
+            flat[t] = (unsigned long long)__double_as_longlong(acc);
+        }
+    }
+}
+
 __global__ void init_flat_kernel(unsigned long long* flat, int n_combos) {
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
     const int n = n_combos * QMMX_AGG_SLOTS;

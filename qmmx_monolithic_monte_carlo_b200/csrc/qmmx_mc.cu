@@ -33,6 +33,8 @@ struct qmmx_ctx {
     bool dirty = true;
     // derived device state
     DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
+    struct CellGrid { int32_t obase, shift, ncell; };
+    std::vector<CellGrid> grids;
     std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
     unsigned long long* d_flat = nullptr; int flat_combos = 0;
@@ -141,7 +143,8 @@ int prepare(qmmx_ctx* ctx) {
             return fail(ctx, QMMX_E_UNSUPPORTED, "EXIT_ON_HL / TINY_PRICES must be the same for all combos of a run");
     ctx->n_tables = (int)tabs.size();
     ctx->max_ncell = 1;
-    for (auto& t : tabs) ctx->max_ncell = std::max(ctx->max_ncell, t.ncell);
+    ctx->grids.clear();
+    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell}); }
     int rc;
     if ((rc = upload_vec(ctx, &ctx->d_tables, tabs.data(), tabs.size())) != 0) return rc;
     ctx->h_combos = combos;
@@ -187,6 +190,8 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.pol = ctx->d_pol; A.n_pol = ctx->n_pol; A.n_days = ctx->n_lr;
     A.z_go = ctx->z_go; A.z_skip = ctx->z_skip;
     A.hist_lo = ctx->hist_lo; A.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
+    A.n_levels = ctx->L;
+    A.cell_obase = ctx->grids[D.table].obase; A.cell_shift = ctx->grids[D.table].shift; A.cell_ncell = ctx->grids[D.table].ncell;
     A.combo = D;
 }
 
@@ -693,6 +698,17 @@ int qmmx_agg_device(qmmx_ctx* c, void** d_flat, size_t* bytes) {
     if (!ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
     if (d_flat) *d_flat = ctx->d_flat;
     if (bytes) *bytes = ctx->params.size() * QMMX_AGG_SLOTS * 8;
+    return QMMX_OK;
+}
+
+int qmmx_merge_flat(qmmx_ctx* c, const void* d_parts, int n_parts) {
+    ENTER(c);
+    if (!ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    if (!d_parts || n_parts < 1) return fail(ctx, QMMX_E_BADARG, "merge_flat: null parts");
+    const int n = (int)ctx->params.size() * QMMX_AGG_SLOTS;
+    merge_flat_kernel<<<std::max(1, (n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, static_cast<const unsigned long long*>(d_parts), n_parts, n);
+    ctx->launches++;
+    CK(cudaGetLastError());
     return QMMX_OK;
 }
 

@@ -76,6 +76,20 @@ def allreduce_flat_(flat_i64, group=None):
     return flat_i64
 
 
+def allgather_merge_(eng, device_index: int, group=None, scratch=None):
+    """The production N>1 merge: ONE NCCL all-gather of the 2.3 KB-per-combo vector, then the library's own merge
+    kernel (qmmx_merge_flat) on the ctx stream.  Returns the gather scratch tensor for reuse."""
+    import torch
+    import torch.distributed as dist
+    flat = device_flat_tensor(eng, device_index)
+    world = dist.get_world_size(group)
+    if scratch is None or scratch.shape != (world,) + tuple(flat.shape):
+        scratch = torch.empty((world,) + tuple(flat.shape), dtype=torch.int64, device=flat.device)
+    dist.all_gather_into_tensor(scratch, flat, group=group)
+    eng.merge_flat(scratch.data_ptr(), world)
+    return scratch
+
+
 def device_flat_tensor(eng, device_index: int):
     """torch int64 view [n_combos, AGG_SLOTS] of the engine's device reduction buffer (zero copy)."""
     import torch

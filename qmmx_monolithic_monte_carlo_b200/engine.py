@@ -67,6 +67,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_fetch_agg": (C.c_int, [vp, vp]),
         "qmmx_agg_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "qmmx_agg_unpack": (C.c_int, [vp, vp, C.c_int, vp]),
+        "qmmx_merge_flat": (C.c_int, [vp, vp, C.c_int]),
         "qmmx_lr_score": (C.c_int, [vp, vp, i64, i32, vp, vp, i32, vp]),
         "qmmx_run_jitter": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, dbl, dbl, vp, i64, u64, u64,
                                       vp, vp, vp, vp, vp, vp, vp]),
@@ -311,6 +312,10 @@ class MCEngine:
         p, n = C.c_void_p(), C.c_size_t()
         self._ck(self._L.qmmx_agg_device(self._h, C.byref(p), C.byref(n)))
         return p.value, n.value
+
+    def merge_flat(self, d_parts_ptr: int, n_parts: int):
+        """Reduce all-gathered flat buffers (device pointer, [n_parts][n_combos * AGG_SLOTS]) into this ctx's."""
+        self._ck(self._L.qmmx_merge_flat(self._h, C.c_void_p(d_parts_ptr), n_parts))
 
     def unpack_flat(self, flat_host: np.ndarray):
         flat_host = np.ascontiguousarray(flat_host).view(np.uint64).reshape(-1, abi.AGG_SLOTS)
