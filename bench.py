@@ -155,6 +155,105 @@ def run_reference(args, wl, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_extra(args, name, rank, local_rank, world):
+    """Secondary configs of BASELINE.json (not the driver's headline line): c2hl (C2 with OHLC bars and exits on
+    high/low), c3 (fused Philox GBM + scan, 12.5M paths per GPU), c4 (256-combo stop/target x cooldown sweep over
+    resident bars), c5 (block bootstrap of a 40-bar window into 5-day paths, per-day LR weights)."""
+    import torch
+    import torch.distributed as dist
+    from qmmx_monolithic_monte_carlo_b200 import distributed as D, engine as E
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    eng = E.MCEngine(local_rank, args.lib)
+    stream = torch.cuda.Stream(); torch.cuda.set_stream(stream); eng.set_stream(stream.cuda_stream)
+    eng.set_levels(F.levels_30())
+    g = abi.make_gbm()
+    cfg = {}
+    if name == "c3":
+        P = args.paths or 12_500_000
+        eng.set_params(engine_params()); eng.set_lr(lr_weights())
+        units = P * STEPS_PER_PATH
+        run = lambda: eng.run_fused_gbm_async(F.HOST_SEED, rank * P, P, STEPS_PER_PATH, g)
+        cfg = dict(workload=f"C3: {P} Philox GBM paths x 390 per GPU, generated and scanned in registers (no bar traffic)",
+                   bytes_per_step=0)
+    elif name == "c2hl":
+        P = args.paths or 1_000_000
+        eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True)); eng.set_lr(lr_weights())
+        eng.gen_gbm(F.HOST_SEED, rank * P, P, STEPS_PER_PATH, abi.make_gbm(sub_steps=4))
+        units = P * STEPS_PER_PATH
+        run = eng.run_scan_async
+        cfg = dict(workload=f"C2-HL: {P} device GBM OHLC paths x 390 per GPU, exits on bar high/low", bytes_per_step=12)
+    elif name == "c4":
+        P = args.paths or 1_000_000
+        grid = [abi.make_params(contact_prox=0.10, stop_padding=0.10 + 0.05 * i, tp_padding=tp, cooldown_s=cd)
+                for i in range(16) for tp in (0.15, 0.25, 0.35, 0.50) for cd in (0, 60, 300, 900)]
+        eng.set_params(grid); eng.set_lr(lr_weights())
+        eng.gen_gbm(F.HOST_SEED, rank * P, P, STEPS_PER_PATH, g)
+        units = len(grid) * P * STEPS_PER_PATH
+        run = eng.run_scan_async
+        cfg = dict(workload=f"C4: {len(grid)} stop/target x cooldown combos x {P} resident GBM paths x 390 per GPU",
+                   bytes_per_step=4.0 / len(grid), unit_note="combo-path-steps")
+    elif name == "c5":
+        P, days = args.paths or 1_250_000, 5
+        rng = np.random.default_rng(5)
+        lr5 = np.column_stack([rng.normal(0.2, 0.2, days), rng.normal(-0.5, 0.2, days), rng.normal(-0.45, 0.1, days),
+                               rng.normal(0.35, 0.1, days), rng.normal(1.0, 0.1, days)])
+        eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True)); eng.set_lr(lr5)
+        window = F.synthetic_window(40)
+        T = days * STEPS_PER_PATH
+        units = P * T
+
+        def run():
+            eng.gen_bootstrap(F.HOST_SEED, rank * P, P, T, window, 5)
+            eng.run_scan_async()
+        cfg = dict(workload=f"C5: block bootstrap (block 5) of a 40-bar window into {P} x {days}-day paths per GPU, "
+                            "per-day LR weights, exits on high/low; generate (c,h,l) then scan", bytes_per_step=24)
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    scratch = [None]
+
+    def step():
+        run()
+        if world > 1:
+            scratch[0] = D.allgather_merge_(eng, local_rank, scratch=scratch[0])
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    res = eng.fetch_agg()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local_rank); sampler.start()
+    l0 = eng.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clocks = sampler.stop()
+    if rank == 0:
+        peak, src = measured_peak_hbm()
+        ach = cfg["bytes_per_step"] * units / (ms * 1e-3) / 1e9
+        print(json.dumps({
+            "metric": METRIC, "value": units * world / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 bars", "data": "synthetic", "config": cfg,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                         "note": "whole step (all kernels) / algorithmic bytes", "peak_source": src},
+            "clocks": clocks, "gpu_launches": eng.launch_count() - l0,
+            "result_check": {"n_paths": res[0].n_paths, "n_trades": res[0].n_trades, "hit_rate": res[0].hit_rate,
+                             "combos": len(res)}}), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -172,6 +271,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "ours" and args.workload in ("c3", "c4", "c5", "c2hl"):
+        run_extra(args, args.workload, rank, local_rank, world)
+        return
     wl = workload(args.workload)
     if args.paths:
         wl["paths"] = args.paths

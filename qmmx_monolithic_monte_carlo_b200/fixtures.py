@@ -55,3 +55,13 @@ def host_gbm_closes(paths: int, steps: int = 390, *, seed: int = HOST_SEED, s0: 
             px = np.round(px, 2)
         out[:, lo:hi] = px.astype(np.float32)
     return out
+
+
+def synthetic_window(n_bars: int = 40, *, seed: int = 5, s0: float = GBM_S0, sigma: float = GBM_SIGMA_ANNUAL) -> np.ndarray:
+    """A seeded OHLC candle window `[n_bars][4]` (o, h, l, c), fp32: 4 GBM sub-steps per bar."""
+    rng = np.random.Generator(np.random.Philox(key=seed))
+    vol = sigma * np.sqrt(GBM_DT / 4.0)
+    sub = s0 * np.exp(np.cumsum(-0.5 * vol * vol + vol * rng.standard_normal(4 * n_bars))).reshape(n_bars, 4)
+    o = np.concatenate([[s0], sub[:-1, 3]])
+    h = np.maximum(o, sub.max(axis=1)); l = np.minimum(o, sub.min(axis=1))
+    return np.stack([o, h, l, sub[:, 3]], axis=1).astype(np.float32)
