@@ -46,7 +46,8 @@ struct ScanArgs {
     // parity-mode outputs (may be null)
     qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
     int32_t max_trades, n_days, n_pol, n_levels;
-    int32_t cell_obase, cell_shift, cell_ncell, pad;   // grid of the table (tables.h cell_of_bits), as constants
+    int32_t cell_obase, cell_shift, cell_ncell;        // grid of the table (tables.h cell_of_bits), as constants
+    int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
     DevCombo combo;
 };
 
@@ -67,11 +68,12 @@ struct BlockShared {
     uint32_t hist[QMMX_PNL_HIST_BINS];  // per-path PnL histogram (32-bit: native shared-memory atomics)
     double d[QMMX_AGG_ND];
     double xmax, xnegmin;
-    // per-thread touch counters: 4-bit saturating, 64 levels -> 8 words per thread, [word][thread]
-    uint32_t touch[8 * kThreads];
 };
 
 __shared__ BlockShared g_S;
+// per-thread touch counters of the lockstep-v1 engine: 4-bit saturating, 64 levels -> 8 words per thread,
+// [word][thread].  A separate symbol so that kernels which do not use it (scan_lean.cuh) do not pay for it.
+__shared__ uint32_t g_touch[8 * kThreads];
 extern __shared__ __align__(16) uint8_t g_cell[];   // level index / kFar / kMixed per grid cell
 
 __device__ __forceinline__ void smem_inc(unsigned long long* p, unsigned long long v = 1ull) { atomicAdd(p, v); }
@@ -181,7 +183,7 @@ template <> struct LatchType<true> { typedef unsigned long long T; };
 template <bool HL, bool PARITY, bool TINY, bool WIDE>
 struct PathEngine {
     typedef typename LatchType<WIDE>::T latch_t;
-    uint32_t* tptr;        // &g_S.touch[tid]: this thread's column of touch counters
+    uint32_t* tptr;        // &g_touch[tid]: this thread's column of touch counters
     // EngineState (M:259-270) + contact latch (M:1376)
     float prev;            // NaN until the first tick
     int d;                 // last_direction: 0 unknown, 1 up, 2 down
@@ -202,7 +204,7 @@ struct PathEngine {
     int64_t path; int entry_bar; int ntr;
 
     __device__ __forceinline__ void reset(int tid, int64_t path_) {
-        tptr = &g_S.touch[tid]; path = path_;
+        tptr = &g_touch[tid]; path = path_;
         prev = __int_as_float(0x7fc00000);
         d = 0; cool_until = 0; pos = -1; lo_thr = 0.f; hi_thr = 0.f; entry = 0.f; entry_bar = 0;
         latch = 0; c_gate = 0u; c_ml = 0u; c_exit = 0u; c_span = 0u; c_dir = 0u;

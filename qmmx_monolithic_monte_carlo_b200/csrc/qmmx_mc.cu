@@ -5,11 +5,13 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "kernels.cuh"
+#include "scan_lean.cuh"
 #include "tables_host.h"
 
 using namespace qmmx;
@@ -39,6 +41,8 @@ struct qmmx_ctx {
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
     unsigned long long* d_flat = nullptr; int flat_combos = 0;
     bool any_hl = false, any_tiny = false;
+    bool lean_ok = false;      // scan_lean.cuh's sign-encoded gate table is valid for these levels
+    bool force_v1 = false;     // QMMX_SCAN_V1=1: run the first-generation lockstep kernel (A/B measurements)
     // resident bars
     float *d_close = nullptr, *d_high = nullptr, *d_low = nullptr;
     bool own_bars = false;
@@ -145,6 +149,11 @@ int prepare(qmmx_ctx* ctx) {
     ctx->max_ncell = 1;
     ctx->grids.clear();
     for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell}); }
+    ctx->lean_ok = true;       // every non-empty confidence interval must have a positive upper bound (sign encoding)
+    for (auto& t : tabs)
+        for (int k = 0; k < t.L; ++k)
+            for (int b = 0; b < 3; ++b)
+                if (t.lev[k].cpass[b][0] <= t.lev[k].cpass[b][1] && !(t.lev[k].cpass[b][1] > 0.0f)) ctx->lean_ok = false;
     int rc;
     if ((rc = upload_vec(ctx, &ctx->d_tables, tabs.data(), tabs.size())) != 0) return rc;
     ctx->h_combos = combos;
@@ -192,6 +201,7 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.hist_lo = ctx->hist_lo; A.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
     A.n_levels = ctx->L;
     A.cell_obase = ctx->grids[D.table].obase; A.cell_shift = ctx->grids[D.table].shift; A.cell_ncell = ctx->grids[D.table].ncell;
+    A.cell_bytes = (int32_t)scan_smem_bytes(ctx);
     A.combo = D;
 }
 
@@ -242,12 +252,33 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
     } while (0)
     const bool multiday = ctx->n_lr > 1;
     const bool wide = ctx->L > 32;
+    const bool lean = ctx->lean_ok && !tiny && !ctx->force_v1;
+    const size_t lean_smem = lean_smem_bytes((int)smem, ctx->L);
+    const dim3 lean_grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(((paths + 31) / 32 + kLeanWarps - 1) / kLeanWarps,
+                                                                            (int64_t)ctx->sm_count * kLeanBlocksPerSM)), 1, 1);
+#define LEAN3(MDv, HLv, PARv, Wv, SLv)                                                        \
+    do {                                                                                      \
+        auto k = lean_scan_kernel<MDv, HLv, PARv, Wv, SLv>;                                   \
+        if ((rc = set_smem_attr(ctx, k, lean_smem)) != 0) return rc;                          \
+        k<<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A);                            \
+    } while (0)
+#define LEAN2(MDv, HLv, PARv, Wv)                                                             \
+    do { if (PARv || slow) LEAN3(MDv, HLv, PARv, Wv, true); else LEAN3(MDv, HLv, false, Wv, false); } while (0)
+#define LEAN(HLv, PARv)                                                                       \
+    do {                                                                                      \
+        if (multiday) { if (wide) LEAN2(true, HLv, PARv, true); else LEAN2(true, HLv, PARv, false); } \
+        else { if (wide) LEAN2(false, HLv, PARv, true); else LEAN2(false, HLv, PARv, false); }        \
+    } while (0)
     for (int c = 0; c < nc; ++c) {
         ScanArgs A;
         fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
         const bool parity = par && c == 0;
         if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
-        if (!parity) {
+        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
+        if (lean) {
+            if (!parity) { if (hl) LEAN(true, false); else LEAN(false, false); }
+            else { if (hl) LEAN(true, true); else LEAN(false, true); }
+        } else if (!parity) {
             if (!hl && !tiny) LAUNCH(false, false, false);
             else if (hl && !tiny) LAUNCH(true, false, false);
             else if (!hl && tiny) LAUNCH(false, false, true);
@@ -263,6 +294,9 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
     }
 #undef LAUNCH
 #undef LAUNCH2
+#undef LEAN
+#undef LEAN2
+#undef LEAN3
     return QMMX_OK;
 }
 
@@ -336,6 +370,7 @@ int qmmx_create(int device, qmmx_ctx** out) {
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(QMMX_E_CUDA);
     if (prop.major < 10) return bail(QMMX_E_UNSUPPORTED);   // sm_100a cubin only
     ctx->sm_count = prop.multiProcessorCount;
+    { const char* v1 = std::getenv("QMMX_SCAN_V1"); ctx->force_v1 = v1 && v1[0] == '1'; }
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     ctx->stream = ctx->own_stream;

@@ -232,6 +232,9 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
         const int z0 = zone_index(std::min(c_lo, omax)), z1 = zone_index(std::min(c_hi, omax));
         T->cell[c] = (z0 == z1) ? T->zlev[z0] : kMixed;
     }
+    // scan_lean.cuh clamps with one unsigned min, which sends prices below the grid to the LAST cell: both end cells
+    // must then resolve the same way (both far in the full-coverage case; else through the exact zone search)
+    if (T->cell[0] != T->cell[ncell - 1]) { T->cell[0] = kMixed; T->cell[ncell - 1] = kMixed; }
     return 0;
 }
 
