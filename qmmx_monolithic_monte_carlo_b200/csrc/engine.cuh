@@ -47,6 +47,7 @@ struct ScanArgs {
     qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
     int32_t max_trades, n_days, n_pol, n_levels;
     int32_t cell_obase, cell_shift, cell_ncell;        // grid of the table (tables.h cell_of_bits), as constants
+    float guard[4];                                    // far zones adjoining the grid (tables.h DevTables::guard)
     int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
     DevCombo combo;
 };
@@ -289,7 +290,7 @@ struct PathEngine {
     // price -> level index touched, or kFar (exact: see tables.h)
     __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
         uint32_t v = g_cell[cell_of_bits(__float_as_int(pf), A.cell_obase, A.cell_shift, A.cell_ncell)];
-        if (v == kMixed) v = classify_zones(pf);
+        if (v >= kMixBase && v != kFar) v = classify_zones(pf);   // any straddling cell: exact zone search
         return v;
     }
 

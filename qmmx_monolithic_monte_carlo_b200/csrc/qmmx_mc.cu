@@ -35,7 +35,7 @@ struct qmmx_ctx {
     bool dirty = true;
     // derived device state
     DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
-    struct CellGrid { int32_t obase, shift, ncell; };
+    struct CellGrid { int32_t obase, shift, ncell; float guard[4]; };
     std::vector<CellGrid> grids;
     std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
@@ -148,7 +148,7 @@ int prepare(qmmx_ctx* ctx) {
     ctx->n_tables = (int)tabs.size();
     ctx->max_ncell = 1;
     ctx->grids.clear();
-    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell}); }
+    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell, {t.guard[0], t.guard[1], t.guard[2], t.guard[3]}}); }
     ctx->lean_ok = true;       // every non-empty confidence interval must have a positive upper bound (sign encoding)
     for (auto& t : tabs)
         for (int k = 0; k < t.L; ++k)
@@ -202,6 +202,7 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.n_levels = ctx->L;
     A.cell_obase = ctx->grids[D.table].obase; A.cell_shift = ctx->grids[D.table].shift; A.cell_ncell = ctx->grids[D.table].ncell;
     A.cell_bytes = (int32_t)scan_smem_bytes(ctx);
+    for (int g = 0; g < 4; ++g) A.guard[g] = ctx->grids[D.table].guard[g];
     A.combo = D;
 }
 
@@ -253,7 +254,7 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
     const bool multiday = ctx->n_lr > 1;
     const bool wide = ctx->L > 32;
     const bool lean = ctx->lean_ok && !tiny && !ctx->force_v1;
-    const size_t lean_smem = lean_smem_bytes((int)smem, ctx->L);
+    const size_t lean_smem = lean_smem_bytes(ctx->L);
     const dim3 lean_grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(((paths + 31) / 32 + kLeanWarps - 1) / kLeanWarps,
                                                                             (int64_t)ctx->sm_count * kLeanBlocksPerSM)), 1, 1);
 #define LEAN3(MDv, HLv, PARv, Wv, SLv)                                                        \

@@ -27,29 +27,54 @@ constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kTouchStride = kLeanThreads + 4;      // bytes per level row; stride/4 is odd, so level rows rotate over the banks
 constexpr int kNoCool = 0x7fffffff;
 
-__host__ __device__ inline int lean_lpad(int L) { return L > 32 ? 64 : 32; }
-__host__ __device__ inline size_t lean_smem_bytes(int cell_bytes, int L) {
-    return (size_t)cell_bytes + (size_t)lean_lpad(L) * 2 * 16 * sizeof(float4) + (size_t)lean_lpad(L) * kTouchStride;
-}
-
-struct LeanTables {
-    const float4* gate;      // [level][side][tc]: {lo, +-hi, exit-low threshold, exit-high threshold}
-    uint8_t* touch;          // [level][kTouchStride]
+// Dynamic shared memory of the lean kernels: ONE base address (a register) + compile-time offsets, read with
+// ld.shared [reg + imm].  (Static __shared__ symbols make ptxas rebuild the CTA's shared-window base from
+// SR_CgaCtaId at every use inside the divergent blocks: ~10 issue slots per step in the first version.)
+template <int LPAD>
+struct LeanLayout {
+    static constexpr int kCell = 0;                                  // uint8 [kMaxCells]
+    static constexpr int kGate = kCell + kMaxCells;                  // float4 [LPAD][2][16]: {lo, +-hi, exit-low, exit-high}
+    static constexpr int kTouch = kGate + LPAD * 32 * 16;            // uint8 [LPAD][kTouchStride]
+    static constexpr int kWin = kTouch + LPAD * kTouchStride;        // float2 [LPAD]: contact window {wlo, whi}
+    static constexpr int kCand = kWin + LPAD * 8;                    // uint64 [LPAD]: levels whose window overlaps
+    static constexpr int kPrice = kCand + LPAD * 8;                  // double [LPAD]
+    static constexpr int kMix = kPrice + LPAD * 8;                   // {float bound, uint32 lo | hi << 8} [kMaxMixed]
+    static constexpr int kEnd = kMix + kMaxMixed * 8;
+    static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kWin % 8 == 0 && kMix % 8 == 0, "alignment");
 };
+inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
 
-// per-CTA: gate[(k*2+side)*16+tc] from the exact confidence intervals, the overtouch limit and (single day, AND
-// mode) the host-evaluated logistic mask.  Encoding: in range & y>0 -> OK; in range & y<0 -> ML_CONF_LOW;
-// out of range & y = -inf -> LEVEL_OVERTOUCHED (x = +inf: never in range); out of range otherwise -> CONF_LOW.  z, w = the exit thresholds an entry at
-// this (level, side) arms (M:1669-1674; float64 stop/target rounded toward the inside of the band, as block_setup).
-template <bool MULTIDAY>
-__device__ inline LeanTables lean_setup(const ScanArgs& A) {
-    float4* gate = reinterpret_cast<float4*>(g_cell + A.cell_bytes);
-    const int lpad = lean_lpad(A.n_levels);
-    uint8_t* touch = reinterpret_cast<uint8_t*>(gate + lpad * 32);
+#define QMMX_LDS(type, ptxty, cons)                                                                         \
+    template <int OFF> __device__ __forceinline__ type lds_##ptxty(uint32_t a) {                            \
+        type v; asm("ld.shared." #ptxty " %0, [%1+%2];" : "=" cons(v) : "r"(a), "n"(OFF)); return v; }
+QMMX_LDS(uint32_t, u8, "r")
+QMMX_LDS(uint32_t, u32, "r")
+QMMX_LDS(unsigned long long, u64, "l")
+QMMX_LDS(double, f64, "d")
+#undef QMMX_LDS
+template <int OFF> __device__ __forceinline__ float2 lds_f2(uint32_t a) {
+    float2 v; asm("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(a), "n"(OFF)); return v; }
+template <int OFF> __device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 v; asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a), "n"(OFF)); return v; }
+// touch bytes are read-modify-written by their own thread only; volatile keeps the asm statements in program order
+__device__ __forceinline__ uint32_t touch_ld(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void touch_st(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v)); }
+
+// per-CTA tables.  gate[(k*2+side)*16+tc] from the exact confidence intervals, the overtouch limit and (single day,
+// AND mode) the host-evaluated logistic mask.  Encoding: in range & y>0 -> OK; in range & y<0 -> ML_CONF_LOW;
+// out of range & y = -inf -> LEVEL_OVERTOUCHED (x = +inf: never in range); out of range otherwise -> CONF_LOW.
+// z, w = the exit thresholds an entry at this (level, side) arms (M:1669-1674; float64 stop/target rounded toward
+// the inside of the band, as block_setup does for the first-generation kernel).
+// The sign encoding needs every non-empty confidence interval to have a positive upper bound (prices are
+// positive) -- checked on the host before a lean kernel is chosen (qmmx_mc.cu lean_ok).
+template <bool MULTIDAY, int LPAD>
+__device__ inline void lean_setup(const ScanArgs& A) {
+    typedef LeanLayout<LPAD> Y;
     const DevTables* __restrict__ T = A.tables;
     const float inf = __int_as_float(0x7f800000);
     const bool fold_ml = !MULTIDAY && A.mlmask && !(A.combo.flags & QMMX_F_USE_BLEND);
-    for (int t = threadIdx.x; t < lpad * 32; t += blockDim.x) {
+    float4* gate = reinterpret_cast<float4*>(g_cell + Y::kGate);
+    for (int t = threadIdx.x; t < LPAD * 32; t += blockDim.x) {
         const int k = t >> 5, side = (t >> 4) & 1, tc = t & 15;
         float4 g = make_float4(inf, inf, -inf, inf);            // never in range, CONF_LOW
         if (k < A.n_levels) {
@@ -64,91 +89,106 @@ __device__ inline LeanTables lean_setup(const ScanArgs& A) {
         }
         gate[t] = g;
     }
-    LeanTables S; S.gate = gate; S.touch = touch;
-    return S;
+    float2* win = reinterpret_cast<float2*>(g_cell + Y::kWin);
+    unsigned long long* cand = reinterpret_cast<unsigned long long*>(g_cell + Y::kCand);
+    double* price = reinterpret_cast<double*>(g_cell + Y::kPrice);
+    for (int k = threadIdx.x; k < LPAD; k += blockDim.x) {
+        const bool in = k < A.n_levels;
+        win[k] = in ? make_float2(T->lev[k].wlo, T->lev[k].whi) : make_float2(inf, -inf);
+        cand[k] = in ? (((unsigned long long)T->lev[k].cand_hi << 32) | T->lev[k].cand_lo) : 0ull;
+        price[k] = in ? T->lev[k].price : 0.0;
+    }
+    uint2* mix = reinterpret_cast<uint2*>(g_cell + Y::kMix);
+    for (int m = threadIdx.x; m < kMaxMixed; m += blockDim.x) {
+        const bool in = m < T->nmixed;
+        mix[m] = in ? make_uint2((uint32_t)__float_as_int(T->mixb[m]), (uint32_t)T->mixlo[m] | ((uint32_t)T->mixhi[m] << 8))
+                    : make_uint2(0u, (uint32_t)kFar | ((uint32_t)kFar << 8));
+    }
 }
-
-// the sign encoding needs every finite upper bound of a confidence interval to be positive (prices are)
-// -- checked on the host before this kernel is chosen (qmmx_mc.cu lean_ok).
 
 // SLOW = the blend gate or the OnlinePolicy gate is enabled (float64 slow paths compiled in)
 template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW>
 struct LeanEngine {
     typedef typename LatchType<WIDE>::T latch_t;
+    static constexpr int LPAD = WIDE ? 64 : 32;
+    typedef LeanLayout<LPAD> Y;
+    uint32_t sb, st;       // shared addresses: table base; this thread's column of touch bytes
     float prev, d;         // last price; last non-zero price change (0 = direction unknown, M:1529-1538)
     int cool;              // first step at which an entry may be evaluated; kNoCool while in a position
     float lo_thr, hi_thr;  // exit when low <= lo_thr or high >= hi_thr; (-inf, +inf) when flat
-    float entry;
-    int pos, entry_bar;    // level | side << 8
+    float entry_s;         // entry price, sign flipped for a short: pnl = (+-exit) - entry_s
+    uint32_t sgn;          // 0 long, 0x80000000 short
+    int pos, entry_bar;    // level | side << 8 (stale when flat)
     latch_t latch;
     uint32_t c_gate, c_ml, c_exit, c_span, c_dir;    // packed 16-bit tallies, as PathEngine
     double pnl, pnl2, mtm;
     int ntr; int64_t path;
-    uint8_t* tcol;         // this thread's column of touch bytes
 
-    __device__ __forceinline__ void reset(const LeanTables& S, int lpad, int64_t path_) {
+    __device__ __forceinline__ bool is_open() const { return cool == kNoCool; }
+
+    __device__ __forceinline__ void reset(uint32_t sb_, int64_t path_) {
         path = path_;
-        tcol = S.touch + threadIdx.x;
-        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry = 0.f; entry_bar = 0;
+        sb = sb_; st = sb_ + Y::kTouch + threadIdx.x;
+        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry_s = 0.f; sgn = 0u; entry_bar = 0;
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
         latch = 0; c_gate = c_ml = c_exit = c_span = c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
-        for (int k = 0; k < lpad; ++k) tcol[k * kTouchStride] = 0;
+#pragma unroll 8
+        for (int k = 0; k < LPAD; ++k) touch_st(st + k * kTouchStride, 0u);
     }
 
     // steps 0 .. j0-1 carry no direction (DIR_UNKNOWN, M:1538): j0 = index of the first close that differs from close[0]
-    __device__ __forceinline__ void prologue(const ScanArgs& A, float p0, int j0) {
-        prev = p0; cool = j0; c_dir = (uint32_t)j0;
-    }
+    __device__ __forceinline__ void prologue(float p0, int j0) { prev = p0; cool = j0; c_dir = (uint32_t)j0; }
+
+    __device__ __forceinline__ float entry_price() const { return __int_as_float(__float_as_int(entry_s) ^ sgn); }
 
     __device__ __forceinline__ void do_exit(const ScanArgs& A, float pf, bool hit_lo, bool hit_hi, int i) {
-        const int side = pos >> 8;
-        const bool is_stop = (side == 0) ? hit_lo : hit_hi;      // stop is tested first (M:2975-3010, M:3621-3636)
+        const bool is_short = sgn != 0u;
+        const bool is_stop = is_short ? hit_hi : hit_lo;         // stop is tested first (M:2975-3010, M:3621-3636)
         double tp;
         float exit_f = pf;
         if (!HL) {
-            const double diff = (double)pf - (double)entry;      // fp32 values, float64 difference (M:1926)
-            tp = side == 0 ? diff : -diff;
-        } else {
-            const double lp = g_S.cold[pos & 0xff].price;
+            // close exit (M:2979-3012): fp32 values, float64 difference (M:1926); a short negates both operands (exact)
+            tp = (double)__int_as_float(__float_as_int(pf) ^ sgn) - (double)entry_s;
+        } else {                                                  // exit at the stop/target level itself (M:3636)
+            const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
             double exit_px;
-            if (side == 0) exit_px = is_stop ? lp - A.combo.sp : lp + A.combo.tp;
+            if (!is_short) exit_px = is_stop ? lp - A.combo.sp : lp + A.combo.tp;
             else exit_px = is_stop ? lp + A.combo.sp : lp - A.combo.tp;
-            const double e = (double)entry;
-            tp = (side == 0) ? (exit_px - e) : (e - exit_px);
+            const double e = (double)entry_price();
+            tp = is_short ? (e - exit_px) : (exit_px - e);
             exit_f = (float)exit_px;
         }
         pnl += tp; pnl2 += tp * tp;
-        cool = i + A.combo.cool_steps;                            // M:2982, M:269-270
-        const int ncool = max(min(cool, A.steps) - i - 1, 0);     // steps coded COOLDOWN (M:1516)
+        const int ncool = max(min(A.combo.cool_steps, A.steps - i) - 1, 0);   // steps coded COOLDOWN (M:1516)
         c_span += (uint32_t)(i - entry_bar) + ((uint32_t)ncool << 16);
+        cool = i + A.combo.cool_steps;                            // M:2982, M:269-270
         if (tp > 0) c_ml += 1u << 16;                             // label, M:1936
         c_exit += is_stop ? 1u : (1u << 16);
-        if (PARITY) record_trade(&A, path, ntr, entry_bar, i, side, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET, pos & 0xff, entry, exit_f, (float)tp);
+        if (PARITY) record_trade(&A, path, ntr, entry_bar, i, is_short ? 1 : 0, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET,
+                                 pos & 0xff, entry_price(), exit_f, (float)tp);
         ++ntr;
-        pos = -1;
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
     }
 
-    __device__ __forceinline__ int contact(const ScanArgs& A, const LeanTables& S, int k, float pf, int i, int day_off) {
+    __device__ __forceinline__ int contact(const ScanArgs& A, int k, float pf, int i, int day_off) {
         const int side = d < 0.f ? 1 : 0;                         // M:1645: up -> long(0), down -> short(1)
         // latch + touch count (M:1562-1576)
-        latch_t bit, cand;
-        if (WIDE) {
-            bit = (latch_t)(1ull << k);
-            cand = (latch_t)(((unsigned long long)g_S.cand_hi[k] << 32) | g_S.cand_lo[k]);
-        } else {
-            bit = (latch_t)(1u << k);
-            cand = (latch_t)g_S.cand_lo[k];
-        }
+        const latch_t bit = (latch_t)1 << k;
+        const latch_t cand = WIDE ? (latch_t)lds_u64<Y::kCand>(sb + k * 8) : (latch_t)lds_u32<Y::kCand>(sb + k * 8);
         const bool isnew = (latch & bit) == 0;
-        const latch_t keep = latch & cand;
+        latch_t keep = latch & cand;
         latch = bit;
-        if (keep) latch |= (latch_t)keep_neighbours(pf, (uint32_t)keep, WIDE ? (uint32_t)((unsigned long long)keep >> 32) : 0u);
-        uint8_t* tp = tcol + k * kTouchStride;
-        int tc = *tp;
-        if (isnew) { tc = min(tc + 1, 15); *tp = (uint8_t)tc; }
-        const float4 g = S.gate[(k * 2 + side) * 16 + tc];
+        while (keep) {      // a latched neighbour stays latched only while p is still inside its own window (M:1572-1576)
+            const int j = WIDE ? __ffsll((long long)keep) - 1 : __ffs((int)keep) - 1;
+            keep &= keep - 1;
+            const float2 w = lds_f2<Y::kWin>(sb + j * 8);
+            if (pf >= w.x && pf <= w.y) latch |= (latch_t)1 << j;
+        }
+        const uint32_t ta = st + k * kTouchStride;
+        uint32_t tc = touch_ld(ta);
+        if (isnew) { tc = min(tc + 1u, 15u); touch_st(ta, tc); }
+        const float4 g = lds_f4<Y::kGate>(sb + (((k * 2 + side) * 16 + (int)tc) << 4));
         const bool neg = __float_as_int(g.y) < 0;
         if (!(pf >= g.x && pf <= fabsf(g.y))) {
             const bool over = __float_as_int(g.y) == (int)0xff800000;   // y = -inf marks tc >= overtouch limit
@@ -157,22 +197,24 @@ struct LeanEngine {
         }
         if (neg) { c_ml += 1u; return QMMX_ML_CONF_LOW; }         // M:1745-1755 (single day, AND mode)
         if (SLOW && (A.combo.flags & QMMX_F_USE_BLEND)) {         // M:1730-1742
-            if (blend_fails(&A, k, pf, tc, side, day_off)) return QMMX_COMBINED_LOW;
+            if (blend_fails(&A, k, pf, (int)tc, side, day_off)) return QMMX_COMBINED_LOW;
         } else if (MULTIDAY && A.mlmask) {
             const uint32_t m = __ldg(&A.mlmask[day_off + k]);
-            if ((m >> (side * 16 + tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
+            if ((m >> (side * 16 + (int)tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         if (SLOW && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {   // OnlinePolicy gate of the live loop (M:3046-3109)
             if (!policy_passes(&A, k, pf, side, i)) return QMMX_ONLINE_POLICY;
         }
         lo_thr = g.z; hi_thr = g.w;                               // M:1669-1674
         pos = k | (side << 8);
-        entry = pf; entry_bar = i;
+        sgn = (uint32_t)side << 31;
+        entry_s = __int_as_float(__float_as_int(pf) ^ sgn);
+        entry_bar = i;
         cool = kNoCool;
         return QMMX_OK_ENTRY;
     }
 
-    __device__ __forceinline__ void step(const ScanArgs& A, const LeanTables& S, float pf, float hh, float ll, int i, int day_off) {
+    __device__ __forceinline__ void step(const ScanArgs& A, float pf, float hh, float ll, int i, int day_off) {
         const bool elig = i >= cool;
         int code = QMMX_TOO_FAR;
         if (PARITY) code = (cool == kNoCool) ? QMMX_IN_POSITION : (elig ? QMMX_TOO_FAR : QMMX_COOLDOWN);
@@ -185,10 +227,19 @@ struct LeanEngine {
         if (PARITY && d == 0.f) code = QMMX_DIR_UNKNOWN;
         // nearest level within CONTACT_PROX (M:1543-1545): the cell byte is read by every lane, the branch is taken by few
         const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase) >> A.cell_shift, (uint32_t)(A.cell_ncell - 1));
-        uint32_t v = g_cell[c];
+        uint32_t v = lds_u8<Y::kCell>(sb + c);
         if (elig && v != kFar) {
-            if (v == kMixed) v = classify_zones(pf);
-            if (v != kFar) code = contact(A, S, (int)v, pf, i, day_off);
+            if (v >= kMixBase) {                                  // the cell straddles a zone boundary
+                if (v == kMixed) {                                // several boundaries, or an end cell (price left the grid)
+                    if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
+                    else v = classify_zones(pf);
+                } else {
+                    const float2 r = lds_f2<Y::kMix>(sb + (v - kMixBase) * 8);
+                    const uint32_t lohi = (uint32_t)__float_as_int(r.y);
+                    v = pf <= r.x ? (lohi & 0xffu) : (lohi >> 8);
+                }
+            }
+            if (v != kFar) code = contact(A, (int)v, pf, i, day_off);
         }
         if (PARITY && A.codes) {
             if (A.n_levels == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
@@ -197,12 +248,12 @@ struct LeanEngine {
     }
 
     __device__ __forceinline__ void finish(const ScanArgs& A) {
-        if (pos >= 0) {
-            const int side = pos >> 8;
-            const double e = (double)entry, last = (double)prev;
-            mtm = (side == 0) ? (last - e) : (e - last);
+        if (is_open()) {
+            const bool is_short = sgn != 0u;
+            const double e = (double)entry_price(), last = (double)prev;
+            mtm = is_short ? (e - last) : (last - e);
             c_span += (uint32_t)(A.steps - 1 - entry_bar);
-            if (PARITY) record_trade(&A, path, ntr, entry_bar, -1, side, QMMX_EXIT_OPEN, pos & 0xff, entry, prev, 0.0f);
+            if (PARITY) record_trade(&A, path, ntr, entry_bar, -1, is_short ? 1 : 0, QMMX_EXIT_OPEN, pos & 0xff, entry_price(), prev, 0.0f);
             ++ntr;
         }
         if (PARITY && A.tcounts) A.tcounts[path] = ntr;
@@ -217,7 +268,7 @@ struct LeanEngine {
 // HBM latency is ~0.8 us.
 template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, int U>
 __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW>& E, const ScanArgs& A,
-                                               const LeanTables& S, int64_t path) {
+                                               int64_t path) {
     const size_t pitch = (size_t)A.pitch;
     const float* pc = A.close + path;
     const float* ph = HL ? A.high + path : nullptr;
@@ -227,7 +278,7 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
         const float p0 = __ldg(pc);
         int j0 = 1;
         while (j0 < steps && __ldg(pc + (size_t)j0 * pitch) == p0) ++j0;
-        E.prologue(A, p0, j0);
+        E.prologue(p0, j0);
     }
     float c0[U], c1[U], h0[U], h1[U], l0[U], l1[U];
     const int nfull = steps / (2 * U);
@@ -248,7 +299,7 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
                 if (HL) { h1[u] = __ldg(ph); l1[u] = __ldg(pl); ph += pitch; pl += pitch; }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(A, S, c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u, day.at(A, i + u));
+            for (int u = 0; u < U; ++u) E.step(A, c0[u], HL ? h0[u] : 0.f, HL ? l0[u] : 0.f, i + u, day.at(A, i + u));
             if (n + 1 < nfull) {
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
@@ -257,7 +308,7 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
                 }
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u) E.step(A, S, c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u, day.at(A, i + U + u));
+            for (int u = 0; u < U; ++u) E.step(A, c1[u], HL ? h1[u] : 0.f, HL ? l1[u] : 0.f, i + U + u, day.at(A, i + U + u));
         }
     }
 #pragma unroll 1
@@ -265,26 +316,27 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
         const float c = __ldg(pc); pc += pitch;
         float h = 0.f, l = 0.f;
         if (HL) { h = __ldg(ph); l = __ldg(pl); ph += pitch; pl += pitch; }
-        E.step(A, S, c, h, l, i, day.at(A, i));
+        E.step(A, c, h, l, i, day.at(A, i));
     }
 }
 
 template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kernel(const __grid_constant__ ScanArgs A) {
     block_setup(A);
-    const LeanTables S = lean_setup<MULTIDAY>(A);
+    lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
     LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int lpad = lean_lpad(A.n_levels);
+    // through a shuffle so that ptxas keeps the base in a register instead of rebuilding it from SR_CgaCtaId at every use
+    const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
     for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
-        E.reset(S, lpad, path);
-        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, 2>(E, A, S, path); E.finish(A); }
+        E.reset(sb, path);
+        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, 2>(E, A, path); E.finish(A); }
         __syncwarp();
-        accumulate_path(active, E);
+        warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.is_open());
     }
     __syncthreads();
     block_flush_agg(A.flat, A.steps);

@@ -20,7 +20,9 @@ constexpr int kMaxZones = 272;
 constexpr int kMaxTables = 8;           // distinct (CONTACT_PROX, Q_MIN_PROB) pairs across the combos of one run
 constexpr int kMaxDays = 64;
 constexpr uint8_t kFar = 0xFF;
-constexpr uint8_t kMixed = 0xFE;
+constexpr uint8_t kMixed = 0xFE;          // cell straddles two or more zone boundaries: exact zone search
+constexpr uint8_t kMixBase = 0x40;        // kMixBase + m: cell straddles exactly ONE boundary, record m resolves it
+constexpr int kMaxMixed = kMixed - kMixBase;
 
 constexpr uint32_t kLvSolid = 1u, kLvConfl06 = 2u, kLvConfl015 = 4u;
 
@@ -34,14 +36,22 @@ struct DevLevel {                       // 64 bytes
 };
 static_assert(sizeof(DevLevel) == 64, "DevLevel layout");
 
-struct DevTables {
+struct alignas(16) DevTables {          // arrays of DevTables: cell[] is copied with 16-byte loads
     int32_t L, Z, ncell, shift;         // cell = clamp((bits(p) - obase) >> shift, 0, ncell-1)
     int32_t obase, pad0, pad1, pad2;
     DevLevel lev[kMaxLevels];
     float zhi[kMaxZones];               // inclusive fp32 upper bound of zone z; zone z = (zhi[z-1], zhi[z]]
     uint8_t zlev[kMaxZones];            // level touched in zone z, or kFar
-    uint8_t cell[kMaxCells];            // level index / kFar / kMixed per grid cell
+    uint8_t cell[kMaxCells];            // level index / kFar / kMixBase + m / kMixed per grid cell
+    // single-boundary cells: p <= mixb[m] ? mixlo[m] : mixhi[m]  (level index or kFar)
+    int32_t nmixed, pad3[3];
+    // far zones adjoining the grid (prices that leave the grid land in an end cell): guard[0] < p <= guard[1] or
+    // guard[2] < p <= guard[3]  =>  far, without the zone search; an empty interval is (+inf, -inf]
+    float guard[4];
+    float mixb[kMaxMixed];
+    uint8_t mixlo[kMaxMixed], mixhi[kMaxMixed];
 };
+static_assert(sizeof(DevTables) % 16 == 0, "DevTables stride");
 
 struct DevCombo {                       // one parameter combination (qmmx_params, preprocessed)
     double sp, tp, qmin, prox, pmax, wr, wm;

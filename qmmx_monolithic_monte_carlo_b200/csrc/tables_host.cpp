@@ -212,7 +212,10 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
             for (int j = i; j < L; ++j) { if (ord_of(price[order[j]] + prox) - a <= cap) ++n; else break; }
             if (n > best_n) { best_n = n; best = i; }
         }
-        o_lo = std::max<int64_t>(0, ord_of(price[order[best]] - prox) - margin);
+        // centre the cluster in the grid: the spare cells on both sides absorb price excursions
+        const int64_t c_lo = ord_of(price[order[best]] - prox), c_hi = ord_of(price[order[best + best_n - 1]] + prox);
+        const int64_t spare = std::max<int64_t>(0, ((int64_t)kMaxCells << shift) - (c_hi - c_lo) - 2 * margin);
+        o_lo = std::max<int64_t>(0, c_lo - margin - spare / 2);
         o_hi = std::min<int64_t>(o_lo + ((int64_t)kMaxCells << shift) - 1, omax);
     }
     const int ncell = (int)std::min<int64_t>(kMaxCells, ((o_hi - o_lo) >> shift) + 1);
@@ -230,7 +233,26 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
         const int64_t c_lo = (c == 0) ? omin : o_lo + ((int64_t)c << shift);
         const int64_t c_hi = (c == ncell - 1) ? omax : o_lo + (((int64_t)c + 1) << shift) - 1;
         const int z0 = zone_index(std::min(c_lo, omax)), z1 = zone_index(std::min(c_hi, omax));
-        T->cell[c] = (z0 == z1) ? T->zlev[z0] : kMixed;
+        if (z0 == z1) T->cell[c] = T->zlev[z0];
+        else if (z1 == z0 + 1 && T->nmixed < kMaxMixed) {
+            const int m = T->nmixed++;
+            T->mixb[m] = T->zhi[z0]; T->mixlo[m] = T->zlev[z0]; T->mixhi[m] = T->zlev[z1];
+            T->cell[c] = (uint8_t)(kMixBase + m);
+        } else T->cell[c] = kMixed;
+    }
+    // guard intervals: the far zones that contain the ordinals just outside the grid
+    {
+        const float finf2 = INFINITY;
+        T->guard[0] = finf2; T->guard[1] = -finf2; T->guard[2] = finf2; T->guard[3] = -finf2;
+        const int64_t below = o_lo - 1, above = o_lo + ((int64_t)ncell << shift);
+        if (below >= omin) {
+            const int z = zone_index(below);
+            if (T->zlev[z] == kFar) { T->guard[0] = z > 0 ? T->zhi[z - 1] : -finf2; T->guard[1] = T->zhi[z]; }
+        }
+        if (above <= omax) {
+            const int z = zone_index(above);
+            if (T->zlev[z] == kFar) { T->guard[2] = z > 0 ? T->zhi[z - 1] : -finf2; T->guard[3] = T->zhi[z]; }
+        }
     }
     // scan_lean.cuh clamps with one unsigned min, which sends prices below the grid to the LAST cell: both end cells
     // must then resolve the same way (both far in the full-coverage case; else through the exact zone search)
@@ -293,7 +315,12 @@ int classify_tables(const DevTables* T, float p) {
     int32_t bits;
     std::memcpy(&bits, &p, 4);
     uint8_t v = T->cell[cell_of_bits(bits, T->obase, T->shift, T->ncell)];
-    if (v == kMixed) {
+    if (v >= kMixBase && v < kMixed) {
+        const int m = v - kMixBase;
+        v = p <= T->mixb[m] ? T->mixlo[m] : T->mixhi[m];
+    } else if (v == kMixed && ((p > T->guard[0] && p <= T->guard[1]) || (p > T->guard[2] && p <= T->guard[3]))) {
+        v = kFar;
+    } else if (v == kMixed) {
         int a = 0, b = T->Z - 1;
         while (a < b) {
             const int m = (a + b) >> 1;
