@@ -29,6 +29,9 @@ from qmmx_monolithic_monte_carlo_b200 import abi, fixtures as F  # noqa: E402
 METRIC = "simulated path-steps/sec (390-step paths)"
 UNIT = "path-steps/s"
 STEPS_PER_PATH = 390
+# DRAM bytes of one lean_scan_kernel launch over 1M x 390 fp32 closes, from the committed ncu capture
+# (1.560333 GB read + 4.03 MB written; algorithmic bytes are 1.560000 GB: nothing is re-read)
+NCU_TRAFFIC_BYTES = 1.560333e9 + 4.028e6
 
 
 def workload(name: str):
@@ -394,7 +397,10 @@ def main():
                        "l2": "inputs (1.56 GB per GPU) larger than the 126 MB L2; no flush needed",
                        "parallelism": f"paths sharded over {world} GPU(s); one NCCL all-reduce of the aggregate vector"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "scan_kernel<false,false,false>", "kernel_ms": k_ms,
+                         "traffic": NCU_TRAFFIC_BYTES if paths == 1_000_000 else None,
+                         "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch "
+                                           "(profiles/r1_ncu_lean_scan_close_summary.txt)",
+                         "kernel": "lean_scan_kernel<MULTIDAY=0,HL=0,PARITY=0,WIDE=0,SLOW=0>", "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
             "clocks": clocks, "gpu_launches": int(launches),
             "result_check": {"n_trades": res.n_trades, "n_wins": res.n_wins, "sum_pnl": res.sum_pnl},

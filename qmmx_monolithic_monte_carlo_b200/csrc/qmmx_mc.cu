@@ -703,6 +703,9 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     if ((rc = init_flat(ctx)) != 0) return rc;
     const bool wide = ctx->L > 32, hl = gbm->sub_steps == 4;
+    const size_t lean_smem = lean_smem_bytes(ctx->L);
+    const dim3 lean_grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(((paths + 31) / 32 + kLeanWarps - 1) / kLeanWarps,
+                                                                            (int64_t)ctx->sm_count * kLeanBlocksPerSM)), 1, 1);
     for (int c = 0; c < (int)ctx->params.size() && paths > 0 && steps > 0; ++c) {
         ScanArgs A;
         fill_args(ctx, A, c, nullptr, nullptr, nullptr, 0, paths, steps);
@@ -711,8 +714,20 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
             if ((rc = set_smem_attr(ctx, fused_gbm_kernel<HLv, Wv>, smem)) != 0) return rc;   \
             fused_gbm_kernel<HLv, Wv><<<grid, kThreads, smem, ctx->stream>>>(A, g);           \
         } while (0)
-        if (hl) { if (wide) FUSED(true, true); else FUSED(true, false); }
+#define LFUSED(HLv, Wv, SLv)                                                                  \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, lean_fused_gbm_kernel<HLv, Wv, SLv>, lean_smem)) != 0) return rc;   \
+            lean_fused_gbm_kernel<HLv, Wv, SLv><<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A, g);  \
+        } while (0)
+#define LFUSED2(HLv, Wv) do { if (slow) LFUSED(HLv, Wv, true); else LFUSED(HLv, Wv, false); } while (0)
+        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
+        if (ctx->lean_ok && !ctx->force_v1) {
+            if (hl) { if (wide) LFUSED2(true, true); else LFUSED2(true, false); }
+            else { if (wide) LFUSED2(false, true); else LFUSED2(false, false); }
+        } else if (hl) { if (wide) FUSED(true, true); else FUSED(true, false); }
         else { if (wide) FUSED(false, true); else FUSED(false, false); }
+#undef LFUSED2
+#undef LFUSED
 #undef FUSED
         ctx->launches++;
         CK(cudaGetLastError());

@@ -342,4 +342,80 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
     block_flush_agg(A.flat, A.steps);
 }
 
+// ---- fused GBM generate + scan on the lean engine: bars live in registers only (Philox4x32-10 + Box-Muller) ----------
+// The DIR_UNKNOWN prefix needs close[0] and the index of the first differing close before the walk starts: the
+// first Philox group(s) are generated twice (one extra group per path, ~1 % of the generator work).
+template <bool HL, bool WIDE, bool SLOW>
+__global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
+    block_setup(A);
+    lean_setup<true, WIDE ? 64 : 32>(A);
+    __syncthreads();
+    LeanEngine<true, HL, false, WIDE, SLOW> E;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
+    const int64_t ntiles = (A.paths + 31) / 32;
+    const int steps = A.steps;
+    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+        const int64_t path = tile * 32 + lane;
+        const bool active = path < A.paths;
+        E.reset(sb, path);
+        if (active) {
+            const uint64_t gid = g.path_offset + (uint64_t)path;
+            float z[4];
+            {   // prologue: close[0] and the first step whose close differs from it
+                float P = g.s0, p0 = 0.f;
+                int j0 = steps;
+                for (int i = 0; i < steps && j0 == steps; i += HL ? 1 : 4) {
+                    gbm_normals(g, gid, (uint32_t)(HL ? i : (i >> 2)), z);
+                    if (HL) {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) P = gbm_advance(g, P, z[u]);
+                        const float c = g.cents ? round_cents(P) : P;
+                        if (i == 0) p0 = c; else if (c != p0) j0 = i;
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (i + u < steps && j0 == steps) {
+                                P = gbm_advance(g, P, z[u]);
+                                const float c = g.cents ? round_cents(P) : P;
+                                if (i + u == 0) p0 = c; else if (c != p0) j0 = i + u;
+                            }
+                        }
+                    }
+                }
+                E.prologue(p0, j0);
+            }
+            float P = g.s0;
+            DayTracker<true> day;
+            day.init(A);
+            if (!HL) {
+                for (int i = 0; i < steps; i += 4) {
+                    gbm_normals(g, gid, (uint32_t)(i >> 2), z);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (i + u < steps) {
+                            P = gbm_advance(g, P, z[u]);
+                            E.step(A, g.cents ? round_cents(P) : P, 0.f, 0.f, i + u, day.at(A, i + u));
+                        }
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int i = 0; i < steps; ++i) {
+                    gbm_normals(g, gid, (uint32_t)i, z);
+                    float hi = P, lo = P;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { P = gbm_advance(g, P, z[u]); hi = fmaxf(hi, P); lo = fminf(lo, P); }
+                    E.step(A, g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i, day.at(A, i));
+                }
+            }
+            E.finish(A);
+        }
+        __syncwarp();
+        warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.is_open());
+    }
+    __syncthreads();
+    block_flush_agg(A.flat, A.steps);
+}
+
 }  // namespace qmmx
