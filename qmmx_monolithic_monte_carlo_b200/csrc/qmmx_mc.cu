@@ -50,6 +50,7 @@ struct qmmx_ctx {
     // staging for qmmx_run_scan_host
     float* d_stage[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
     int64_t stage_elems = 0;
+    float* d_ratios = nullptr; size_t ratios_cap = 0;     // bootstrap return ratios (qmmx_gen_bootstrap)
     bool ran = false;
 };
 
@@ -77,6 +78,8 @@ void free_bars(qmmx_ctx* c) {
 }
 
 int alloc_bars(qmmx_ctx* ctx, int64_t paths, int32_t steps, bool hl) {
+    // same shape as the resident buffers: reuse them (a generator called once per step must not pay cudaMalloc/cudaFree)
+    if (ctx->own_bars && ctx->d_close && ctx->paths == paths && ctx->steps == steps && (ctx->d_high != nullptr) == hl) return QMMX_OK;
     free_bars(ctx);
     const int64_t pitch = round_up(std::max<int64_t>(paths, 1), 32);
     const size_t bytes = (size_t)pitch * (size_t)std::max(steps, 1) * sizeof(float);
@@ -393,7 +396,7 @@ int qmmx_destroy(qmmx_ctx* ctx) {
     free_bars(ctx);
     for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
     cudaFree(ctx->d_tables); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
-    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat);
+    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
     cudaStreamDestroy(ctx->own_stream); cudaStreamDestroy(ctx->copy_stream);
@@ -561,8 +564,14 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
         ratios[nret + t - 1] = window_ohlc[4 * t + 2] / pc;
         ratios[2 * nret + t - 1] = window_ohlc[4 * t + 3] / pc;
     }
-    float* d_r = nullptr;
-    CK(cudaMalloc(&d_r, ratios.size() * 4));
+    if (ctx->ratios_cap < ratios.size()) {
+        if (ctx->d_ratios) cudaFree(ctx->d_ratios);
+        ctx->d_ratios = nullptr; ctx->ratios_cap = 0;
+        CK(cudaMalloc(&ctx->d_ratios, ratios.size() * 4));
+        ctx->ratios_cap = ratios.size();
+    }
+    float* d_r = ctx->d_ratios;
+    // pageable source: the runtime stages the copy before returning, so `ratios` may go out of scope
     cudaError_t e = cudaMemcpyAsync(d_r, ratios.data(), ratios.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) {
         BootDev g;
@@ -574,9 +583,7 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
         ctx->launches++;
         e = cudaGetLastError();
         cudaEventRecord(ctx->ev1, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     }
-    cudaFree(d_r);
     if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("gen_bootstrap: ") + cudaGetErrorString(e));
     ctx->ran = true;
     return QMMX_OK;
@@ -714,12 +721,17 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
             if ((rc = set_smem_attr(ctx, fused_gbm_kernel<HLv, Wv>, smem)) != 0) return rc;   \
             fused_gbm_kernel<HLv, Wv><<<grid, kThreads, smem, ctx->stream>>>(A, g);           \
         } while (0)
-#define LFUSED(HLv, Wv, SLv)                                                                  \
+#define LFUSED(MDv, HLv, Wv, SLv)                                                             \
         do {                                                                                  \
-            if ((rc = set_smem_attr(ctx, lean_fused_gbm_kernel<HLv, Wv, SLv>, lean_smem)) != 0) return rc;   \
-            lean_fused_gbm_kernel<HLv, Wv, SLv><<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A, g);  \
+            if ((rc = set_smem_attr(ctx, lean_fused_gbm_kernel<MDv, HLv, Wv, SLv>, lean_smem)) != 0) return rc;   \
+            lean_fused_gbm_kernel<MDv, HLv, Wv, SLv><<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A, g);  \
         } while (0)
-#define LFUSED2(HLv, Wv) do { if (slow) LFUSED(HLv, Wv, true); else LFUSED(HLv, Wv, false); } while (0)
+#define LFUSED2(HLv, Wv)                                                                      \
+        do {                                                                                  \
+            if (multiday) { if (slow) LFUSED(true, HLv, Wv, true); else LFUSED(true, HLv, Wv, false); }   \
+            else { if (slow) LFUSED(false, HLv, Wv, true); else LFUSED(false, HLv, Wv, false); }          \
+        } while (0)
+        const bool multiday = ctx->n_lr > 1;
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
         if (ctx->lean_ok && !ctx->force_v1) {
             if (hl) { if (wide) LFUSED2(true, true); else LFUSED2(true, false); }

@@ -26,6 +26,8 @@ constexpr int kLeanBlocksPerSM = 2;
 constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kTouchStride = kLeanThreads + 4;      // bytes per level row; stride/4 is odd, so level rows rotate over the banks
 constexpr int kNoCool = 0x7fffffff;
+constexpr int kSmemDays = 16;         // per-day logistic masks of up to this many days are staged in shared memory
+static_assert(kMaxLevels == 64, "DayTracker offsets are day * 64 (day_off >> 6 below)");
 
 // Dynamic shared memory of the lean kernels: ONE base address (a register) + compile-time offsets, read with
 // ld.shared [reg + imm].  (Static __shared__ symbols make ptxas rebuild the CTA's shared-window base from
@@ -39,7 +41,8 @@ struct LeanLayout {
     static constexpr int kCand = kWin + LPAD * 8;                    // uint64 [LPAD]: levels whose window overlaps
     static constexpr int kPrice = kCand + LPAD * 8;                  // double [LPAD]
     static constexpr int kMix = kPrice + LPAD * 8;                   // {float bound, uint32 lo | hi << 8} [kMaxMixed]
-    static constexpr int kEnd = kMix + kMaxMixed * 8;
+    static constexpr int kMask = kMix + kMaxMixed * 8;               // uint32 [kSmemDays][LPAD]: per-day logistic masks (MULTIDAY)
+    static constexpr int kEnd = kMask + kSmemDays * LPAD * 4;
     static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kWin % 8 == 0 && kMix % 8 == 0, "alignment");
 };
 inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
@@ -97,6 +100,10 @@ __device__ inline void lean_setup(const ScanArgs& A) {
         win[k] = in ? make_float2(T->lev[k].wlo, T->lev[k].whi) : make_float2(inf, -inf);
         cand[k] = in ? (((unsigned long long)T->lev[k].cand_hi << 32) | T->lev[k].cand_lo) : 0ull;
         price[k] = in ? T->lev[k].price : 0.0;
+    }
+    if (MULTIDAY && A.mlmask && A.n_days <= kSmemDays) {
+        uint32_t* mk = reinterpret_cast<uint32_t*>(g_cell + Y::kMask);
+        for (int t = threadIdx.x; t < A.n_days * LPAD; t += blockDim.x) mk[t] = A.mlmask[(t / LPAD) * kMaxLevels + (t % LPAD)];
     }
     uint2* mix = reinterpret_cast<uint2*>(g_cell + Y::kMix);
     for (int m = threadIdx.x; m < kMaxMixed; m += blockDim.x) {
@@ -199,7 +206,9 @@ struct LeanEngine {
         if (SLOW && (A.combo.flags & QMMX_F_USE_BLEND)) {         // M:1730-1742
             if (blend_fails(&A, k, pf, (int)tc, side, day_off)) return QMMX_COMBINED_LOW;
         } else if (MULTIDAY && A.mlmask) {
-            const uint32_t m = __ldg(&A.mlmask[day_off + k]);
+            // day_off = day * kMaxLevels (DayTracker); masks of short horizons sit in shared memory
+            const uint32_t m = A.n_days <= kSmemDays ? lds_u32<Y::kMask>(sb + ((day_off >> 6) * LPAD + k) * 4)
+                                                     : __ldg(&A.mlmask[day_off + k]);
             if ((m >> (side * 16 + (int)tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         if (SLOW && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {   // OnlinePolicy gate of the live loop (M:3046-3109)
@@ -345,12 +354,12 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
 // ---- fused GBM generate + scan on the lean engine: bars live in registers only (Philox4x32-10 + Box-Muller) ----------
 // The DIR_UNKNOWN prefix needs close[0] and the index of the first differing close before the walk starts: the
 // first Philox group(s) are generated twice (one extra group per path, ~1 % of the generator work).
-template <bool HL, bool WIDE, bool SLOW>
+template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
     block_setup(A);
-    lean_setup<true, WIDE ? 64 : 32>(A);
+    lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
-    LeanEngine<true, HL, false, WIDE, SLOW> E;
+    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
@@ -386,7 +395,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm
                 E.prologue(p0, j0);
             }
             float P = g.s0;
-            DayTracker<true> day;
+            DayTracker<MULTIDAY> day;
             day.init(A);
             if (!HL) {
                 for (int i = 0; i < steps; i += 4) {

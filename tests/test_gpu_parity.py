@@ -415,3 +415,36 @@ def test_gpu_full_size_properties(eng):
     eng.gen_gbm(11, 0, P, T, g)
     scan = eng.run_scan()[0].agg
     assert list(scan.entry_hist) == list(a.entry_hist) and list(scan.pnl_hist) == list(a.pnl_hist)
+
+
+@pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
+def test_gpu_lean_kernels_equal_first_generation(eng, hl, monkeypatch):
+    """The production (lean) scan and fused kernels against the first-generation lockstep kernels (QMMX_SCAN_V1=1,
+    read by qmmx_create) on the full C2 size: two independent implementations of the same engine, every integer
+    aggregate identical and the per-path trade records identical on a 64k-path slice."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=hl)
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    g = abi.make_gbm(sub_steps=4 if hl else 1)
+    P, T = 1_000_000, 390
+    monkeypatch.setenv("QMMX_SCAN_V1", "1")
+    v1 = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_SCAN_V1")
+    try:
+        out = []
+        for e in (eng, v1):
+            configure(e, price, solid, params, lr)
+            fused = e.run_fused_gbm(5, 0, P, T, g)[0].agg
+            e.gen_gbm(5, 0, P, T, g)
+            scan = e.run_scan()[0].agg
+            e.gen_gbm(5, 0, 65_536, T, g)
+            res, tr, cnt, _ = e.run_scan(trades=48, paths_steps=(T, 65_536))
+            out.append((fused, scan, res[0].agg, tr, cnt))
+        (f0, s0, a0, tr0, c0), (f1, s1, a1, tr1, c1) = out
+        assert_agg_equal(f0, f1)
+        assert_agg_equal(s0, s1)
+        assert_agg_equal(f0, s0)
+        assert_agg_equal(a0, a1)
+        assert_trades_equal(tr0, c0, tr1, c1)
+    finally:
+        v1.close()
