@@ -279,7 +279,9 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         const bool parity = par && c == 0;
         if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
-        if (lean) {
+        // the lean exit block assumes a single price cannot hit both thresholds: stop below / target above the level
+        const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
+        if (lean && band_ok) {
             if (!parity) { if (hl) LEAN(true, false); else LEAN(false, false); }
             else { if (hl) LEAN(true, true); else LEAN(false, true); }
         } else if (!parity) {
@@ -733,7 +735,7 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
         } while (0)
         const bool multiday = ctx->n_lr > 1;
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
-        if (ctx->lean_ok && !ctx->force_v1) {
+        if (ctx->lean_ok && !ctx->force_v1 && A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0) {
             if (hl) { if (wide) LFUSED2(true, true); else LFUSED2(true, false); }
             else { if (wide) LFUSED2(false, true); else LFUSED2(false, false); }
         } else if (hl) { if (wide) FUSED(true, true); else FUSED(true, false); }

@@ -125,9 +125,11 @@ struct LeanEngine {
     float lo_thr, hi_thr;  // exit when low <= lo_thr or high >= hi_thr; (-inf, +inf) when flat
     float entry_s;         // entry price, sign flipped for a short: pnl = (+-exit) - entry_s
     uint32_t sgn;          // 0 long, 0x80000000 short
-    int pos, entry_bar;    // level | side << 8 (stale when flat)
+    int pos, entry_bar;    // level | side << 8 (stale when flat); entry_bar is only read in PARITY mode
+    uint32_t inc_lo;       // c_exit increment of an exit through the LOW threshold: 1 (stop, long) or 0x10000 (target, short)
+    int a_inpos;           // sum of (exit bar - entry bar) = steps coded IN_POSITION (M:1508), kept as running -entry +exit
     latch_t latch;
-    uint32_t c_gate, c_ml, c_exit, c_span, c_dir;    // packed 16-bit tallies, as PathEngine
+    uint32_t c_gate, c_ml, c_exit, c_span, c_dir;    // packed 16-bit tallies, as PathEngine (c_span is built in finish)
     double pnl, pnl2, mtm;
     int ntr; int64_t path;
 
@@ -136,7 +138,7 @@ struct LeanEngine {
     __device__ __forceinline__ void reset(uint32_t sb_, int64_t path_) {
         path = path_;
         sb = sb_; st = sb_ + Y::kTouch + threadIdx.x;
-        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry_s = 0.f; sgn = 0u; entry_bar = 0;
+        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry_s = 0.f; sgn = 0u; entry_bar = 0; inc_lo = 1u; a_inpos = 0;
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
         latch = 0; c_gate = c_ml = c_exit = c_span = c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
@@ -154,9 +156,13 @@ struct LeanEngine {
         const bool is_stop = is_short ? hit_hi : hit_lo;         // stop is tested first (M:2975-3010, M:3621-3636)
         double tp;
         float exit_f = pf;
+        bool win;
         if (!HL) {
             // close exit (M:2979-3012): fp32 values, float64 difference (M:1926); a short negates both operands (exact)
-            tp = (double)__int_as_float(__float_as_int(pf) ^ sgn) - (double)entry_s;
+            const float xs = __int_as_float(__float_as_int(pf) ^ sgn);
+            tp = (double)xs - (double)entry_s;
+            win = xs > entry_s;                                   // pnl > 0 (label, M:1936), decided on the fp32 operands
+            c_exit += hit_lo ? inc_lo : (inc_lo ^ 0x10001u);      // exactly one threshold is hit by a single price
         } else {                                                  // exit at the stop/target level itself (M:3636)
             const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
             double exit_px;
@@ -165,13 +171,13 @@ struct LeanEngine {
             const double e = (double)entry_price();
             tp = is_short ? (e - exit_px) : (exit_px - e);
             exit_f = (float)exit_px;
+            win = tp > 0;
+            c_exit += is_stop ? 1u : (1u << 16);
         }
         pnl += tp; pnl2 += tp * tp;
-        const int ncool = max(min(A.combo.cool_steps, A.steps - i) - 1, 0);   // steps coded COOLDOWN (M:1516)
-        c_span += (uint32_t)(i - entry_bar) + ((uint32_t)ncool << 16);
-        cool = i + A.combo.cool_steps;                            // M:2982, M:269-270
-        if (tp > 0) c_ml += 1u << 16;                             // label, M:1936
-        c_exit += is_stop ? 1u : (1u << 16);
+        a_inpos += i;                                             // IN_POSITION steps of this trade: i - entry bar
+        cool = i + A.combo.cool_steps;                            // M:2982, M:269-270; COOLDOWN steps are counted in finish
+        if (win) c_ml += 1u << 16;
         if (PARITY) record_trade(&A, path, ntr, entry_bar, i, is_short ? 1 : 0, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET,
                                  pos & 0xff, entry_price(), exit_f, (float)tp);
         ++ntr;
@@ -218,7 +224,9 @@ struct LeanEngine {
         pos = k | (side << 8);
         sgn = (uint32_t)side << 31;
         entry_s = __int_as_float(__float_as_int(pf) ^ sgn);
-        entry_bar = i;
+        inc_lo = side ? 0x10000u : 1u;
+        a_inpos -= i;
+        if (PARITY) entry_bar = i;
         cool = kNoCool;
         return QMMX_OK_ENTRY;
     }
@@ -257,14 +265,20 @@ struct LeanEngine {
     }
 
     __device__ __forceinline__ void finish(const ScanArgs& A) {
+        // COOLDOWN steps (M:1516): every exit is followed by cool_steps - 1 of them, except that the last one may be cut
+        // by the end of the path (only the last: no entry can follow an exit whose cooldown outlasts the path)
+        const int n_exits = (int)((c_exit & 0xffffu) + (c_exit >> 16));
+        int n_cool = n_exits * max(A.combo.cool_steps - 1, 0);
+        if (!is_open() && n_exits > 0 && cool > A.steps) n_cool -= cool - A.steps;
         if (is_open()) {
             const bool is_short = sgn != 0u;
             const double e = (double)entry_price(), last = (double)prev;
             mtm = is_short ? (e - last) : (last - e);
-            c_span += (uint32_t)(A.steps - 1 - entry_bar);
+            a_inpos += A.steps - 1;
             if (PARITY) record_trade(&A, path, ntr, entry_bar, -1, is_short ? 1 : 0, QMMX_EXIT_OPEN, pos & 0xff, entry_price(), prev, 0.0f);
             ++ntr;
         }
+        c_span = (uint32_t)a_inpos | ((uint32_t)n_cool << 16);
         if (PARITY && A.tcounts) A.tcounts[path] = ntr;
         double fb = floor((pnl - A.hist_lo) * A.hist_inv_w);
         const int bin = fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
