@@ -14,6 +14,7 @@
  *   qmmx_set_lr          engine.model (sklearn LogisticRegression, 4 coef + intercept)  M:1401-1407, M:1454-1466
  *   qmmx_set_policy      app.policy.w_entry (OnlinePolicy go_long/go_short/skip, dim 7) M:296-331, M:2096-2104
  *   qmmx_upload_bars     engine.recent_bars = [{t,o,h,l,c}, ...]                        M:220-240, M:2430
+ *   qmmx_upload_volume   the "v" of those bars (read by _calc_volume_slope only)        M:1796-1811, M:1880
  *   qmmx_run_scan        evaluate_entry per tick + the live loop's exit block,
  *                        open_trade / close_trade pnl, set_cooldown                     M:1492-1771, M:2927-3016, M:3044-3115,
  *                                                                                       M:1888-1948, M:259-270
@@ -74,7 +75,7 @@ enum {
 enum { QMMX_EXIT_STOP = 0, QMMX_EXIT_TARGET, QMMX_EXIT_ESCALATE, QMMX_EXIT_OPEN };
 
 /* qmmx_params.flags */
-#define QMMX_F_ENABLE_VETO          (1u << 0)  /* ENABLE_VETO (inert without per-bar volume)       */
+#define QMMX_F_ENABLE_VETO          (1u << 0)  /* ENABLE_VETO (needs qmmx_upload_volume to ever fire) */
 #define QMMX_F_DISABLE_ML_GATE      (1u << 1)  /* DISABLE_ML_GATE                                  */
 #define QMMX_F_USE_BLEND            (1u << 2)  /* USE_BLEND                                        */
 #define QMMX_F_DISABLE_POLICY_GATE  (1u << 3)  /* DISABLE_POLICY_GATE (1 = OnlinePolicy bypassed)  */
@@ -191,6 +192,14 @@ int  qmmx_device_bars(qmmx_ctx* ctx, float** d_close, float** d_high, float** d_
 int  qmmx_pin_host(qmmx_ctx* ctx, void* ptr, size_t bytes);
 int  qmmx_unpin_host(qmmx_ctx* ctx, void* ptr);
 int  qmmx_download_bars(qmmx_ctx* ctx, float* close, float* high, float* low);
+/* per-bar volume of the resident bars ([step][path] fp32, same shape; NULL drops it).  Only the soft veto
+ * (QMMX_F_ENABLE_VETO: _calc_volume_slope over the last 6 bars, M:1796-1811, then _soft_veto, M:1773-1794) reads
+ * it; without volume the slope is 0 and the veto never fires, which is the reference on its own data. */
+int  qmmx_upload_volume(qmmx_ctx* ctx, const float* volume, int64_t paths, int32_t steps);
+int  qmmx_download_volume(qmmx_ctx* ctx, float* volume);
+/* volume of the window bars ([window_len] fp32, NULL clears): the next qmmx_gen_bootstrap with the same
+ * window_len also writes a volume plane (a resampled bar carries the volume of the window bar it came from) */
+int  qmmx_set_bootstrap_volume(qmmx_ctx* ctx, const float* window_volume, int32_t window_len);
 /* Philox4x32-10 generators, counter = (global path id, step group), key = seed: results do not
  * depend on how paths are split across GPUs.  path_offset = first global path id of this shard. */
 int  qmmx_gen_gbm(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,

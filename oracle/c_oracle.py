@@ -38,12 +38,23 @@ def lib():
             C.c_void_p, C.c_void_p, C.c_int, C.POINTER(abi.Params),
             C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double,
             C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(abi.Agg), C.c_int]
+        L.oq_run_paths_v.restype = C.c_int
+        L.oq_run_paths_v.argtypes = [
+            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+            C.c_void_p, C.c_void_p, C.c_int, C.POINTER(abi.Params),
+            C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double,
+            C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(abi.Agg), C.c_int]
         L.oq_gen_gbm.restype = C.c_int
         L.oq_gen_gbm.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.POINTER(abi.Gbm),
                                  C.c_void_p, C.c_void_p, C.c_void_p]
         L.oq_gen_bootstrap.restype = C.c_int
         L.oq_gen_bootstrap.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_void_p,
                                        C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oq_gen_bootstrap_v.restype = C.c_int
+        L.oq_gen_bootstrap_v.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                         C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oq_volume_slope.restype = C.c_double
+        L.oq_volume_slope.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int]
         L.oq_philox4x32_10.restype = None
         L.oq_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.oq_dot_py312.restype = C.c_double
@@ -58,7 +69,7 @@ def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=None, low=None,
+def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=None, low=None, volume=None,
               lr=None, policy=None, hist_range=(-8.0, 8.0), want_codes=False, max_trades=0,
               n_threads=1):
     """Oracle batch run. close/high/low: fp32 [steps][paths]. Returns dict(agg, codes, trades, counts)."""
@@ -66,6 +77,8 @@ def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=N
     steps, paths = close.shape
     high = None if high is None else np.ascontiguousarray(high, dtype=np.float32)
     low = None if low is None else np.ascontiguousarray(low, dtype=np.float32)
+    volume = None if volume is None else np.ascontiguousarray(volume, dtype=np.float32)
+    assert volume is None or volume.shape == close.shape
     lp = np.ascontiguousarray(levels_price, dtype=np.float64)
     ls = np.ascontiguousarray(levels_solid, dtype=np.uint8)
     lr_a = None if lr is None else np.ascontiguousarray(lr, dtype=np.float64).reshape(-1, 5)
@@ -74,7 +87,7 @@ def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=N
     trades = np.zeros((paths, max_trades), dtype=abi.TRADE_DTYPE) if max_trades > 0 else None
     counts = np.zeros(paths, dtype=np.int32) if max_trades > 0 else None
     agg = abi.Agg()
-    rc = lib().oq_run_paths(_ptr(close), _ptr(high), _ptr(low), paths, steps, _ptr(lp), _ptr(ls), len(lp),
+    rc = lib().oq_run_paths_v(_ptr(close), _ptr(high), _ptr(low), _ptr(volume), paths, steps, _ptr(lp), _ptr(ls), len(lp),
                             C.byref(params), _ptr(lr_a), 0 if lr_a is None else len(lr_a),
                             _ptr(pol_a), 0 if pol_a is None else len(pol_a),
                             float(hist_range[0]), float(hist_range[1]),
@@ -94,16 +107,20 @@ def gen_gbm(seed, path_offset, paths, steps, gbm: "abi.Gbm", ohlc=False):
     return close, high, low
 
 
-def gen_bootstrap(seed, path_offset, paths, steps, window_ohlc, block_len):
+def gen_bootstrap(seed, path_offset, paths, steps, window_ohlc, block_len, window_volume=None):
+    """Returns (close, high, low), plus volume when window_volume [window_len] is given."""
     w = np.ascontiguousarray(window_ohlc, dtype=np.float32).reshape(-1, 4)
+    wv = None if window_volume is None else np.ascontiguousarray(window_volume, dtype=np.float32)
+    assert wv is None or len(wv) == len(w)
     close = np.empty((steps, paths), dtype=np.float32)
     high = np.empty((steps, paths), dtype=np.float32)
     low = np.empty((steps, paths), dtype=np.float32)
-    rc = lib().oq_gen_bootstrap(seed, path_offset, paths, steps, _ptr(w), len(w), block_len,
-                                _ptr(close), _ptr(high), _ptr(low))
+    vol = None if wv is None else np.empty((steps, paths), dtype=np.float32)
+    rc = lib().oq_gen_bootstrap_v(seed, path_offset, paths, steps, _ptr(w), _ptr(wv), len(w), block_len,
+                                  _ptr(close), _ptr(high), _ptr(low), _ptr(vol))
     if rc != 0:
         raise RuntimeError(f"oq_gen_bootstrap failed: {rc}")
-    return close, high, low
+    return (close, high, low) if wv is None else (close, high, low, vol)
 
 
 def philox(ctr, key):

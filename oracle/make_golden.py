@@ -61,7 +61,8 @@ CASES = [
 ]
 
 SETTING_KEYS = dict(contact_prox="CONTACT_PROX", stop_padding="STOP_PADDING", tp_padding="TP_PADDING",
-                    q_min_prob="Q_MIN_PROB", cooldown_s="Q_SIGNAL_COOLDOWN", w_rules="W_RULES", w_ml="W_ML")
+                    q_min_prob="Q_MIN_PROB", cooldown_s="Q_SIGNAL_COOLDOWN", w_rules="W_RULES", w_ml="W_ML",
+                    veto_vol_strong="VETO_VOL_STRONG", veto_prox="VETO_PROX")
 
 
 def settings_for(params: dict) -> dict:

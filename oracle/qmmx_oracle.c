@@ -37,6 +37,39 @@ static double dot_py312(const double* w, const double* x, int n) {
 
 double oq_dot_py312(const double* w, const double* x, int n) { return dot_py312(w, x, n); }
 
+/* builtin sum() of n floats, CPython >= 3.12 (same compensated loop as above with unit weights) */
+static double sum_py312(const double* v, int n) {
+    double f = 0.0 + v[0];
+    double c = 0.0;
+    for (int i = 1; i < n; ++i) {
+        double t = f + v[i];
+        if (fabs(f) >= fabs(v[i])) c += (f - t) + v[i];
+        else c += (v[i] - t) + f;
+        f = t;
+    }
+    if (c != 0.0 && isfinite(c)) f += c;
+    return f;
+}
+
+/* _calc_volume_slope (M:1796-1811) at tick i of one path: recent_bars = the last min(i+1, 240) bars
+ * (frozen in oracle/headless.py:run_path), window 6; volume is [step][paths] fp32 */
+static double volume_slope_at(const float* volume, int64_t paths, int64_t path, int i) {
+    const int len = i + 1 < 240 ? i + 1 : 240;
+    if (!volume || len < 3) return 0.0;
+    const int n = len < 6 ? len : 6;
+    double v[6];
+    for (int j = 0; j < n; ++j) {
+        const double x = (double)volume[(int64_t)(i - n + 1 + j) * paths + path];
+        v[j] = (x == 0.0) ? 0.0 : x;              /* `b.get("v") or ... or 0.0`: a falsy volume becomes +0.0 */
+    }
+    const int half = n / 2 > 2 ? n / 2 : 2;
+    const double v1 = sum_py312(v, half) / (double)half;
+    const double v2 = sum_py312(v + (n - half), half) / (double)half;
+    if (v1 == 0 && v2 == 0) return 0.0;
+    return (v2 - v1) / (fabs(v1) + 1e-9);
+}
+double oq_volume_slope(const float* volume, int64_t paths, int64_t path, int i) { return volume_slope_at(volume, paths, path, i); }
+
 /* M:20-26 */
 static double sigmoid_policy(double x) {
     if (x < -50) return 0.0;
@@ -62,7 +95,7 @@ double oq_confidence(double dist, int solid, int tc, double prox) {
 }
 
 typedef struct {
-    const float *close, *high, *low;
+    const float *close, *high, *low, *volume;
     int64_t paths, p0, p1;
     int32_t steps;
     const double* lprice;
@@ -148,10 +181,20 @@ static void run_range(job_t* J) {
                                 if (d == 1) { stop = lp - P->stop_padding; target = lp + P->tp_padding; side = 0; }
                                 else { stop = lp + P->stop_padding; target = lp - P->tp_padding; side = 1; }
                                 code = QMMX_OK_ENTRY;
-                                /* veto: volume slope is 0 without per-bar volume => never vetoes (M:1773-1794) */
-                                (void)veto;
+                                if (veto) {        /* M:1678-1705 + _soft_veto M:1773-1794; slope 0 without per-bar volume */
+                                    const double vs = volume_slope_at(J->volume, J->paths, path, i);
+                                    int confl = 0;
+                                    for (int j = 0; j < L; ++j) if (fabs(J->lprice[j] - lp) <= 0.15) ++confl;
+                                    if (!(fabs(vs) < 0.05 && !(confl >= 2))) {
+                                        const double pw = prox * 0.12;
+                                        const int near_ = dist <= (P->veto_prox > pw ? P->veto_prox : pw);
+                                        /* the side follows the direction (M:1645), so only these two branches can fire */
+                                        if (near_ && vs < -P->veto_vol_strong)
+                                            code = (d == 1) ? QMMX_VETO_CONTRA_VOL_LONG : QMMX_VETO_CONTRA_VOL_SHORT;
+                                    }
+                                }
                                 double mlp = conf; int ok_ml = 1;
-                                if (!no_ml && J->n_lr > 0) {
+                                if (code == QMMX_OK_ENTRY && !no_ml && J->n_lr > 0) {
                                     const double* m = J->lr + 5 * (day < J->n_lr ? day : J->n_lr - 1);
                                     const double distf = fabs(lp - stop);
                                     double z = m[4];
@@ -162,7 +205,8 @@ static void run_range(job_t* J) {
                                     const double prob = 1.0 / (1.0 + exp(-z));
                                     ok_ml = prob >= qmin; mlp = prob;
                                 }
-                                if (blend) {
+                                if (code != QMMX_OK_ENTRY) { /* vetoed */ }
+                                else if (blend) {
                                     const double blended = w_rules * conf + w_ml * mlp;
                                     if (blended < qmin) code = QMMX_COMBINED_LOW;
                                 } else if (!no_ml && !ok_ml) code = QMMX_ML_CONF_LOW;
@@ -271,12 +315,30 @@ static void run_range(job_t* J) {
 static void* thread_main(void* arg) { run_range((job_t*)arg); return NULL; }
 
 /* Batch run over `[step][path]` fp32 bars; n_threads pthreads each take a contiguous path range. */
+int oq_run_paths_v(const float* close, const float* high, const float* low, const float* volume, int64_t paths, int32_t steps,
+                   const double* lprice, const uint8_t* lsolid, int L, const qmmx_params* P,
+                   const double* lr, int n_lr, const double* pol, int n_pol,
+                   double hist_lo, double hist_hi,
+                   uint8_t* codes, qmmx_trade* trades, int32_t* tcounts, int32_t max_trades,
+                   qmmx_agg* agg, int n_threads);
+
 int oq_run_paths(const float* close, const float* high, const float* low, int64_t paths, int32_t steps,
                  const double* lprice, const uint8_t* lsolid, int L, const qmmx_params* P,
                  const double* lr, int n_lr, const double* pol, int n_pol,
                  double hist_lo, double hist_hi,
                  uint8_t* codes, qmmx_trade* trades, int32_t* tcounts, int32_t max_trades,
                  qmmx_agg* agg, int n_threads) {
+    return oq_run_paths_v(close, high, low, NULL, paths, steps, lprice, lsolid, L, P, lr, n_lr, pol, n_pol, hist_lo, hist_hi,
+                          codes, trades, tcounts, max_trades, agg, n_threads);
+}
+
+/* same with per-bar volume [step][path] (NULL = none): only the soft veto reads it */
+int oq_run_paths_v(const float* close, const float* high, const float* low, const float* volume, int64_t paths, int32_t steps,
+                   const double* lprice, const uint8_t* lsolid, int L, const qmmx_params* P,
+                   const double* lr, int n_lr, const double* pol, int n_pol,
+                   double hist_lo, double hist_hi,
+                   uint8_t* codes, qmmx_trade* trades, int32_t* tcounts, int32_t max_trades,
+                   qmmx_agg* agg, int n_threads) {
     if (L > QMMX_MAX_LEVELS || paths < 0 || steps < 0) return -1;
     if ((P->flags & QMMX_F_EXIT_ON_HL) && (!high || !low)) return -1;
     if (n_threads < 1) n_threads = 1;
@@ -285,7 +347,7 @@ int oq_run_paths(const float* close, const float* high, const float* low, int64_
     pthread_t* th = (pthread_t*)calloc((size_t)n_threads, sizeof(pthread_t));
     for (int t = 0; t < n_threads; ++t) {
         job_t* J = &jobs[t];
-        J->close = close; J->high = high; J->low = low; J->paths = paths; J->steps = steps;
+        J->close = close; J->high = high; J->low = low; J->volume = volume; J->paths = paths; J->steps = steps;
         J->p0 = paths * t / n_threads; J->p1 = paths * (t + 1) / n_threads;
         J->lprice = lprice; J->lsolid = lsolid; J->L = L; J->P = *P;
         J->lr = lr; J->n_lr = n_lr; J->pol = pol; J->n_pol = n_pol;
@@ -384,9 +446,20 @@ int oq_gen_gbm(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps
 }
 
 /* Circular block bootstrap of the window's bar returns (relative to the previous close). */
+int oq_gen_bootstrap_v(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                       const float* window_ohlc, const float* window_volume, int32_t window_len, int32_t block_len,
+                       float* close, float* high, float* low, float* volume);
+
 int oq_gen_bootstrap(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
                      const float* window_ohlc, int32_t window_len, int32_t block_len,
                      float* close, float* high, float* low) {
+    return oq_gen_bootstrap_v(seed, path_offset, paths, steps, window_ohlc, NULL, window_len, block_len, close, high, low, NULL);
+}
+
+/* with per-bar volume: a resampled bar carries the volume of the window bar it was drawn from */
+int oq_gen_bootstrap_v(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                       const float* window_ohlc, const float* window_volume, int32_t window_len, int32_t block_len,
+                       float* close, float* high, float* low, float* volume) {
     const int nret = window_len - 1;
     if (nret < 1 || block_len < 1 || nret > 4096) return -1;
     float* rh = (float*)malloc(sizeof(float) * 3 * (size_t)nret);
@@ -419,6 +492,7 @@ int oq_gen_bootstrap(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t
             if (low) low[o] = S * rl[idx];
             S = S * rc[idx];
             close[o] = S;
+            if (volume && window_volume) volume[o] = window_volume[idx + 1];
         }
     }
     free(rh);

@@ -146,7 +146,7 @@ def make_sklearn_model(coef, intercept):
 
 
 def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy_w=None,
-                         disable_policy_gate=True, steps_per_day=390):
+                         disable_policy_gate=True, steps_per_day=390, volume=None):
     """Run the real `evaluate_entry` over one close series with the live loop's order.
 
     Transcribes `_engine_loop` (`qmmx_monolithic.py:2927-3016`, `3044-3115`) with the
@@ -156,6 +156,10 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
     lr_model: None, or an object with predict_proba (set as engine.model).
     policy_w: None or {"go_long": [7], "go_short": [7], "skip": [7]} or a per-day list of
               such dicts; the reference `OnlinePolicy` scores them.
+    volume:   None or one per-bar volume per close; at tick i `engine.recent_bars` holds the last
+              min(i+1, 240) bars `{t,o,h,l,c,v}` (Appendix A), which is what `_calc_volume_slope` reads.
+              When the soft veto fires the reference raises NameError (`VETO` is undefined, M:1705,
+              Appendix C) AFTER writing its policy_events row; the step code is taken from that row.
     Returns dict(codes=[...str per step], trades=[...], touch_counts=...).
     """
     q, conn, eng = make_engine(levels, settings)
@@ -172,7 +176,15 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
         prev_price = eng.state.last_price
         now_ms = 60000 * i
         eng.state.last_ts_ms = now_ms  # always fresh (Appendix A [CHOICE])
-        ok, code, msg, extras = eng.evaluate_entry(price, prev_price, now_ms, True)
+        if volume is not None:
+            lo = max(0, i - 239)
+            eng.recent_bars = [dict(t=60000 * j, o=float(closes[j]), h=float(closes[j]), l=float(closes[j]),
+                                    c=float(closes[j]), v=float(volume[j])) for j in range(lo, i + 1)]
+        try:
+            ok, code, msg, extras = eng.evaluate_entry(price, prev_price, now_ms, True)
+        except NameError:
+            row = conn.execute("SELECT features_json FROM policy_events ORDER BY id DESC LIMIT 1").fetchone()
+            ok, code, msg, extras = False, "VETO_" + json.loads(row[0])["reason"], "veto", {}
         eng.state.last_price = price
         if prev_price is not None and price != prev_price:
             eng.state.last_direction = "up" if price > prev_price else "down"

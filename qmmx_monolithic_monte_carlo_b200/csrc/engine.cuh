@@ -34,6 +34,7 @@ constexpr uint32_t kCbHasMl = 1u << 16, kCbHasProb = 1u << 17;   // internal Dev
 // Kernel parameters of one scan launch = one parameter combo over one set of paths (constant bank).
 struct ScanArgs {
     const float* close; const float* high; const float* low;   // [steps][pitch] fp32
+    const float* vol;             // per-bar volume [steps][pitch], or null: the soft veto is inert (M:1796-1811)
     int64_t pitch, paths;
     int32_t steps, combo_index;
     const DevTables* tables;                                    // the table of this combo
@@ -145,6 +146,63 @@ __device__ __noinline__ bool blend_fails(const ScanArgs* A, int k, float pf, int
     return fails;
 }
 
+// builtin sum() of n <= 3 floats under CPython >= 3.12 (Neumaier-compensated), as _calc_volume_slope uses it
+__device__ __forceinline__ double sum3_py312(double a, double b, double c3, int n) {
+    double f = 0.0 + a, c = 0.0;
+    {
+        const double t = f + b;
+        if (fabs(f) >= fabs(b)) c += (f - t) + b; else c += (b - t) + f;
+        f = t;
+    }
+    if (n > 2) {
+        const double t = f + c3;
+        if (fabs(f) >= fabs(c3)) c += (f - t) + c3; else c += (c3 - t) + f;
+        f = t;
+    }
+    if (c != 0.0 && isfinite(c)) f += c;
+    return f;
+}
+
+// rare: behavioural soft veto (M:1678-1705; _soft_veto M:1773-1794; _calc_volume_slope M:1796-1811 over
+// engine.recent_bars = the last min(i+1, 240) bars, window 6).  Returns 0 (allow) or the veto reason code.
+// The side follows the direction (M:1645), so of the four branches of _soft_veto only "approaching with falling
+// volume" can fire: from_below & long & slope < -strong, from_above & short & slope < -strong.
+__device__ __noinline__ int veto_check(const ScanArgs* A, int k, float pf, int side, int i, int64_t path) {
+    const int len = i + 1 < 240 ? i + 1 : 240;
+    double vs = 0.0;
+    if (len >= 3) {
+        const int n = len < 6 ? len : 6;
+        double v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0;      // newest six, oldest first from index 6 - n
+        const float* col = A->vol + path;
+        const size_t pitch = (size_t)A->pitch;
+        v5 = (double)__ldg(col + (size_t)i * pitch); v4 = (double)__ldg(col + (size_t)(i - 1) * pitch);
+        v3 = (double)__ldg(col + (size_t)(i - 2) * pitch);
+        if (n > 3) v2 = (double)__ldg(col + (size_t)(i - 3) * pitch);
+        if (n > 4) v1 = (double)__ldg(col + (size_t)(i - 4) * pitch);
+        if (n > 5) v0 = (double)__ldg(col + (size_t)(i - 5) * pitch);
+        // `b.get("v") or ... or 0.0`: a zero volume of either sign becomes +0.0; adding 0.0 does exactly that
+        v0 += 0.0; v1 += 0.0; v2 += 0.0; v3 += 0.0; v4 += 0.0; v5 += 0.0;
+        // vols = [oldest .. newest] of length n; half = max(2, n // 2); first half vs last half
+        double a1, a2;
+        if (n == 6) { a1 = sum3_py312(v0, v1, v2, 3) / 3.0; a2 = sum3_py312(v3, v4, v5, 3) / 3.0; }
+        else if (n == 5) { a1 = sum3_py312(v1, v2, 0.0, 2) / 2.0; a2 = sum3_py312(v4, v5, 0.0, 2) / 2.0; }
+        else if (n == 4) { a1 = sum3_py312(v2, v3, 0.0, 2) / 2.0; a2 = sum3_py312(v4, v5, 0.0, 2) / 2.0; }
+        else { a1 = sum3_py312(v3, v4, 0.0, 2) / 2.0; a2 = sum3_py312(v4, v5, 0.0, 2) / 2.0; }
+        vs = (a1 == 0.0 && a2 == 0.0) ? 0.0 : (a2 - a1) / (fabs(a1) + 1e-9);
+    }
+    const bool confl = (g_S.cold[k].flags & kLvConfl015) != 0;        // _has_confluence_near(level, 0.15), M:1885
+    if (fabs(vs) < 0.05 && !confl) return 0;                          // INCONCLUSIVE
+    const double dist = fabs(g_S.cold[k].price - (double)pf);
+    const double pw = A->combo.prox * 0.12;
+    const bool near_ = dist <= (A->combo.vprox > pw ? A->combo.vprox : pw);
+    if (near_ && vs < -A->combo.vstrong) {
+        const int code = side == 0 ? QMMX_VETO_CONTRA_VOL_LONG : QMMX_VETO_CONTRA_VOL_SHORT;
+        smem_inc(&g_S.u[U_ENTRY + code]);
+        return code;
+    }
+    return 0;
+}
+
 // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
 __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i) {
     if (A->n_pol <= 0) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return false; }   // zero weights: sigmoid(0) = 0.5 < 0.60
@@ -238,6 +296,7 @@ struct PathEngine {
         const float2 cp = g_S.cpass[min(tc, 3) - 1][k];
         if (!(pf >= cp.x && pf <= cp.y)) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
         const int side = dir - 1;                                            // M:1645: up -> long(0), down -> short(1)
+        if (A.vol) { const int vc = veto_check(&A, k, pf, side, i, path); if (vc) return vc; }   // M:1678-1705
         if (A.combo.flags & QMMX_F_USE_BLEND) {                              // M:1730-1742
             if (blend_fails(&A, k, pf, tc, side, day_off)) return QMMX_COMBINED_LOW;
         } else if (A.mlmask) {                                               // M:1454-1466, M:1745-1755

@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) fused_gbm_kernel(const
 // ---- circular block bootstrap of a candle window ---------------------------------------------------------------
 constexpr int kMaxWindow = 1024;
 struct BootDev {
-    const float* ratios;        // [3][nret]: high, low, close of bar t over close of bar t-1
+    const float* ratios;        // [3][nret]: high, low, close of bar t over close of bar t-1; [4th plane]: volume of bar t
     int32_t nret, block_len;
     float s0;
     uint32_t k0, k1;
@@ -233,11 +233,13 @@ struct BootDev {
 };
 
 __global__ void __launch_bounds__(kThreads) gen_bootstrap_kernel(float* __restrict__ close, float* __restrict__ high,
-                                                                 float* __restrict__ low, int64_t pitch, int64_t paths,
+                                                                 float* __restrict__ low, float* __restrict__ vol,
+                                                                 int64_t pitch, int64_t paths,
                                                                  int32_t steps, const BootDev g) {
-    __shared__ float rh[kMaxWindow], rl[kMaxWindow], rc[kMaxWindow];
+    __shared__ float rh[kMaxWindow], rl[kMaxWindow], rc[kMaxWindow], rv[kMaxWindow];
     for (int t = threadIdx.x; t < g.nret; t += blockDim.x) {
         rh[t] = g.ratios[t]; rl[t] = g.ratios[g.nret + t]; rc[t] = g.ratios[2 * g.nret + t];
+        rv[t] = vol ? g.ratios[3 * g.nret + t] : 0.f;
     }
     __syncthreads();
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -259,6 +261,7 @@ __global__ void __launch_bounds__(kThreads) gen_bootstrap_kernel(float* __restri
             if (low) __stcs(low + o, __fmul_rn(S, rl[idx]));
             S = __fmul_rn(S, rc[idx]);
             __stcs(close + o, S);
+            if (vol) __stcs(vol + o, rv[idx]);
             if (++off == g.block_len) { off = 0; ++blk; }
         }
     }

@@ -45,6 +45,8 @@ struct qmmx_ctx {
     bool force_v1 = false;     // QMMX_SCAN_V1=1: run the first-generation lockstep kernel (A/B measurements)
     // resident bars
     float *d_close = nullptr, *d_high = nullptr, *d_low = nullptr;
+    float* d_vol = nullptr;                 // per-bar volume of the resident bars (library-owned), or null
+    std::vector<float> boot_vol;            // window volumes for the next qmmx_gen_bootstrap
     bool own_bars = false;
     int64_t paths = 0, pitch = 0; int32_t steps = 0;
     // staging for qmmx_run_scan_host
@@ -71,7 +73,10 @@ int fail(qmmx_ctx* c, int code, const std::string& msg) {
 
 inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
+void free_volume(qmmx_ctx* c) { if (c->d_vol) cudaFree(c->d_vol); c->d_vol = nullptr; }
+
 void free_bars(qmmx_ctx* c) {
+    free_volume(c);
     if (c->own_bars) { cudaFree(c->d_close); cudaFree(c->d_high); cudaFree(c->d_low); }
     c->d_close = c->d_high = c->d_low = nullptr;
     c->own_bars = false; c->paths = 0; c->pitch = 0; c->steps = 0;
@@ -133,6 +138,7 @@ int prepare(qmmx_ctx* ctx) {
         std::memset(&D, 0, sizeof(D));
         D.sp = P.stop_padding; D.tp = P.tp_padding; D.qmin = P.q_min_prob; D.prox = P.contact_prox;
         D.pmax = 0.0001 > P.contact_prox ? 0.0001 : P.contact_prox;
+        D.vstrong = P.veto_vol_strong; D.vprox = P.veto_prox;
         double wr = P.w_rules, wm = P.w_ml, s = wr + wm;                // M:1714-1719
         if (s <= 0) { wr = 1.0; wm = 0.0; s = 1.0; }
         D.wr = wr / s; D.wm = wm / s;
@@ -193,7 +199,9 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
                int64_t paths, int32_t steps) {
     std::memset(&A, 0, sizeof(A));
     const DevCombo& D = ctx->h_combos[c];
-    A.close = cl; A.high = h; A.low = l; A.pitch = pitch; A.paths = paths; A.steps = steps; A.combo_index = c;
+    A.close = cl; A.high = h; A.low = l;
+    A.vol = (cl && cl == ctx->d_close && (D.flags & QMMX_F_ENABLE_VETO)) ? ctx->d_vol : nullptr;
+    A.pitch = pitch; A.paths = paths; A.steps = steps; A.combo_index = c;
     A.tables = ctx->d_tables + D.table;
     A.flat = ctx->d_flat + (size_t)c * QMMX_AGG_SLOTS;
     const size_t per_mask = (size_t)ctx->n_lr * kMaxLevels;
@@ -278,7 +286,7 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
         const bool parity = par && c == 0;
         if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
-        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
+        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE) || A.vol != nullptr;
         // the lean exit block assumes a single price cannot hit both thresholds: stop below / target above the level
         const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
         if (lean && band_ok) {
@@ -469,6 +477,7 @@ int qmmx_upload_bars(qmmx_ctx* c, const float* close, const float* high, const f
         return fail(ctx, QMMX_E_BADARG, "close must be non-null; high and low come together");
     int rc = alloc_bars(ctx, paths, steps, high != nullptr);
     if (rc != 0) return rc;
+    free_volume(ctx);                       // new bars: a volume plane of the old ones would be stale
     if (paths == 0 || steps == 0) return QMMX_OK;
     const size_t w = (size_t)paths * 4, dp = (size_t)ctx->pitch * 4;
     CK(cudaMemcpy2DAsync(ctx->d_close, dp, close, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
@@ -531,12 +540,46 @@ int qmmx_download_bars(qmmx_ctx* c, float* close, float* high, float* low) {
     return QMMX_OK;
 }
 
+int qmmx_upload_volume(qmmx_ctx* c, const float* volume, int64_t paths, int32_t steps) {
+    ENTER(c);
+    if (!volume) { free_volume(ctx); return QMMX_OK; }
+    if (!ctx->d_close) return fail(ctx, QMMX_E_STATE, "no resident bars (qmmx_upload_bars / qmmx_gen_* first)");
+    if (!ctx->own_bars) return fail(ctx, QMMX_E_UNSUPPORTED, "volume needs library-owned bars (pitch is the library's)");
+    if (paths != ctx->paths || steps != ctx->steps) return fail(ctx, QMMX_E_BADARG, "volume shape differs from the resident bars");
+    if (paths == 0 || steps == 0) return QMMX_OK;
+    if (!ctx->d_vol) CK(cudaMalloc(&ctx->d_vol, (size_t)ctx->pitch * (size_t)steps * sizeof(float)));
+    const size_t w = (size_t)paths * 4, dp = (size_t)ctx->pitch * 4;
+    CK(cudaMemcpy2DAsync(ctx->d_vol, dp, volume, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return QMMX_OK;
+}
+
+int qmmx_download_volume(qmmx_ctx* c, float* volume) {
+    ENTER(c);
+    if (!ctx->d_vol) return fail(ctx, QMMX_E_STATE, "no resident volume");
+    if (!volume) return fail(ctx, QMMX_E_BADARG, "null destination");
+    if (ctx->paths == 0 || ctx->steps == 0) return QMMX_OK;
+    const size_t w = (size_t)ctx->paths * 4, dp = (size_t)ctx->pitch * 4;
+    CK(cudaMemcpy2DAsync(volume, w, ctx->d_vol, dp, w, ctx->steps, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return QMMX_OK;
+}
+
+int qmmx_set_bootstrap_volume(qmmx_ctx* c, const float* window_volume, int32_t window_len) {
+    ENTER(c);
+    if (!window_volume) { ctx->boot_vol.clear(); return QMMX_OK; }
+    if (window_len < 2 || window_len > kMaxWindow + 1) return fail(ctx, QMMX_E_BADARG, "window_len must be 2..1025");
+    ctx->boot_vol.assign(window_volume, window_volume + window_len);
+    return QMMX_OK;
+}
+
 int qmmx_gen_gbm(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps, const qmmx_gbm* gbm) {
     ENTER(c);
     int rc = check_gbm(ctx, gbm);
     if (rc != 0) return rc;
     if (paths < 0 || steps < 0) return fail(ctx, QMMX_E_BADARG, "negative size");
     if ((rc = alloc_bars(ctx, paths, steps, gbm->sub_steps == 4)) != 0) return rc;
+    free_volume(ctx);
     if (paths == 0 || steps == 0) return QMMX_OK;
     const GbmDev g = make_gbm(gbm, seed, path_offset);
     const int64_t blocks = std::min<int64_t>((paths + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
@@ -559,7 +602,11 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
     int rc = alloc_bars(ctx, paths, steps, true);
     if (rc != 0) return rc;
     if (paths == 0 || steps == 0) return QMMX_OK;
-    std::vector<float> ratios(3 * (size_t)nret);
+    const bool with_vol = (int32_t)ctx->boot_vol.size() == window_len;     // qmmx_set_bootstrap_volume
+    std::vector<float> ratios((with_vol ? 4 : 3) * (size_t)nret);
+    if (with_vol) for (int t = 1; t < window_len; ++t) ratios[3 * (size_t)nret + t - 1] = ctx->boot_vol[t];
+    if (with_vol) { if (!ctx->d_vol) CK(cudaMalloc(&ctx->d_vol, (size_t)ctx->pitch * (size_t)steps * sizeof(float))); }
+    else free_volume(ctx);
     for (int t = 1; t < window_len; ++t) {
         const float pc = window_ohlc[4 * (t - 1) + 3];
         ratios[t - 1] = window_ohlc[4 * t + 1] / pc;
@@ -581,7 +628,7 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
         g.k0 = (uint32_t)seed; g.k1 = (uint32_t)(seed >> 32); g.path_offset = path_offset;
         const int64_t blocks = std::min<int64_t>((paths + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
         cudaEventRecord(ctx->ev0, ctx->stream);
-        gen_bootstrap_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(ctx->d_close, ctx->d_high, ctx->d_low, ctx->pitch, paths, steps, g);
+        gen_bootstrap_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(ctx->d_close, ctx->d_high, ctx->d_low, with_vol ? ctx->d_vol : nullptr, ctx->pitch, paths, steps, g);
         ctx->launches++;
         e = cudaGetLastError();
         cudaEventRecord(ctx->ev1, ctx->stream);

@@ -113,7 +113,7 @@ __device__ inline void lean_setup(const ScanArgs& A) {
     }
 }
 
-// SLOW = the blend gate or the OnlinePolicy gate is enabled (float64 slow paths compiled in)
+// SLOW = the blend gate, the OnlinePolicy gate or the volume veto is enabled (float64 slow paths compiled in)
 template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW>
 struct LeanEngine {
     typedef typename LatchType<WIDE>::T latch_t;
@@ -208,6 +208,7 @@ struct LeanEngine {
             c_gate += over ? 1u : (1u << 16);                     // M:1579 / M:1628
             return over ? QMMX_LEVEL_OVERTOUCHED : QMMX_CONF_LOW;
         }
+        if (SLOW && A.vol) { const int vc = veto_check(&A, k, pf, side, i, path); if (vc) return vc; }   // M:1678-1705
         if (neg) { c_ml += 1u; return QMMX_ML_CONF_LOW; }         // M:1745-1755 (single day, AND mode)
         if (SLOW && (A.combo.flags & QMMX_F_USE_BLEND)) {         // M:1730-1742
             if (blend_fails(&A, k, pf, (int)tc, side, day_off)) return QMMX_COMBINED_LOW;

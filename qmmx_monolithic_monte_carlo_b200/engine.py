@@ -57,6 +57,9 @@ def load_library(path: Optional[str] = None):
         "qmmx_pin_host": (C.c_int, [vp, vp, C.c_size_t]),
         "qmmx_unpin_host": (C.c_int, [vp, vp]),
         "qmmx_download_bars": (C.c_int, [vp, vp, vp, vp]),
+        "qmmx_upload_volume": (C.c_int, [vp, vp, i64, i32]),
+        "qmmx_download_volume": (C.c_int, [vp, vp]),
+        "qmmx_set_bootstrap_volume": (C.c_int, [vp, vp, i32]),
         "qmmx_gen_gbm": (C.c_int, [vp, u64, u64, i64, i32, C.POINTER(abi.Gbm)]),
         "qmmx_gen_bootstrap": (C.c_int, [vp, u64, u64, i64, i32, vp, i32, i32]),
         "qmmx_run_scan": (C.c_int, [vp, vp, vp, vp, i32, vp]),
@@ -236,6 +239,21 @@ class MCEngine:
         steps, paths = close.shape
         self._ck(self._L.qmmx_upload_bars(self._h, _ptr(close), _ptr(high), _ptr(low), paths, steps))
 
+    def upload_volume(self, volume):
+        """Per-bar volume of the resident bars ([steps][paths]); None drops it.  Read by the soft veto only
+        (ENABLE_VETO: `_calc_volume_slope` M:1796-1811, `_soft_veto` M:1773-1794)."""
+        if volume is None:
+            self._ck(self._L.qmmx_upload_volume(self._h, None, 0, 0))
+            return
+        volume = _f32_2d(volume, "volume")
+        steps, paths = volume.shape
+        self._ck(self._L.qmmx_upload_volume(self._h, _ptr(volume), paths, steps))
+
+    def download_volume(self, paths, steps):
+        v = np.empty((steps, paths), dtype=np.float32)
+        self._ck(self._L.qmmx_download_volume(self._h, _ptr(v)))
+        return v
+
     def bind_device_bars(self, close_ptr: int, high_ptr: Optional[int], low_ptr: Optional[int], paths: int,
                          steps: int, pitch: Optional[int] = None):
         self._ck(self._L.qmmx_bind_device_bars(self._h, C.c_void_p(close_ptr), C.c_void_p(high_ptr or 0),
@@ -259,8 +277,13 @@ class MCEngine:
     def gen_gbm(self, seed, path_offset, paths, steps, gbm: "abi.Gbm"):
         self._ck(self._L.qmmx_gen_gbm(self._h, seed, path_offset, paths, steps, C.byref(gbm)))
 
-    def gen_bootstrap(self, seed, path_offset, paths, steps, window_ohlc, block_len):
+    def gen_bootstrap(self, seed, path_offset, paths, steps, window_ohlc, block_len, window_volume=None):
+        """window_volume [window_len]: also generate the per-bar volume plane (soft veto input)."""
         w = np.ascontiguousarray(window_ohlc, dtype=np.float32).reshape(-1, 4)
+        wv = None if window_volume is None else np.ascontiguousarray(window_volume, dtype=np.float32)
+        if wv is not None and len(wv) != len(w):
+            raise ValueError("window_volume must have one value per window bar")
+        self._ck(self._L.qmmx_set_bootstrap_volume(self._h, _ptr(wv), len(w)))
         self._ck(self._L.qmmx_gen_bootstrap(self._h, seed, path_offset, paths, steps, _ptr(w), len(w), block_len))
 
     # ---- the hot path ----

@@ -118,3 +118,59 @@ def test_bootstrap_generator_uses_window_returns():
     d = np.abs(ratio[..., None] - rc[None, None, :]).min(axis=-1)
     assert d.max() < 2e-7
     assert np.all(h >= l)
+
+
+VETO_LONG, VETO_SHORT = abi.ENTRY_CODES.index("VETO_CONTRA_VOL_LONG"), abi.ENTRY_CODES.index("VETO_CONTRA_VOL_SHORT")
+
+
+def _volume_for(close, rng):
+    """Per-bar volume with swings big enough that the 6-bar slope crosses +-0.25 regularly."""
+    steps, paths = close.shape
+    base = rng.uniform(5e4, 2e5, size=(1, paths))
+    v = base * np.exp(np.cumsum(rng.normal(0, 0.35, size=(steps, paths)), axis=0) * 0.5)
+    v[rng.random(size=v.shape) < 0.01] = 0.0          # a few empty bars (`v or 0.0`)
+    return v.astype(np.float32)
+
+
+def test_c_oracle_volume_veto_matches_headless():
+    """Row a7 (M:1678-1705, M:1773-1811): with per-bar volume the soft veto fires; C restatement == headless.py."""
+    rng = np.random.default_rng(11)
+    close = F.host_gbm_closes(48, 390, seed=31)
+    vol = _volume_for(close, rng)
+    lv = H.sort_levels(F.levels_30())
+    kw = dict(contact_prox=0.1, cooldown_s=60, enable_veto=True, veto_prox=0.08)
+    P, params = H.Params(**kw), abi.make_params(**kw)
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    r = CO.run_paths(close, [x.price for x in lv], [x.solid for x in lv], params, volume=vol, lr=lr,
+                     want_codes=True, max_trades=64, n_threads=2)
+    n_veto = 0
+    for j in range(48):
+        o = H.run_path(close[:, j], lv, P, volume=[float(x) for x in vol[:, j]],
+                       lr=[H.LRModel(coef=[0.2, -0.5, -0.45, 0.35], intercept=1.0)])
+        assert o.codes == r["codes"][:, j].tolist(), j
+        assert len(o.trades) == r["counts"][j]
+        n_veto += sum(1 for c in o.codes if c in (VETO_LONG, VETO_SHORT))
+    assert n_veto > 20          # the gate is exercised, both codes
+    a = r["agg"]
+    assert a.entry_hist[VETO_LONG] > 0 and a.entry_hist[VETO_SHORT] > 0
+    # slope helper alone, every tick of one path
+    for i in range(390):
+        assert CO.lib().oq_volume_slope(vol.ctypes.data, 48, 3, i) == H.volume_slope([float(x) for x in vol[max(0, i - 239):i + 1, 3]])
+    # without volume the veto is inert (the reference on its own data, SURVEY section 2)
+    r0 = CO.run_paths(close, [x.price for x in lv], [x.solid for x in lv], params, lr=lr, want_codes=True)
+    assert r0["agg"].entry_hist[VETO_LONG] == 0 and r0["agg"].entry_hist[VETO_SHORT] == 0
+
+
+def test_bootstrap_generator_carries_window_volume():
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    wv = np.arange(1000, 1040, dtype=np.float32)
+    c, h, l, v = CO.gen_bootstrap(9, 0, 16, 390, window, 5, window_volume=wv)
+    c2, _, _ = CO.gen_bootstrap(9, 0, 16, 390, window, 5)
+    assert np.array_equal(c, c2)
+    assert set(np.unique(v)) <= set(wv[1:].tolist())
+    idx = (v - 1000).astype(int)                       # the window bar each step was drawn from
+    prev = np.vstack([np.full((1, 16), window[-1, 3], dtype=np.float32), c[:-1]])
+    assert np.array_equal(c, prev * (window[idx, 3] / window[idx - 1, 3]).astype(np.float32))

@@ -448,3 +448,65 @@ def test_gpu_lean_kernels_equal_first_generation(eng, hl, monkeypatch):
         assert_trades_equal(tr0, c0, tr1, c1)
     finally:
         v1.close()
+
+
+@pytest.mark.parametrize("variant", ["lean", "lean_hl", "first_generation(tiny)"])
+def test_gpu_volume_soft_veto(eng, variant):
+    """per-bar volume feeds `_calc_volume_slope` (M:1796-1811) and the soft veto
+    (M:1678-1705, M:1773-1794), which sits between the confidence gate and the LR gate.  Codes, trades and
+    aggregates against the oracle (itself pinned against the reference with volume in recent_bars)."""
+    from tests.test_c_oracle import _volume_for, VETO_LONG, VETO_SHORT
+    rng = np.random.default_rng(12)
+    hl = variant == "lean_hl"
+    tiny = variant.startswith("first")
+    if hl:
+        close, high, low = CO.gen_gbm(41, 0, 4096, 390, abi.make_gbm(sub_steps=4), ohlc=True)
+    else:
+        close, high, low = F.host_gbm_closes(4096, 390, seed=33), None, None
+    vol = _volume_for(close, rng)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    params = abi.make_params(contact_prox=0.1, cooldown_s=60, enable_veto=True, veto_prox=0.08, exit_on_hl=hl,
+                             tiny_prices=tiny)
+    configure(eng, price, solid, params, lr)
+    eng.upload_bars(close, high, low)
+    # veto enabled but no volume: inert, exactly the run without the flag
+    inert = eng.run_scan()[0].agg
+    assert inert.entry_hist[VETO_LONG] == 0 and inert.entry_hist[VETO_SHORT] == 0
+    eng.upload_volume(vol)
+    assert np.array_equal(eng.download_volume(*close.shape[::-1]), vol)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=close.shape)
+    o = CO.run_paths(close, price, solid, params, high=high, low=low, volume=vol, lr=lr, want_codes=True,
+                     max_trades=64, n_threads=8)
+    assert o["agg"].entry_hist[VETO_LONG] > 100 and o["agg"].entry_hist[VETO_SHORT] > 100
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    assert_agg_equal(eng.run_scan()[0].agg, o["agg"])          # aggregate-only kernel variant
+    eng.upload_volume(None)
+    assert_agg_equal(eng.run_scan()[0].agg, inert)
+
+
+def test_gpu_bootstrap_volume_plane_and_veto(eng):
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    wv = np.random.default_rng(2).uniform(1e4, 3e5, 40).astype(np.float32)
+    paths, steps = 2000, 2 * 390
+    eng.gen_bootstrap(9, 11, paths, steps, window, 5, window_volume=wv)
+    c, h, l = eng.download_bars(paths, steps, hl=True)
+    v = eng.download_volume(paths, steps)
+    oc, oh, ol, ov = CO.gen_bootstrap(9, 11, paths, steps, window, 5, window_volume=wv)
+    assert np.array_equal(c, oc) and np.array_equal(h, oh) and np.array_equal(l, ol) and np.array_equal(v, ov)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True, enable_veto=True)
+    configure(eng, price, solid, params, None)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=c.shape)
+    o = CO.run_paths(c, price, solid, params, high=h, low=l, volume=v, want_codes=True, max_trades=64, n_threads=8)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    eng.gen_bootstrap(9, 11, paths, steps, window, 5)           # without volume: the plane is dropped
+    with pytest.raises(E.QmmxError):
+        eng.download_volume(paths, steps)

@@ -11,14 +11,15 @@ from qmmx_monolithic_monte_carlo_b200 import fixtures as F
 pytestmark = pytest.mark.skipif(not rh.reference_available(), reason="reference not mounted")
 
 
-def _check(levels, params, closes, lr=None, pol=None):
+def _check(levels, params, closes, lr=None, pol=None, volume=None):
     lv = H.sort_levels(levels)
     P = H.Params(**params)
     models = [rh.make_sklearn_model(m.coef, m.intercept) for m in lr] if lr else None
     for j in range(closes.shape[1]):
+        vj = None if volume is None else [float(x) for x in volume[:, j]]
         ref = rh.drive_reference_path(closes[:, j], levels, settings_for(params), lr_model=models,
-                                      policy_w=pol, disable_policy_gate=P.disable_policy_gate)
-        o = H.run_path(closes[:, j], lv, P, lr=lr, policy=pol)
+                                      policy_w=pol, disable_policy_gate=P.disable_policy_gate, volume=vj)
+        o = H.run_path(closes[:, j], lv, P, lr=lr, policy=pol, volume=vj)
         assert [H.ENTRY_CODES[c] for c in o.codes] == ref["codes"]
         assert len(o.trades) == len(ref["trades"])
         for a, b in zip(ref["trades"], o.trades):
@@ -43,6 +44,20 @@ def test_random_params_against_reference(seed):
     closes = F.host_gbm_closes(6, 390, seed=seed, round_cents=bool(rng.integers(2)),
                                sigma=float(rng.choice([0.05, 0.15, 0.4])))
     _check(F.levels_30(), params, closes, lr=lr, pol=pol)
+
+
+def test_volume_soft_veto_against_reference():
+    """Row a7: per-bar volume in engine.recent_bars makes the reference's soft veto fire (M:1678-1705, M:1773-1811)."""
+    rng = np.random.default_rng(7)
+    closes = F.host_gbm_closes(4, 390, seed=77)
+    vol = (1e5 * np.exp(0.5 * np.cumsum(rng.normal(0, 0.35, size=closes.shape), axis=0))).astype(np.float32)
+    vol[rng.random(size=vol.shape) < 0.01] = 0.0
+    params = dict(contact_prox=0.1, cooldown_s=60, enable_veto=True, veto_prox=0.08)
+    _check(F.levels_30(), params, closes, volume=vol)
+    lv = H.sort_levels(F.levels_30())
+    codes = [c for j in range(4) for c in H.run_path(closes[:, j], lv, H.Params(**params),
+                                                      volume=[float(x) for x in vol[:, j]]).codes]
+    assert sum(1 for c in codes if H.ENTRY_CODES[c].startswith("VETO_CONTRA")) >= 3
 
 
 def test_lr_contract_matches_sklearn_predict_proba():
