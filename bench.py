@@ -30,8 +30,8 @@ METRIC = "simulated path-steps/sec (390-step paths)"
 UNIT = "path-steps/s"
 STEPS_PER_PATH = 390
 # DRAM bytes of one lean_scan_kernel launch over 1M x 390 fp32 closes, from the committed ncu capture
-# (1.560333 GB read + 4.03 MB written; algorithmic bytes are 1.560000 GB: nothing is re-read)
-NCU_TRAFFIC_BYTES = 1.560333e9 + 4.028e6
+# (1.560352 GB read + 7.43 MB written; algorithmic bytes are 1.560000 GB: nothing is re-read)
+NCU_TRAFFIC_BYTES = 1.560352e9 + 7.427e6
 
 
 def workload(name: str):

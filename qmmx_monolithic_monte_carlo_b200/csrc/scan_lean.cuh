@@ -21,8 +21,12 @@
 
 namespace qmmx {
 
-constexpr int kLeanThreads = 512;
-constexpr int kLeanBlocksPerSM = 2;
+#ifndef QMMX_LEAN_THREADS
+#define QMMX_LEAN_THREADS 1024
+#define QMMX_LEAN_BLOCKS 1
+#endif
+constexpr int kLeanThreads = QMMX_LEAN_THREADS;
+constexpr int kLeanBlocksPerSM = QMMX_LEAN_BLOCKS;
 constexpr int kLeanWarps = kLeanThreads / 32;
 constexpr int kTouchStride = kLeanThreads + 4;      // bytes per level row; stride/4 is odd, so level rows rotate over the banks
 constexpr int kNoCool = 0x7fffffff;
