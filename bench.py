@@ -212,6 +212,18 @@ def run_extra(args, name, rank, local_rank, world):
             eng.run_scan_async()
         cfg = dict(workload=f"C5: block bootstrap (block 5) of a 40-bar window into {P} x {days}-day paths per GPU, "
                             "per-day LR weights, exits on high/low; generate (c,h,l) then scan", bytes_per_step=24)
+    elif name == "c5f":
+        P, days = args.paths or 1_250_000, 5
+        rng = np.random.default_rng(5)
+        lr5 = np.column_stack([rng.normal(0.2, 0.2, days), rng.normal(-0.5, 0.2, days), rng.normal(-0.45, 0.1, days),
+                               rng.normal(0.35, 0.1, days), rng.normal(1.0, 0.1, days)])
+        eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True)); eng.set_lr(lr5)
+        window = F.synthetic_window(40)
+        T = days * STEPS_PER_PATH
+        units = P * T
+        run = lambda: eng.run_fused_bootstrap_async(F.HOST_SEED, rank * P, P, T, window, 5)
+        cfg = dict(workload=f"C5 fused: block bootstrap (block 5) of a 40-bar window into {P} x {days}-day paths per GPU, "
+                            "per-day LR weights, exits on high/low; generated and scanned in registers", bytes_per_step=0)
     else:
         raise SystemExit(f"unknown workload {name}")
     scratch = [None]
@@ -274,7 +286,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    if args.impl == "ours" and args.workload in ("c3", "c4", "c5", "c2hl"):
+    if args.impl == "ours" and args.workload in ("c3", "c4", "c5", "c5f", "c2hl"):
         run_extra(args, args.workload, rank, local_rank, world)
         return
     wl = workload(args.workload)

@@ -20,7 +20,7 @@
  *                                                                                       M:1888-1948, M:259-270
  *   qmmx_lr_score        OnlinePolicy.score_entry / predict_proba as a batch            M:334-355, M:20-26, M:1463
  *   qmmx_run_jitter      QMMXApp.simulate_monte_carlo trial loop (walk_outcome)         M:3449-3510
- *   qmmx_gen_gbm / qmmx_gen_bootstrap / qmmx_run_fused_gbm
+ *   qmmx_gen_gbm / qmmx_gen_bootstrap / qmmx_run_fused_gbm / qmmx_run_fused_bootstrap
  *                        no reference equivalent (the reference simulates on real Polygon bars);
  *                        synthetic 1-minute paths demanded by BASELINE.json north_star.
  *
@@ -224,6 +224,12 @@ int  qmmx_run_scan_host(qmmx_ctx* ctx, const float* close, const float* high, co
 /* generate GBM closes in registers and scan them in the same kernel (no bar traffic to HBM) */
 int  qmmx_run_fused_gbm(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
                         const qmmx_gbm* gbm, qmmx_agg* agg_out);
+/* block-bootstrap the window (as qmmx_gen_bootstrap: same draws, same bars) and scan in the same kernel; the bars
+ * are never written, so they carry no volume plane (the soft veto is inert on this path) */
+int  qmmx_run_fused_bootstrap(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                              const float* window_ohlc, int32_t window_len, int32_t block_len, qmmx_agg* agg_out);
+int  qmmx_run_fused_bootstrap_async(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                                    const float* window_ohlc, int32_t window_len, int32_t block_len);
 /* launch only; results stay on the device until qmmx_fetch_agg / qmmx_agg_device */
 int  qmmx_run_scan_async(qmmx_ctx* ctx);
 int  qmmx_run_fused_gbm_async(qmmx_ctx* ctx, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,

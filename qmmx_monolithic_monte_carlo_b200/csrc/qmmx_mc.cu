@@ -798,6 +798,72 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     return QMMX_OK;
 }
 
+int qmmx_run_fused_bootstrap_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                                   const float* window_ohlc, int32_t window_len, int32_t block_len) {
+    ENTER(c);
+    const int nret = window_len - 1;
+    if (!window_ohlc || nret < 1 || nret > kMaxWindow || block_len < 1 || paths < 0 || steps < 0)
+        return fail(ctx, QMMX_E_BADARG, "window_len must be 2..1025, block_len >= 1");
+    int rc = prepare(ctx);
+    if (rc != 0) return rc;
+    if (ctx->any_tiny || !ctx->lean_ok) return fail(ctx, QMMX_E_UNSUPPORTED, "fused bootstrap needs the lean engine (no TINY_PRICES, positive level prices)");
+    if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
+    std::vector<float> ratios(3 * (size_t)nret);
+    for (int t = 1; t < window_len; ++t) {
+        const float pc = window_ohlc[4 * (t - 1) + 3];
+        ratios[t - 1] = window_ohlc[4 * t + 1] / pc;
+        ratios[nret + t - 1] = window_ohlc[4 * t + 2] / pc;
+        ratios[2 * nret + t - 1] = window_ohlc[4 * t + 3] / pc;
+    }
+    if (ctx->ratios_cap < ratios.size()) {
+        if (ctx->d_ratios) cudaFree(ctx->d_ratios);
+        ctx->d_ratios = nullptr; ctx->ratios_cap = 0;
+        CK(cudaMalloc(&ctx->d_ratios, ratios.size() * 4));
+        ctx->ratios_cap = ratios.size();
+    }
+    CK(cudaMemcpyAsync(ctx->d_ratios, ratios.data(), ratios.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    BootDev g;
+    g.ratios = ctx->d_ratios; g.nret = nret; g.block_len = block_len; g.s0 = window_ohlc[4 * (window_len - 1) + 3];
+    g.k0 = (uint32_t)seed; g.k1 = (uint32_t)(seed >> 32); g.path_offset = path_offset;
+    const bool wide = ctx->L > 32, hl = ctx->any_hl, multiday = ctx->n_lr > 1;
+    const size_t smem = wide ? (size_t)LeanLayout<64>::kEndBoot : (size_t)LeanLayout<32>::kEndBoot;
+    const dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(((paths + 31) / 32 + kLeanWarps - 1) / kLeanWarps,
+                                                                       (int64_t)ctx->sm_count * kLeanBlocksPerSM)), 1, 1);
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    if ((rc = init_flat(ctx)) != 0) return rc;
+    for (int cc = 0; cc < (int)ctx->params.size() && paths > 0 && steps > 0; ++cc) {
+        ScanArgs A;
+        fill_args(ctx, A, cc, nullptr, nullptr, nullptr, 0, paths, steps);
+        if (!(A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0))
+            return fail(ctx, QMMX_E_UNSUPPORTED, "fused bootstrap needs stop_padding, tp_padding >= 0 and not both 0");
+        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
+#define FB(MDv, HLv, Wv, SLv)                                                                 \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, lean_fused_boot_kernel<MDv, HLv, Wv, SLv>, smem)) != 0) return rc;   \
+            lean_fused_boot_kernel<MDv, HLv, Wv, SLv><<<grid, kLeanThreads, smem, ctx->stream>>>(A, g);       \
+        } while (0)
+#define FB2(MDv, HLv, Wv) do { if (slow) FB(MDv, HLv, Wv, true); else FB(MDv, HLv, Wv, false); } while (0)
+#define FB3(MDv, HLv) do { if (wide) FB2(MDv, HLv, true); else FB2(MDv, HLv, false); } while (0)
+        if (multiday) { if (hl) FB3(true, true); else FB3(true, false); }
+        else { if (hl) FB3(false, true); else FB3(false, false); }
+#undef FB3
+#undef FB2
+#undef FB
+        ctx->launches++;
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_run_fused_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
+                             const float* window_ohlc, int32_t window_len, int32_t block_len, qmmx_agg* agg_out) {
+    int rc = qmmx_run_fused_bootstrap_async(c, seed, path_offset, paths, steps, window_ohlc, window_len, block_len);
+    if (rc != 0) return rc;
+    return qmmx_fetch_agg(c, agg_out);
+}
+
 int qmmx_run_fused_gbm(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps,
                        const qmmx_gbm* gbm, qmmx_agg* agg_out) {
     int rc = qmmx_run_fused_gbm_async(c, seed, path_offset, paths, steps, gbm);

@@ -47,6 +47,8 @@ struct LeanLayout {
     static constexpr int kMix = kPrice + LPAD * 8;                   // {float bound, uint32 lo | hi << 8} [kMaxMixed]
     static constexpr int kMask = kMix + kMaxMixed * 8;               // uint32 [kSmemDays][LPAD]: per-day logistic masks (MULTIDAY)
     static constexpr int kEnd = kMask + kSmemDays * LPAD * 4;
+    static constexpr int kBoot = kEnd;                               // float [3][kMaxWindow]: bootstrap return ratios (fused bootstrap only)
+    static constexpr int kEndBoot = kBoot + 3 * kMaxWindow * 4;
     static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kWin % 8 == 0 && kMix % 8 == 0, "alignment");
 };
 inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
@@ -58,6 +60,7 @@ QMMX_LDS(uint32_t, u8, "r")
 QMMX_LDS(uint32_t, u32, "r")
 QMMX_LDS(unsigned long long, u64, "l")
 QMMX_LDS(double, f64, "d")
+QMMX_LDS(float, f32, "f")
 #undef QMMX_LDS
 template <int OFF> __device__ __forceinline__ float2 lds_f2(uint32_t a) {
     float2 v; asm("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(a), "n"(OFF)); return v; }
@@ -436,6 +439,75 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm
                     for (int u = 0; u < 4; ++u) { P = gbm_advance(g, P, z[u]); hi = fmaxf(hi, P); lo = fminf(lo, P); }
                     E.step(A, g.cents ? round_cents(P) : P, g.cents ? round_cents(hi) : hi, g.cents ? round_cents(lo) : lo, i, day.at(A, i));
                 }
+            }
+            E.finish(A);
+        }
+        __syncwarp();
+        warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.is_open());
+    }
+    __syncthreads();
+    block_flush_agg(A.flat, A.steps);
+}
+
+// ---- fused block bootstrap + scan (BASELINE config 5 without the 12 B/step round trip through HBM) ----------------
+// Same draws and the same IEEE products as gen_bootstrap_kernel (Philox counter (path id, block group, stream 1),
+// start = umulhi(r, nret), circular blocks), consumed in registers.  Bars carry no volume here: the soft veto is inert.
+template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW>
+__global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boot_kernel(const __grid_constant__ ScanArgs A, const BootDev g) {
+    typedef LeanLayout<WIDE ? 64 : 32> Y;
+    block_setup(A);
+    lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
+    {
+        float* rb = reinterpret_cast<float*>(g_cell + Y::kBoot);
+        for (int t = threadIdx.x; t < g.nret; t += blockDim.x) {
+            rb[t] = g.ratios[t]; rb[kMaxWindow + t] = g.ratios[g.nret + t]; rb[2 * kMaxWindow + t] = g.ratios[2 * g.nret + t];
+        }
+    }
+    __syncthreads();
+    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW> E;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
+    const int64_t ntiles = (A.paths + 31) / 32;
+    const int steps = A.steps, nret = g.nret, block_len = g.block_len;
+    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+        const int64_t path = tile * 32 + lane;
+        const bool active = path < A.paths;
+        E.reset(sb, path);
+        if (active) {
+            const uint64_t gid = g.path_offset + (uint64_t)path;
+            uint4 x = make_uint4(0, 0, 0, 0);
+            int start = 0, off = 0, blk = 0;
+            float S = g.s0;
+            auto draw = [&](float& hi, float& lo) {          // one bar: advances (S, off, blk)
+                if (off == 0) {
+                    if ((blk & 3) == 0) x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), (uint32_t)(blk >> 2), 1u), g.k0, g.k1);
+                    const uint32_t r = (blk & 3) == 0 ? x.x : (blk & 3) == 1 ? x.y : (blk & 3) == 2 ? x.z : x.w;
+                    start = (int)__umulhi(r, (uint32_t)nret);
+                }
+                int idx = start + off;
+                idx %= nret;
+                const uint32_t a = sb + (uint32_t)idx * 4u;
+                if (HL) { hi = __fmul_rn(S, lds_f32<Y::kBoot>(a)); lo = __fmul_rn(S, lds_f32<Y::kBoot + kMaxWindow * 4>(a)); }
+                S = __fmul_rn(S, lds_f32<Y::kBoot + 2 * kMaxWindow * 4>(a));
+                if (++off == block_len) { off = 0; ++blk; }
+            };
+            {   // prologue: close[0] and the first step whose close differs from it (DIR_UNKNOWN prefix)
+                float hi, lo, p0 = 0.f;
+                int j0 = steps;
+                for (int i = 0; i < steps && j0 == steps; ++i) {
+                    draw(hi, lo);
+                    if (i == 0) p0 = S; else if (S != p0) j0 = i;
+                }
+                E.prologue(p0, j0);
+                S = g.s0; start = 0; off = 0; blk = 0;
+            }
+            DayTracker<MULTIDAY> day;
+            day.init(A);
+#pragma unroll 2
+            for (int i = 0; i < steps; ++i) {
+                float hi = 0.f, lo = 0.f;
+                draw(hi, lo);
+                E.step(A, S, hi, lo, i, day.at(A, i));
             }
             E.finish(A);
         }

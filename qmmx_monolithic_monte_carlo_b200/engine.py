@@ -67,6 +67,8 @@ def load_library(path: Optional[str] = None):
         "qmmx_run_fused_gbm": (C.c_int, [vp, u64, u64, i64, i32, C.POINTER(abi.Gbm), vp]),
         "qmmx_run_scan_async": (C.c_int, [vp]),
         "qmmx_run_fused_gbm_async": (C.c_int, [vp, u64, u64, i64, i32, C.POINTER(abi.Gbm)]),
+        "qmmx_run_fused_bootstrap": (C.c_int, [vp, u64, u64, i64, i32, vp, i32, i32, vp]),
+        "qmmx_run_fused_bootstrap_async": (C.c_int, [vp, u64, u64, i64, i32, vp, i32, i32]),
         "qmmx_fetch_agg": (C.c_int, [vp, vp]),
         "qmmx_agg_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "qmmx_agg_unpack": (C.c_int, [vp, vp, C.c_int, vp]),
@@ -324,6 +326,18 @@ class MCEngine:
 
     def run_fused_gbm_async(self, seed, path_offset, paths, steps, gbm: "abi.Gbm"):
         self._ck(self._L.qmmx_run_fused_gbm_async(self._h, seed, path_offset, paths, steps, C.byref(gbm)))
+
+    def run_fused_bootstrap(self, seed, path_offset, paths, steps, window_ohlc, block_len):
+        """Block-bootstrap the candle window and scan in one kernel (the bars of gen_bootstrap, never written)."""
+        w = np.ascontiguousarray(window_ohlc, dtype=np.float32).reshape(-1, 4)
+        aggs = self._aggs()
+        self._ck(self._L.qmmx_run_fused_bootstrap(self._h, seed, path_offset, paths, steps, _ptr(w), len(w), block_len,
+                                                  C.cast(aggs, C.c_void_p)))
+        return [MCResult(a) for a in aggs]
+
+    def run_fused_bootstrap_async(self, seed, path_offset, paths, steps, window_ohlc, block_len):
+        w = np.ascontiguousarray(window_ohlc, dtype=np.float32).reshape(-1, 4)
+        self._ck(self._L.qmmx_run_fused_bootstrap_async(self._h, seed, path_offset, paths, steps, _ptr(w), len(w), block_len))
 
     def fetch_agg(self):
         aggs = self._aggs()

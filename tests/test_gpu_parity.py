@@ -510,3 +510,29 @@ def test_gpu_bootstrap_volume_plane_and_veto(eng):
     eng.gen_bootstrap(9, 11, paths, steps, window, 5)           # without volume: the plane is dropped
     with pytest.raises(E.QmmxError):
         eng.download_volume(paths, steps)
+
+
+@pytest.mark.parametrize("hl", [True, False], ids=["hl", "close"])
+def test_gpu_fused_bootstrap_equals_generate_then_scan(eng, hl):
+    """qmmx_run_fused_bootstrap draws the bars of qmmx_gen_bootstrap (checked against the oracle generator above)
+    and walks them in registers: every aggregate equals generate-then-scan, multi-day LR tables included."""
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    rng = np.random.default_rng(4)
+    lr, pol = _lr_tables(rng, 3)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=hl)
+    configure(eng, price, solid, params, lr)
+    paths, steps = 50_001, 3 * 390
+    fused = eng.run_fused_bootstrap(9, 7, paths, steps, window, 5)[0].agg
+    eng.gen_bootstrap(9, 7, paths, steps, window, 5)
+    scan = eng.run_scan()[0].agg
+    assert scan.n_trades > 0
+    assert_agg_equal(fused, scan, sums_rel=1e-12)
+    # sharding: two shards of the fused run add up to the whole
+    a = eng.run_fused_bootstrap(9, 7, 20_000, steps, window, 5)[0].agg
+    b = eng.run_fused_bootstrap(9, 7 + 20_000, paths - 20_000, steps, window, 5)[0].agg
+    assert list(fused.entry_hist) == [x + y for x, y in zip(a.entry_hist, b.entry_hist)]
+    assert list(fused.pnl_hist) == [x + y for x, y in zip(a.pnl_hist, b.pnl_hist)]
