@@ -53,6 +53,8 @@ def lib():
         L.oq_gen_bootstrap_v.restype = C.c_int
         L.oq_gen_bootstrap_v.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                          C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oq_regime_series.restype = None
+        L.oq_regime_series.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
         L.oq_volume_slope.restype = C.c_double
         L.oq_volume_slope.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int]
         L.oq_philox4x32_10.restype = None
@@ -95,6 +97,17 @@ def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=N
     if rc != 0:
         raise RuntimeError(f"oq_run_paths failed: {rc}")
     return dict(agg=agg, codes=codes, trades=trades, counts=counts)
+
+
+def regime_series(close, volume):
+    """uint8 [steps][paths]: AccumulationBreakoutGuard regime seen by evaluate_entry at every tick."""
+    close = np.ascontiguousarray(close, dtype=np.float32)
+    volume = np.ascontiguousarray(volume, dtype=np.float32)
+    steps, paths = close.shape
+    out = np.empty((paths, steps), dtype=np.uint8)
+    for j in range(paths):
+        lib().oq_regime_series(_ptr(close), _ptr(volume), paths, j, steps, out[j].ctypes.data_as(C.c_void_p))
+    return np.ascontiguousarray(out.T)
 
 
 def gen_gbm(seed, path_offset, paths, steps, gbm: "abi.Gbm", ohlc=False):

@@ -171,6 +171,76 @@ def volume_slope(vols: Sequence[float], window: int = 6) -> float:
     return (v2 - v1) / (abs(v1) + 1e-9)
 
 
+class RegimeGuard:
+    """AccumulationBreakoutGuard (M:1241-1356) as the live loop feeds it: `ingest_tick` (M:1857-1883, called at
+    M:2932 before `evaluate_entry`) rolls one-tick minute bars, so at tick i the guard has seen bars 0..i-1 with
+    o = h = l = c = that tick's price and v = that tick's volume [CHOICE: one tick per minute, Appendix A].
+
+    Regimes: 0 unknown, 1 accumulation, 2 breakout_up, 3 breakout_down.  `allow_trade` (M:1338-1349) blocks SHORTs
+    in breakout_up and LONGs in breakout_down (code 904, M:1652-1666).
+
+    LevelTouchMemory (M:1112-1239) is consulted in the accumulation regime (M:1589-1621) but is inert in the
+    reference: `_on_minute_close` passes `levels=self.levels_cache` (dicts) to `register_touch_if_any`, whose
+    `round(float(L), 2)` raises TypeError on the first level inside a `try/except: pass` (M:1838-1851), so no touch
+    and no edge tap is ever recorded; `edge_fatigued` returns None and `allow_trade_at` returns (True, "ok", 1.0).
+    tests/test_oracle_vs_reference.py::test_touch_memory_is_inert_in_the_reference pins that.
+    """
+    UNKNOWN, ACCUMULATION, BREAKOUT_UP, BREAKOUT_DOWN = 0, 1, 2, 3
+
+    def __init__(self):
+        self.bars: List[tuple] = []          # (ts_ms, high, low, close, volume); deque(maxlen=600) >= the 61 ever read
+        self.regime = 0
+        self.box_low: Optional[float] = None
+        self.box_high: Optional[float] = None
+        self.inside = 0
+
+    def push(self, ts_ms: int, h: float, l: float, c: float, v: float) -> None:
+        self.bars.append((ts_ms, h, l, c, v))
+        if len(self.bars) > 600:
+            self.bars = self.bars[-600:]
+        window = [b for b in self.bars if ts_ms - b[0] <= 60 * 60 * 1000]          # M:1273-1278
+        if len(window) < 30:                                                         # M:1288-1292
+            self.regime, self.box_low, self.box_high, self.inside = 0, None, None, 0
+            return
+        vols = [b[4] for b in window]
+        close = window[-1][3]
+        box_low, box_high = min(b[2] for b in window), max(b[1] for b in window)
+        thresh = close * (18 / 10000.0)                                              # compression_bp = 18
+        ma_s = sum(vols[-5:]) / float(5)                                             # _ma, M:1280-1284 (len >= 30)
+        ma_l = sum(vols[-20:]) / float(20)
+        breakout = self.regime in (2, 3)
+        if box_high - box_low <= max(1e-6, thresh):                                  # M:1311-1322
+            if not breakout:
+                self.regime = 1
+            self.box_low, self.box_high = box_low, box_high
+        elif not breakout:
+            self.regime = 0
+        if self.box_low is not None and ma_s and ma_l:                               # M:1325-1334
+            if close > self.box_high + 1e-6 and ma_s > 1.40 * ma_l:
+                self.regime, self.inside = 2, 0
+            elif close < self.box_low - 1e-6 and ma_s > 1.40 * ma_l:
+                self.regime, self.inside = 3, 0
+        if self.regime in (2, 3) and self.box_low is not None:                       # M:1337-1344
+            if self.box_low <= close <= self.box_high:
+                self.inside += 1
+                if self.inside >= 3:
+                    self.regime = 1
+            else:
+                self.inside = 0
+
+
+def regime_series(close: Sequence[float], volume: Sequence[float]) -> List[int]:
+    """Regime seen by `evaluate_entry` at every tick (the guard has been fed bars 0..i-1)."""
+    g = RegimeGuard()
+    out = []
+    for i in range(len(close)):
+        if i >= 1:
+            c = float(close[i - 1])
+            g.push(60000 * (i - 1), c, c, c, float(volume[i - 1] or 0.0))
+        out.append(g.regime)
+    return out
+
+
 def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
              lr: Optional[Sequence[Optional[LRModel]]] = None,
              policy: Optional[Sequence[dict]] = None,
@@ -202,10 +272,14 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
         w_rules, w_ml, s = 1.0, 0.0, 1.0
     w_rules, w_ml = w_rules / s, w_ml / s
 
+    guard = RegimeGuard() if volume is not None else None    # always on in the reference; inert without volume
     for i, p in enumerate(close):
         p = float(p)
         now = 60000 * i
         day = i // P.steps_per_day
+        if guard is not None and i >= 1:                          # ingest_tick closes bar i-1 (M:2932, M:1864-1870)
+            cb = float(close[i - 1])
+            guard.push(60000 * (i - 1), cb, cb, cb, float(volume[i - 1] or 0.0))
         code = None
         ok_extras = None
         # ---- evaluate_entry (first matching rule returns) ----
@@ -256,7 +330,10 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
                             else:
                                 stop, target, side = lp + P.stop_padding, lp - P.tp_padding, 1
                             code = E["OK"]
-                            if P.enable_veto:                         # M:1678-1705
+                            if guard is not None and ((guard.regime == 2 and side == 1) or
+                                                      (guard.regime == 3 and side == 0)):
+                                code = E["ACC_BREAKOUT_GATE"]         # M:1652-1666 (int code 904)
+                            if code == E["OK"] and P.enable_veto:     # M:1678-1705
                                 vs = volume_slope(volume[max(0, i - 239):i + 1]) if volume is not None else 0.0
                                 confl = sum(1 for lv in levels if abs(lv.price - lp) <= 0.15) >= 2
                                 if not (abs(vs) < 0.05 and not confl):

@@ -68,6 +68,54 @@ static double volume_slope_at(const float* volume, int64_t paths, int64_t path, 
     if (v1 == 0 && v2 == 0) return 0.0;
     return (v2 - v1) / (fabs(v1) + 1e-9);
 }
+/* AccumulationBreakoutGuard (M:1241-1356) as the live loop feeds it (ingest_tick M:1857-1883 at M:2932): one-tick
+ * minute bars, o = h = l = c; restated in oracle/headless.py:RegimeGuard.  Regimes 0 unknown, 1 accumulation,
+ * 2 breakout_up, 3 breakout_down. */
+typedef struct { int regime, inside, has_box; double box_low, box_high; } guard_t;
+
+static double vol_at(const float* volume, int64_t paths, int64_t path, int j) {
+    const double x = (double)volume[(int64_t)j * paths + path];
+    return x == 0.0 ? 0.0 : x;                        /* `float(volume or 0.0)` */
+}
+
+static void guard_push(guard_t* G, const float* close, const float* volume, int64_t paths, int64_t path, int j) {
+    const int n = j + 1 < 61 ? j + 1 : 61;            /* bars with t_end - t <= 60 min */
+    if (n < 30) { G->regime = 0; G->inside = 0; G->has_box = 0; return; }
+    double lo = INFINITY, hi = -INFINITY;
+    for (int k = j - n + 1; k <= j; ++k) {
+        const double c = (double)close[(int64_t)k * paths + path];
+        if (c < lo) lo = c;
+        if (c > hi) hi = c;
+    }
+    const double c = (double)close[(int64_t)j * paths + path];
+    const double thresh = c * (18 / 10000.0);
+    double v[20];
+    for (int k = 0; k < 20; ++k) v[k] = vol_at(volume, paths, path, j - 19 + k);
+    const double ma_s = sum_py312(v + 15, 5) / 5.0, ma_l = sum_py312(v, 20) / 20.0;
+    const int breakout = G->regime == 2 || G->regime == 3;
+    if (hi - lo <= (1e-6 > thresh ? 1e-6 : thresh)) {
+        if (!breakout) G->regime = 1;
+        G->box_low = lo; G->box_high = hi; G->has_box = 1;
+    } else if (!breakout) G->regime = 0;
+    if (G->has_box && ma_s != 0.0 && ma_l != 0.0) {
+        if (c > G->box_high + 1e-6 && ma_s > 1.40 * ma_l) { G->regime = 2; G->inside = 0; }
+        else if (c < G->box_low - 1e-6 && ma_s > 1.40 * ma_l) { G->regime = 3; G->inside = 0; }
+    }
+    if ((G->regime == 2 || G->regime == 3) && G->has_box) {
+        if (G->box_low <= c && c <= G->box_high) { if (++G->inside >= 3) G->regime = 1; }
+        else G->inside = 0;
+    }
+}
+
+/* regime seen by evaluate_entry at every tick of one path (the guard has been fed bars 0..i-1) */
+void oq_regime_series(const float* close, const float* volume, int64_t paths, int64_t path, int32_t steps, uint8_t* out) {
+    guard_t G; memset(&G, 0, sizeof(G));
+    for (int i = 0; i < steps; ++i) {
+        if (i >= 1) guard_push(&G, close, volume, paths, path, i - 1);
+        out[i] = (uint8_t)G.regime;
+    }
+}
+
 double oq_volume_slope(const float* volume, int64_t paths, int64_t path, int i) { return volume_slope_at(volume, paths, path, i); }
 
 /* M:20-26 */
@@ -143,8 +191,10 @@ static void run_range(job_t* J) {
         int ntr = 0;
         memset(touch, 0, sizeof(touch)); memset(latch, 0, sizeof(latch));
         double p = 0.0;
+        guard_t G; memset(&G, 0, sizeof(G));
         for (int i = 0; i < J->steps; ++i) {
             p = (double)J->close[(int64_t)i * J->paths + path];
+            if (J->volume && i >= 1) guard_push(&G, J->close, J->volume, J->paths, path, i - 1);   /* ingest_tick, M:2932 */
             const int64_t now = 60000LL * i;
             const int day = i / P->steps_per_day;
             int code = -1, ok = 0, side = 0, k = 0;
@@ -181,7 +231,9 @@ static void run_range(job_t* J) {
                                 if (d == 1) { stop = lp - P->stop_padding; target = lp + P->tp_padding; side = 0; }
                                 else { stop = lp + P->stop_padding; target = lp - P->tp_padding; side = 1; }
                                 code = QMMX_OK_ENTRY;
-                                if (veto) {        /* M:1678-1705 + _soft_veto M:1773-1794; slope 0 without per-bar volume */
+                                if (J->volume && ((G.regime == 2 && side == 1) || (G.regime == 3 && side == 0)))
+                                    code = QMMX_ACC_BREAKOUT_GATE;         /* M:1652-1666 (int code 904) */
+                                if (code == QMMX_OK_ENTRY && veto) {        /* M:1678-1705 + _soft_veto M:1773-1794; slope 0 without per-bar volume */
                                     const double vs = volume_slope_at(J->volume, J->paths, path, i);
                                     int confl = 0;
                                     for (int j = 0; j < L; ++j) if (fabs(J->lprice[j] - lp) <= 0.15) ++confl;

@@ -177,6 +177,9 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
         now_ms = 60000 * i
         eng.state.last_ts_ms = now_ms  # always fresh (Appendix A [CHOICE])
         if volume is not None:
+            # the live loop feeds every tick to ingest_tick before evaluate_entry (M:2932): it rolls the one-tick minute
+            # bar i-1 into acc_guard / touchmem (M:1857-1883, M:1813-1855)
+            eng.ingest_tick(now_ms, price, float(volume[i]))
             lo = max(0, i - 239)
             eng.recent_bars = [dict(t=60000 * j, o=float(closes[j]), h=float(closes[j]), l=float(closes[j]),
                                     c=float(closes[j]), v=float(volume[j])) for j in range(lo, i + 1)]
@@ -188,7 +191,7 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
         eng.state.last_price = price
         if prev_price is not None and price != prev_price:
             eng.state.last_direction = "up" if price > prev_price else "down"
-        step_code = code if not isinstance(code, int) else f"INT_{code}"
+        step_code = code if not isinstance(code, int) else ("ACC_BREAKOUT_GATE" if code == 904 else f"INT_{code}")
         if step_code == "CONF_LOW":
             # sub-reason lives in the policy_events row the gate just wrote (M:1629, 1733, 1746)
             row = conn.execute("SELECT features_json FROM policy_events ORDER BY id DESC LIMIT 1").fetchone()
@@ -249,7 +252,9 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
                            level=pos["level"], reason="OPEN", entry=pos["entry"], exit=last,
                            pnl=0.0, mtm=mtm))
     return dict(codes=codes, trades=trades,
-                touch_counts=dict(eng.state.level_touch_counts))
+                touch_counts=dict(eng.state.level_touch_counts),
+                touchmem_touches=dict(eng.touchmem.touch), touchmem_edge_taps=len(eng.touchmem.edge_taps),
+                regime=eng.acc_guard.regime)
 
 
 def run_reference_monte_carlo(bars, levels, settings=None, **kw):

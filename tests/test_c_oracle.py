@@ -174,3 +174,37 @@ def test_bootstrap_generator_carries_window_volume():
     idx = (v - 1000).astype(int)                       # the window bar each step was drawn from
     prev = np.vstack([np.full((1, 16), window[-1, 3], dtype=np.float32), c[:-1]])
     assert np.array_equal(c, prev * (window[idx, 3] / window[idx - 1, 3]).astype(np.float32))
+
+
+def breakout_paths(n, seed):
+    """Quiet stretches (60-minute range under 18 bp) broken by jumps on a volume spike: every regime occurs."""
+    rng = np.random.default_rng(seed)
+    closes = np.empty((390, n), dtype=np.float32)
+    vol = np.empty((390, n), dtype=np.float32)
+    for j in range(n):
+        c = 646.0 + rng.uniform(0, 5) + np.cumsum(rng.normal(0, 0.02, 390))
+        v = rng.uniform(1e4, 2e4, 390)
+        for t0 in sorted(rng.integers(60, 360, size=3)):
+            c[t0:] += rng.choice([-1.0, 1.0]) * rng.uniform(1.3, 2.5)
+            if rng.random() < 0.8:
+                v[max(0, t0 - 2):t0 + 6] *= rng.uniform(3, 8)
+        closes[:, j], vol[:, j] = c, v
+    vol[np.random.default_rng(seed + 1).random(size=vol.shape) < 0.01] = 0.0
+    return closes, vol
+
+
+def test_c_oracle_regime_guard_matches_headless():
+    """AccumulationBreakoutGuard regime per tick and the 904 gate, C restatement == headless.py."""
+    closes, vol = breakout_paths(40, 5)
+    reg = CO.regime_series(closes, vol)
+    assert set(np.unique(reg)) == {0, 1, 2, 3}
+    for j in range(40):
+        assert reg[:, j].tolist() == H.regime_series(closes[:, j], vol[:, j]), j
+    lv = H.sort_levels(F.levels_30())
+    kw = dict(contact_prox=0.1, cooldown_s=60, enable_veto=True)
+    r = CO.run_paths(closes, [x.price for x in lv], [x.solid for x in lv], abi.make_params(**kw), volume=vol,
+                     want_codes=True, max_trades=64, n_threads=2)
+    for j in range(40):
+        o = H.run_path(closes[:, j], lv, H.Params(**kw), volume=[float(x) for x in vol[:, j]])
+        assert o.codes == r["codes"][:, j].tolist(), j
+    assert r["agg"].entry_hist[abi.ENTRY_CODES.index("ACC_BREAKOUT_GATE")] >= 5

@@ -60,6 +60,48 @@ def test_volume_soft_veto_against_reference():
     assert sum(1 for c in codes if H.ENTRY_CODES[c].startswith("VETO_CONTRA")) >= 3
 
 
+def _breakout_paths(n, seed):
+    """Quiet stretches (60-minute range under 18 bp) broken by jumps on a volume spike: every regime occurs."""
+    rng = np.random.default_rng(seed)
+    closes = np.empty((390, n), dtype=np.float32)
+    vol = np.empty((390, n), dtype=np.float32)
+    for j in range(n):
+        c = 646.0 + rng.uniform(0, 5) + np.cumsum(rng.normal(0, 0.02, 390))
+        v = rng.uniform(1e4, 2e4, 390)
+        for t0 in sorted(rng.integers(60, 360, size=3)):
+            c[t0:] += rng.choice([-1.0, 1.0]) * rng.uniform(1.3, 2.5)
+            if rng.random() < 0.8:
+                v[max(0, t0 - 2):t0 + 6] *= rng.uniform(3, 8)
+        closes[:, j], vol[:, j] = c, v
+    return closes, vol
+
+
+def test_regime_guard_against_reference():
+    """AccumulationBreakoutGuard fed through ingest_tick; code 904 blocks counter-trend entries."""
+    closes, vol = _breakout_paths(12, 21)
+    params = dict(contact_prox=0.1, cooldown_s=60, enable_veto=True)
+    _check(F.levels_30(), params, closes, volume=vol)
+    lv = H.sort_levels(F.levels_30())
+    n904, regimes = 0, set()
+    for j in range(closes.shape[1]):
+        o = H.run_path(closes[:, j], lv, H.Params(**params), volume=[float(x) for x in vol[:, j]])
+        n904 += sum(1 for c in o.codes if H.ENTRY_CODES[c] == "ACC_BREAKOUT_GATE")
+        regimes |= set(H.regime_series(closes[:, j], vol[:, j]))
+    assert n904 >= 3 and regimes == {0, 1, 2, 3}
+
+
+def test_touch_memory_is_inert_in_the_reference():
+    """LevelTouchMemory never records a touch or an edge tap: register_touch_if_any gets dict levels and fails inside
+    its try/except (M:1838-1851), so the accumulation-regime gates of M:1589-1621 cannot fire."""
+    closes, vol = _breakout_paths(2, 22)
+    for j in range(2):
+        ref = rh.drive_reference_path(closes[:, j], F.levels_30(), settings_for(dict(contact_prox=0.1)),
+                                      volume=[float(x) for x in vol[:, j]])
+        assert ref["touchmem_edge_taps"] == 0
+        assert all(r["count"] == 0 for r in ref["touchmem_touches"].values())
+        assert not any(c.startswith("VETO_EDGE") or c.startswith("VETO_BOUNCE") or c.startswith("VETO_LEVEL") for c in ref["codes"])
+
+
 def test_lr_contract_matches_sklearn_predict_proba():
     rng = np.random.default_rng(5)
     for _ in range(50):
