@@ -192,9 +192,13 @@ int  qmmx_device_bars(qmmx_ctx* ctx, float** d_close, float** d_high, float** d_
 int  qmmx_pin_host(qmmx_ctx* ctx, void* ptr, size_t bytes);
 int  qmmx_unpin_host(qmmx_ctx* ctx, void* ptr);
 int  qmmx_download_bars(qmmx_ctx* ctx, float* close, float* high, float* low);
-/* per-bar volume of the resident bars ([step][path] fp32, same shape; NULL drops it).  Only the soft veto
- * (QMMX_F_ENABLE_VETO: _calc_volume_slope over the last 6 bars, M:1796-1811, then _soft_veto, M:1773-1794) reads
- * it; without volume the slope is 0 and the veto never fires, which is the reference on its own data. */
+/* per-bar volume of the resident bars ([step][path] fp32, same shape; NULL drops it).  Two gates read it:
+ *  - the soft veto (QMMX_F_ENABLE_VETO: _calc_volume_slope over the last 6 bars, M:1796-1811, _soft_veto M:1773-1794);
+ *  - the AccumulationBreakoutGuard regime gate (always on in the reference: 60-minute box, 5/20-bar volume means,
+ *    M:1241-1356, fed by ingest_tick M:1857-1883; counter-trend entries after a confirmed break get
+ *    QMMX_ACC_BREAKOUT_GATE, M:1652-1666).  The regime plane is computed once, when the volume arrives.
+ * Without volume the slope is 0 and no break is ever confirmed: both gates are inert, which is the reference on
+ * its own data. */
 int  qmmx_upload_volume(qmmx_ctx* ctx, const float* volume, int64_t paths, int32_t steps);
 int  qmmx_download_volume(qmmx_ctx* ctx, float* volume);
 /* volume of the window bars ([window_len] fp32, NULL clears): the next qmmx_gen_bootstrap with the same

@@ -34,6 +34,7 @@ constexpr uint32_t kCbHasMl = 1u << 16, kCbHasProb = 1u << 17;   // internal Dev
 // Kernel parameters of one scan launch = one parameter combo over one set of paths (constant bank).
 struct ScanArgs {
     const float* close; const float* high; const float* low;   // [steps][pitch] fp32
+    const uint8_t* regime;        // AccumulationBreakoutGuard regime per tick [steps][pitch] (regime_kernel), or null
     const float* vol;             // per-bar volume [steps][pitch], or null: the soft veto is inert (M:1796-1811)
     int64_t pitch, paths;
     int32_t steps, combo_index;
@@ -144,6 +145,17 @@ __device__ __noinline__ bool blend_fails(const ScanArgs* A, int k, float pf, int
     const bool fails = blended < A->combo.qmin;
     if (fails) smem_inc(&g_S.u[U_ENTRY + QMMX_COMBINED_LOW]);
     return fails;
+}
+
+// rare: accumulation / breakout regime gate (M:1652-1666, int code 904): counter-trend entries are blocked after a
+// volume-confirmed break of the 60-minute box.  Returns 0 or the reason code.
+__device__ __noinline__ int regime_gate(const ScanArgs* A, int side, int i, int64_t path) {
+    const int r = __ldg(A->regime + (size_t)i * (size_t)A->pitch + path);
+    if ((r == 2 && side == 1) || (r == 3 && side == 0)) {
+        smem_inc(&g_S.u[U_ENTRY + QMMX_ACC_BREAKOUT_GATE]);
+        return QMMX_ACC_BREAKOUT_GATE;
+    }
+    return 0;
 }
 
 // builtin sum() of n <= 3 floats under CPython >= 3.12 (Neumaier-compensated), as _calc_volume_slope uses it
@@ -296,6 +308,7 @@ struct PathEngine {
         const float2 cp = g_S.cpass[min(tc, 3) - 1][k];
         if (!(pf >= cp.x && pf <= cp.y)) { c_gate += 1u << 16; return QMMX_CONF_LOW; }   // M:1628
         const int side = dir - 1;                                            // M:1645: up -> long(0), down -> short(1)
+        if (A.regime) { const int rc = regime_gate(&A, side, i, path); if (rc) return rc; }       // M:1652-1666
         if (A.vol) { const int vc = veto_check(&A, k, pf, side, i, path); if (vc) return vc; }   // M:1678-1705
         if (A.combo.flags & QMMX_F_USE_BLEND) {                              // M:1730-1742
             if (blend_fails(&A, k, pf, tc, side, day_off)) return QMMX_COMBINED_LOW;

@@ -369,6 +369,69 @@ __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
     }
 }
 
+// ---- AccumulationBreakoutGuard regime per tick (M:1241-1356, fed by ingest_tick M:1857-1883 at M:2932) -------------
+// The regime depends on the bars only, never on the engine state, so it is a pre-pass over the resident close and
+// volume planes: reg[i][path] = regime evaluate_entry sees at tick i (the guard has been fed the one-tick minute bars
+// 0..i-1, o = h = l = c).  0 unknown, 1 accumulation, 2 breakout_up, 3 breakout_down; restated from
+// oracle/headless.py:RegimeGuard.  The 61-bar box and the 5/20-bar volume means are recomputed per bar exactly as
+// the reference does (min/max are order-free; the means are CPython >= 3.12 compensated sums), reading rows that
+// are L1/L2-resident (a warp re-reads the 61 lines above its cursor).
+__device__ __forceinline__ void neumaier_add(double& f, double& c, double v) {
+    const double t = f + v;
+    if (fabs(f) >= fabs(v)) c += (f - t) + v; else c += (v - t) + f;
+    f = t;
+}
+
+__global__ void __launch_bounds__(kThreads) regime_kernel(const float* __restrict__ close, const float* __restrict__ vol,
+                                                          uint8_t* __restrict__ reg, int64_t pitch, int64_t paths, int32_t steps) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const size_t P = (size_t)pitch;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < paths; q += stride) {
+        int regime = 0, inside = 0;
+        bool has_box = false;
+        float box_lo = 0.f, box_hi = 0.f;
+        if (steps > 0) reg[q] = 0;
+        for (int j = 0; j + 1 < steps; ++j) {
+            const int n = j + 1 < 61 ? j + 1 : 61;                 // bars with t_end - t <= 60 min (M:1273-1278)
+            if (n < 30) { regime = 0; inside = 0; has_box = false; }   // M:1288-1292
+            else {
+                float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+                const float* col = close + (size_t)(j - n + 1) * P + q;
+                for (int k = 0; k < n; ++k) { const float c = __ldg(col + (size_t)k * P); lo = fminf(lo, c); hi = fmaxf(hi, c); }
+                const float cf = __ldg(close + (size_t)j * P + q);
+                const double c = (double)cf;
+                const double thresh = c * (18 / 10000.0);          // compression_bp = 18
+                // volume means over the last 5 and 20 bars, oldest first (`float(v or 0.0)`: x + 0.0 turns -0.0 into +0.0)
+                const float* vcol = vol + (size_t)(j - 19) * P + q;
+                double fs = 0.0, cs = 0.0, fl = 0.0, cl = 0.0;
+#pragma unroll
+                for (int k = 0; k < 20; ++k) {
+                    const double v = (double)__ldg(vcol + (size_t)k * P) + 0.0;
+                    if (k == 0) fl = 0.0 + v; else neumaier_add(fl, cl, v);
+                    if (k == 15) fs = 0.0 + v; else if (k > 15) neumaier_add(fs, cs, v);
+                }
+                if (cl != 0.0 && isfinite(cl)) fl += cl;
+                if (cs != 0.0 && isfinite(cs)) fs += cs;
+                const double ma_s = fs / 5.0, ma_l = fl / 20.0;
+                const bool breakout = regime >= 2;
+                if ((double)hi - (double)lo <= (1e-6 > thresh ? 1e-6 : thresh)) {     // M:1311-1322
+                    if (!breakout) regime = 1;
+                    box_lo = lo; box_hi = hi; has_box = true;
+                } else if (!breakout) regime = 0;
+                if (has_box && ma_s != 0.0 && ma_l != 0.0) {                          // M:1325-1334
+                    if (c > (double)box_hi + 1e-6 && ma_s > 1.40 * ma_l) { regime = 2; inside = 0; }
+                    else if (c < (double)box_lo - 1e-6 && ma_s > 1.40 * ma_l) { regime = 3; inside = 0; }
+                }
+                if (regime >= 2 && has_box) {                                         // M:1337-1344
+                    if ((double)box_lo <= c && c <= (double)box_hi) { if (++inside >= 3) regime = 1; }
+                    else inside = 0;
+                }
+            }
+            reg[(size_t)(j + 1) * P + q] = (uint8_t)regime;
+        }
+    }
+}
+
 // merge the all-gathered reduction buffers of n_parts ranks: SUM u64 counters, SUM f64 sums, MAX extrema
 __global__ void merge_flat_kernel(unsigned long long* __restrict__ flat, const unsigned long long* __restrict__ parts,
                                   int n_parts, int n_slots_total) {

@@ -46,6 +46,7 @@ struct qmmx_ctx {
     // resident bars
     float *d_close = nullptr, *d_high = nullptr, *d_low = nullptr;
     float* d_vol = nullptr;                 // per-bar volume of the resident bars (library-owned), or null
+    uint8_t* d_regime = nullptr;            // AccumulationBreakoutGuard regime per tick (regime_kernel), lives with d_vol
     std::vector<float> boot_vol;            // window volumes for the next qmmx_gen_bootstrap
     bool own_bars = false;
     int64_t paths = 0, pitch = 0; int32_t steps = 0;
@@ -73,7 +74,11 @@ int fail(qmmx_ctx* c, int code, const std::string& msg) {
 
 inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
-void free_volume(qmmx_ctx* c) { if (c->d_vol) cudaFree(c->d_vol); c->d_vol = nullptr; }
+void free_volume(qmmx_ctx* c) {
+    if (c->d_vol) cudaFree(c->d_vol);
+    if (c->d_regime) cudaFree(c->d_regime);
+    c->d_vol = nullptr; c->d_regime = nullptr;
+}
 
 void free_bars(qmmx_ctx* c) {
     free_volume(c);
@@ -201,6 +206,7 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     const DevCombo& D = ctx->h_combos[c];
     A.close = cl; A.high = h; A.low = l;
     A.vol = (cl && cl == ctx->d_close && (D.flags & QMMX_F_ENABLE_VETO)) ? ctx->d_vol : nullptr;
+    A.regime = (cl && cl == ctx->d_close && ctx->d_vol) ? ctx->d_regime : nullptr;
     A.pitch = pitch; A.paths = paths; A.steps = steps; A.combo_index = c;
     A.tables = ctx->d_tables + D.table;
     A.flat = ctx->d_flat + (size_t)c * QMMX_AGG_SLOTS;
@@ -227,6 +233,18 @@ dim3 scan_grid(const qmmx_ctx* ctx, int64_t paths) {
 template <class K>
 int set_smem_attr(qmmx_ctx* ctx, K kernel, size_t bytes) {
     CK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return QMMX_OK;
+}
+
+// the regime plane follows the resident close + volume planes (the reference's guard is always on; without volume it
+// can never leave {unknown, accumulation}, which block nothing)
+int compute_regime(qmmx_ctx* ctx) {
+    if (!ctx->d_vol || !ctx->d_close || ctx->paths == 0 || ctx->steps == 0) return QMMX_OK;
+    if (!ctx->d_regime) CK(cudaMalloc(&ctx->d_regime, (size_t)ctx->pitch * (size_t)ctx->steps));
+    const int64_t blocks = std::min<int64_t>((ctx->paths + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+    regime_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(ctx->d_close, ctx->d_vol, ctx->d_regime, ctx->pitch, ctx->paths, ctx->steps);
+    ctx->launches++;
+    CK(cudaGetLastError());
     return QMMX_OK;
 }
 
@@ -286,7 +304,7 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
         const bool parity = par && c == 0;
         if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
-        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE) || A.vol != nullptr;
+        const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE) || A.vol != nullptr || A.regime != nullptr;
         // the lean exit block assumes a single price cannot hit both thresholds: stop below / target above the level
         const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
         if (lean && band_ok) {
@@ -550,6 +568,8 @@ int qmmx_upload_volume(qmmx_ctx* c, const float* volume, int64_t paths, int32_t 
     if (!ctx->d_vol) CK(cudaMalloc(&ctx->d_vol, (size_t)ctx->pitch * (size_t)steps * sizeof(float)));
     const size_t w = (size_t)paths * 4, dp = (size_t)ctx->pitch * 4;
     CK(cudaMemcpy2DAsync(ctx->d_vol, dp, volume, w, w, steps, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = compute_regime(ctx);
+    if (rc != 0) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     return QMMX_OK;
 }
@@ -634,6 +654,7 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
         cudaEventRecord(ctx->ev1, ctx->stream);
     }
     if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("gen_bootstrap: ") + cudaGetErrorString(e));
+    if (with_vol && (rc = compute_regime(ctx)) != 0) return rc;
     ctx->ran = true;
     return QMMX_OK;
 }

@@ -215,6 +215,7 @@ struct LeanEngine {
             c_gate += over ? 1u : (1u << 16);                     // M:1579 / M:1628
             return over ? QMMX_LEVEL_OVERTOUCHED : QMMX_CONF_LOW;
         }
+        if (SLOW && A.regime) { const int rc = regime_gate(&A, side, i, path); if (rc) return rc; }      // M:1652-1666
         if (SLOW && A.vol) { const int vc = veto_check(&A, k, pf, side, i, path); if (vc) return vc; }   // M:1678-1705
         if (neg) { c_ml += 1u; return QMMX_ML_CONF_LOW; }         // M:1745-1755 (single day, AND mode)
         if (SLOW && (A.combo.flags & QMMX_F_USE_BLEND)) {         // M:1730-1742

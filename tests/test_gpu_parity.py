@@ -536,3 +536,27 @@ def test_gpu_fused_bootstrap_equals_generate_then_scan(eng, hl):
     b = eng.run_fused_bootstrap(9, 7 + 20_000, paths - 20_000, steps, window, 5)[0].agg
     assert list(fused.entry_hist) == [x + y for x, y in zip(a.entry_hist, b.entry_hist)]
     assert list(fused.pnl_hist) == [x + y for x, y in zip(a.pnl_hist, b.pnl_hist)]
+
+
+@pytest.mark.parametrize("variant", ["lean", "first_generation(tiny)"])
+def test_gpu_regime_guard_gate(eng, variant):
+    """the AccumulationBreakoutGuard regime plane (regime_kernel pre-pass over close + volume) and the
+    904 gate (M:1652-1666) between the confidence gate and the soft veto; against the oracle, which is pinned
+    against the reference driven through ingest_tick."""
+    from tests.test_c_oracle import breakout_paths
+    closes, vol = breakout_paths(1536, 8)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    params = abi.make_params(contact_prox=0.1, cooldown_s=60, enable_veto=True, tiny_prices=variant.startswith("first"))
+    configure(eng, price, solid, params, lr)
+    eng.upload_bars(closes)
+    eng.upload_volume(vol)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=closes.shape)
+    o = CO.run_paths(closes, price, solid, params, volume=vol, lr=lr, want_codes=True, max_trades=64, n_threads=8)
+    acc = abi.ENTRY_CODES.index("ACC_BREAKOUT_GATE")
+    assert o["agg"].entry_hist[acc] > 100
+    assert set(np.unique(CO.regime_series(closes[:, :64], vol[:, :64]))) == {0, 1, 2, 3}
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    assert_agg_equal(eng.run_scan()[0].agg, o["agg"])
