@@ -102,6 +102,23 @@ def test_touch_memory_is_inert_in_the_reference():
         assert not any(c.startswith("VETO_EDGE") or c.startswith("VETO_BOUNCE") or c.startswith("VETO_LEVEL") for c in ref["codes"])
 
 
+def test_target_escalation_is_inert_in_the_reference():
+    """at a target touch the live loop asks maybe_escalate_on_target (M:2988, M:3007) with the bars of
+    PriceFeed.get_minute_bars (dicts, M:2972).  ExitStrategy unpacks every bar as a (price, volume, ts) tuple
+    (M:986, M:1009), which raises on dicts inside its try/except, so it never escalates: the exit is always TARGET."""
+    q, conn, eng = rh.make_engine(F.levels_30(), settings_for(dict(contact_prox=0.1)))
+    lp = 648.76
+    for side, entry, stop, target in (("long", lp - 0.02, lp - 0.35, lp + 0.25), ("short", lp + 0.02, lp + 0.35, lp - 0.25)):
+        eng.open_trade(side, entry, stop, target, "sim")
+        rising = [dict(t=60000 * j, o=target - 0.5 + 0.05 * j, h=target, l=target - 0.6, c=target - 0.5 + 0.05 * j, v=1e4 * (j + 1))
+                  for j in range(10)]
+        for bars in (None, [], rising, [{k: b[k] for k in "tohlc"} for b in rising],
+                     [dict(price=b["c"], volume=b["v"], ts=b["t"]) for b in rising]):
+            escalated, meta = eng.maybe_escalate_on_target(target, bars)
+            assert escalated is False
+        eng.close_trade(eng.state.open_trade_id, target, "TARGET")
+
+
 def test_lr_contract_matches_sklearn_predict_proba():
     rng = np.random.default_rng(5)
     for _ in range(50):
