@@ -158,6 +158,17 @@ def run_reference(args, wl, rank):
     print(json.dumps(line), flush=True)
 
 
+def fp32_roofline(eng, units_per_s, flop_per_unit):
+    """Second roofline of SURVEY 8(d): contract flop per path-step (12 scan-only, 24 fused GBM) x measured rate,
+    against the FFMA-only rate measured on this device in this run (outside the timed region)."""
+    peak = eng.measure_fp32_peak()
+    ach = flop_per_unit * units_per_s / 1e12
+    return {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+            "flop_per_path_step": flop_per_unit, "peak_source": "qmmx_measure_fp32_peak: FFMA-only kernel, this run",
+            "note": "essential flop only; the engine is compare/select/table work, so the issue-slot use "
+                    "(smsp__issue_active in profiles/) is the binding figure, not this fraction"}
+
+
 def run_extra(args, name, rank, local_rank, world):
     """Secondary configs of BASELINE.json (not the driver's headline line): c2hl (C2 with OHLC bars and exits on
     high/low), c3 (fused Philox GBM + scan, 12.5M paths per GPU), c4 (256-combo stop/target x cooldown sweep over
@@ -252,6 +263,7 @@ def run_extra(args, name, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     clocks = sampler.stop()
+    launches = eng.launch_count() - l0
     if rank == 0:
         peak, src = measured_peak_hbm()
         ach = cfg["bytes_per_step"] * units / (ms * 1e-3) / 1e9
@@ -261,7 +273,8 @@ def run_extra(args, name, rank, local_rank, world):
             "dtype": "f32 bars", "data": "synthetic", "config": cfg,
             "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                          "note": "whole step (all kernels) / algorithmic bytes", "peak_source": src},
-            "clocks": clocks, "gpu_launches": eng.launch_count() - l0,
+            "roofline_fp32": fp32_roofline(eng, units / (ms * 1e-3), 24 if name == "c3" else 12),
+            "clocks": clocks, "gpu_launches": launches,
             "result_check": {"n_paths": res[0].n_paths, "n_trades": res[0].n_trades, "hit_rate": res[0].hit_rate,
                              "combos": len(res)}}), flush=True)
     eng.close()
@@ -414,6 +427,7 @@ def main():
                                            "(profiles/r1_ncu_lean_scan_close_summary.txt)",
                          "kernel": "lean_scan_kernel<MULTIDAY=0,HL=0,PARITY=0,WIDE=0,SLOW=0>", "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
+            "roofline_fp32": fp32_roofline(eng, paths * STEPS_PER_PATH / (k_ms * 1e-3), 12),
             "clocks": clocks, "gpu_launches": int(launches),
             "result_check": {"n_trades": res.n_trades, "n_wins": res.n_wins, "sum_pnl": res.sum_pnl},
         }

@@ -281,6 +281,9 @@ int  qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels
 
 /* device time of the last run's kernels in ms (CUDA events on the ctx stream) */
 int  qmmx_last_timing(qmmx_ctx* ctx, float* ms);
+/* FP32 FFMA throughput of this device in TFLOP/s, measured now with an FMA-only kernel (best of 3 after a warm-up).
+ * The denominator of the FP32/issue roofline that SURVEY 8(d) asks for beside the HBM one; no reference counterpart. */
+int  qmmx_measure_fp32_peak(qmmx_ctx* ctx, double* tflops);
 /* number of kernel launches issued by this ctx since creation */
 int  qmmx_launch_count(qmmx_ctx* ctx, uint64_t* n);
 

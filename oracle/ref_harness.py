@@ -46,7 +46,12 @@ def _stub_gui_modules() -> None:
     def mod(name, **attrs):
         m = types.ModuleType(name)
         m.__dict__.update(attrs)
-        m.__getattr__ = lambda attr: _Any  # type: ignore[attr-defined]
+
+        def _module_getattr(attr):
+            if attr.startswith("__"):      # __file__, __path__ ...: tools that walk sys.modules must see a plain module
+                raise AttributeError(attr)
+            return _Any
+        m.__getattr__ = _module_getattr  # type: ignore[attr-defined]
         sys.modules[name] = m
         return m
 
@@ -251,7 +256,13 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
         trades.append(dict(entry_bar=pos["entry_bar"], exit_bar=-1, side=pos["side"],
                            level=pos["level"], reason="OPEN", entry=pos["entry"], exit=last,
                            pnl=0.0, mtm=mtm))
-    return dict(codes=codes, trades=trades,
+    # the fold of the reference's log_analyzer.py:14-31 over the rows this run wrote
+    skip_rows, policy_skip_rows = {}, {}
+    for action, fold in (("skip", skip_rows), ("policy_skip", policy_skip_rows)):
+        for (fj,) in conn.execute("SELECT features_json FROM policy_events WHERE phase='entry' AND action=?", (action,)):
+            r = json.loads(fj).get("reason", "UNKNOWN_REASON")
+            fold[r] = fold.get(r, 0) + 1
+    return dict(codes=codes, trades=trades, skip_rows=skip_rows, policy_skip_rows=policy_skip_rows,
                 touch_counts=dict(eng.state.level_touch_counts),
                 touchmem_touches=dict(eng.touchmem.touch), touchmem_edge_taps=len(eng.touchmem.edge_taps),
                 regime=eng.acc_guard.regime)

@@ -462,4 +462,23 @@ __global__ void init_flat_kernel(unsigned long long* flat, int n_combos) {
     }
 }
 
+// ---- FP32 issue-rate probe ("measure an FMA-only microbenchmark on the box and use that") ------------
+// 16 independent FFMA chains per thread; 2 flop per FFMA. The result is stored so that nothing is eliminated.
+__global__ void __launch_bounds__(1024, 1) fp32_probe_kernel(float* out, int iters, float a, float b) {
+    float x[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) x[k] = (float)(threadIdx.x + k) * 1e-3f;
+#pragma unroll 1
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int k = 0; k < 16; ++k) x[k] = __fmaf_rn(x[k], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += x[k];
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 }  // namespace qmmx

@@ -79,6 +79,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_debug_classify": (C.c_int, [vp, vp, C.c_int, dbl, dbl, vp, i64, vp, vp, vp, vp, vp, vp]),
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
+        "qmmx_measure_fp32_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
     }
     for name, (res, args) in protos.items():
         fn = getattr(L, name)          # AttributeError here = header/library mismatch
@@ -397,6 +398,12 @@ class MCEngine:
         ms = C.c_float()
         self._ck(self._L.qmmx_last_timing(self._h, C.byref(ms)))
         return float(ms.value)
+
+    def measure_fp32_peak(self) -> float:
+        """FFMA-only TFLOP/s of this device, measured now (the FP32 roofline denominator of SURVEY 8(d))."""
+        v = C.c_double()
+        self._ck(self._L.qmmx_measure_fp32_peak(self._h, C.byref(v)))
+        return float(v.value)
 
     def launch_count(self) -> int:
         n = C.c_uint64()

@@ -118,3 +118,65 @@ def run_paths(eng: MCEngine, close, levels: Sequence[dict], params, *, high=None
     eng.set_policy(policy)
     eng.upload_bars(close, high, low)
     return eng.run_scan()
+
+
+# ---- results sink (second half): reason-code histograms instead of policy_events rows ----------
+# The reference writes one `policy_events` row per evaluated tick (M:1468-1490) and `log_analyzer.py:23-73` folds the
+# `phase='entry' AND action='skip'` rows into counts per `reason`.  The device already produces those counts
+# (qmmx_agg.entry_hist), so the sink is columnar: one row per parameter combo, one column per reason.
+
+# reasons the reference files under action='policy_skip' (M:1658, M:1694, M:3097): log_analyzer's query does not see them
+POLICY_SKIP_REASONS = ("ACC_BREAKOUT_GATE", "ONLINE_POLICY", "VETO_CONTRA_VOL_LONG", "VETO_CONTRA_VOL_SHORT",
+                       "VETO_EDGE_FATIGUE", "VETO_BOUNCE_BUDGET", "VETO_LEVEL_COOLDOWN")
+
+
+def skip_reason_counts(result, policy_skips: bool = False) -> dict:
+    """reason -> count of the entry-phase skips, the fold `log_analyzer.py:14-31` computes from the action='skip'
+    rows; `policy_skips=True` adds the reasons the reference writes as action='policy_skip' rows."""
+    return {name: n for name, n in result.entry_hist.items()
+            if name != "OK" and n > 0 and (policy_skips or name not in POLICY_SKIP_REASONS)}
+
+
+def skip_report(result) -> str:
+    """The report text of `log_analyzer.py:17-73` (header, then reasons by descending count).  The per-reason
+    detail lines of the reference need the per-event extras, which the aggregate does not keep."""
+    counts = skip_reason_counts(result)
+    total = sum(counts.values())
+    if not total:
+        return "No 'entry' phase skip events found in the policy_events table."
+    lines = [f"Found {total} 'entry' phase skip events.\n", "--- Summary of Skip Reasons ---"]
+    for reason, n in sorted(counts.items(), key=lambda kv: kv[1], reverse=True):
+        lines.append(f"Reason: {reason} (Count: {n})")
+        lines.append("")
+    return "\n".join(lines)
+
+
+def results_columns(results, params=None) -> dict:
+    """Column arrays over the combos of one run: the qmmx_agg counters, PnL moments and both reason histograms
+    (`entry_<REASON>`, `exit_<REASON>`), plus the swept settings when `params` (the list given to set_params) is passed."""
+    results = list(results)
+    cols = {k: np.array([getattr(r, k) for r in results], dtype=np.int64)
+            for k in ("n_paths", "n_steps", "n_trades", "n_wins", "n_open")}
+    for k in ("sum_pnl", "sum_pnl2", "sum_path_pnl2", "sum_open_mtm", "max_path_pnl", "min_path_pnl"):
+        cols[k] = np.array([float(getattr(r.agg, k)) for r in results], dtype=np.float64)
+    for i, name in enumerate(abi.ENTRY_CODES):
+        cols["entry_" + name] = np.array([int(r.agg.entry_hist[i]) for r in results], dtype=np.int64)
+    for i, name in enumerate(abi.EXIT_CODES):
+        cols["exit_" + name] = np.array([int(r.agg.exit_hist[i]) for r in results], dtype=np.int64)
+    if params is not None:
+        plist = list(params) if isinstance(params, (list, tuple)) else [params]
+        if len(plist) != len(results):
+            raise ValueError("params and results differ in length")
+        for k in ("contact_prox", "stop_padding", "tp_padding", "q_min_prob", "cooldown_s"):
+            cols[k.upper()] = np.array([float(getattr(p, k)) for p in plist], dtype=np.float64)
+    return cols
+
+
+def write_results(path: str, results, params=None) -> str:
+    """Write `results_columns` as one Parquet file (pyarrow).  Replaces the audit_log / policy_events tables for runs
+    whose tick count (10^8 .. 10^11) rules out a row per tick."""
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    cols = results_columns(results, params)
+    pq.write_table(pa.table({k: pa.array(v) for k, v in cols.items()}), path)
+    return path

@@ -189,3 +189,36 @@ def test_montecarlo_host_side_matches_oracle():
             assert getattr(m, k) == s[k], k
         m.wins, m.losses, m.opens = s["wins"], s["losses"], s["opens"]
         assert m.message() == case["mc_message"] == format_mc_message(s)
+
+
+def test_results_sink_reason_histograms(tmp_path):
+    """Columnar sink + the skip-reason report in the format of the reference's log_analyzer.py:17-73."""
+    from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    results, plist = [], []
+    for k in range(3):
+        a = abi.Agg()
+        a.struct_size = C.sizeof(abi.Agg)
+        a.n_paths, a.n_steps, a.n_trades, a.n_wins = 10, 3900, 7 + k, 3
+        a.entry_hist[abi.ENTRY_CODES.index("OK")] = 7 + k
+        a.entry_hist[abi.ENTRY_CODES.index("TOO_FAR")] = 3000 - k
+        a.entry_hist[abi.ENTRY_CODES.index("COOLDOWN")] = 14
+        a.entry_hist[abi.ENTRY_CODES.index("CONF_LOW")] = 500
+        a.exit_hist[abi.EXIT_CODES.index("STOP")] = 4 + k
+        a.sum_pnl = -0.35 * k
+        results.append(E.MCResult(a))
+        plist.append(abi.make_params(stop_padding=0.10 + 0.05 * k))
+    assert MC.skip_reason_counts(results[0]) == {"TOO_FAR": 3000, "COOLDOWN": 14, "CONF_LOW": 500}
+    rep = MC.skip_report(results[1]).splitlines()
+    assert rep[0] == "Found 3513 'entry' phase skip events."
+    assert rep[2] == "--- Summary of Skip Reasons ---"
+    assert [ln for ln in rep if ln.startswith("Reason:")] == [
+        "Reason: TOO_FAR (Count: 2999)", "Reason: CONF_LOW (Count: 500)", "Reason: COOLDOWN (Count: 14)"]
+    assert MC.skip_report(E.MCResult(abi.Agg())).startswith("No 'entry' phase skip events")
+    cols = MC.results_columns(results, plist)
+    assert cols["entry_TOO_FAR"].tolist() == [3000, 2999, 2998] and cols["exit_STOP"].tolist() == [4, 5, 6]
+    assert np.allclose(cols["STOP_PADDING"], [0.10, 0.15, 0.20])
+    import pyarrow.parquet as pq
+    path = MC.write_results(str(tmp_path / "run.parquet"), results, plist)
+    t = pq.read_table(path)
+    assert t.num_rows == 3 and t.column("n_trades").to_pylist() == [7, 8, 9]
+    assert t.column("sum_pnl").to_pylist() == [0.0, -0.35, -0.7]

@@ -6,9 +6,16 @@ import pytest
 from oracle import headless as H
 from oracle import ref_harness as rh
 from oracle.make_golden import settings_for
-from qmmx_monolithic_monte_carlo_b200 import fixtures as F
+from qmmx_monolithic_monte_carlo_b200 import abi, engine as E, fixtures as F, montecarlo as MC
 
 pytestmark = pytest.mark.skipif(not rh.reference_available(), reason="reference not mounted")
+
+
+def _agg_from_codes(codes):
+    a = abi.Agg()
+    for c in codes:
+        a.entry_hist[c] += 1
+    return E.MCResult(a)
 
 
 def _check(levels, params, closes, lr=None, pol=None, volume=None):
@@ -27,6 +34,14 @@ def _check(levels, params, closes, lr=None, pol=None, volume=None):
                    (b.entry_bar, b.exit_bar, H.EXIT_CODES[b.reason], lv[b.level].key, ("long", "short")[b.side])
             assert a["pnl"] == b.pnl and a["entry"] == b.entry and a["exit"] == b.exit
         assert {lv[i].key: t for i, t in enumerate(o.touch_counts) if t} == ref["touch_counts"]
+        # the reason histogram (what the product's results sink keeps) == log_analyzer's fold of the policy_events rows:
+        # action='skip' rows for the gate reasons, action='policy_skip' rows for 904 / soft veto (M:1658, M:1694; the veto
+        # row carries the bare veto code).  ONLINE_POLICY rows are written by the GUI loop (M:3097), not by the engine.
+        a = _agg_from_codes(o.codes)
+        assert MC.skip_reason_counts(a) == ref["skip_rows"]
+        pol_skips = {k: v for k, v in MC.skip_reason_counts(a, policy_skips=True).items()
+                     if k not in ref["skip_rows"] and k != "ONLINE_POLICY"}
+        assert {(k[5:] if k.startswith("VETO_") else k): v for k, v in pol_skips.items()} == ref["policy_skip_rows"]
 
 
 @pytest.mark.parametrize("seed", [101, 102, 103])
