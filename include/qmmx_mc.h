@@ -20,6 +20,7 @@
  *                                                                                       M:1888-1948, M:259-270
  *   qmmx_lr_score        OnlinePolicy.score_entry / predict_proba as a batch            M:334-355, M:20-26, M:1463
  *   qmmx_run_jitter      QMMXApp.simulate_monte_carlo trial loop (walk_outcome)         M:3449-3510
+ *   qmmx_run_last_bars   QMMXApp.simulate_last_bars forward walk (stop before target)    M:3619-3639
  *   qmmx_gen_gbm / qmmx_gen_bootstrap / qmmx_run_fused_gbm / qmmx_run_fused_bootstrap
  *                        no reference equivalent (the reference simulates on real Polygon bars);
  *                        synthetic 1-minute paths demanded by BASELINE.json north_star.
@@ -269,6 +270,15 @@ int  qmmx_run_jitter(qmmx_ctx* ctx, const double* high, const double* low, int32
                      const double* replay_normals, const double* replay_uniforms,
                      double* out_total_r, double* out_max_dd, int32_t* out_wins, int32_t* out_losses,
                      int32_t* out_opens);
+
+/* deterministic walk of QMMXApp.simulate_last_bars (M:3619-3639): for each candidate the first bar after cand_bar
+ * whose low/high reaches cand_stop or cand_target, the stop tested first on a bar that reaches both.
+ *   cand_*            [n_cand]   bar index, side (0 long/1 short), stop and target prices (M:3610-3615)
+ *   out_outcome       [n_cand]   0 = "tp", 1 = "stop", 2 = "open" (never hit)
+ *   out_exit_bar      [n_cand]   index of the hit bar, -1 when open                                  */
+int  qmmx_run_last_bars(qmmx_ctx* ctx, const double* high, const double* low, int32_t n_bars,
+                        const int32_t* cand_bar, const uint8_t* cand_side, const double* cand_stop,
+                        const double* cand_target, int32_t n_cand, int32_t* out_outcome, int32_t* out_exit_bar);
 
 /* Host-side check of the exact price-classification tables the kernels use (no device needed):
  * for each fp32 price, level_table/level_brute = touched level by table lookup / by the float64 brute force

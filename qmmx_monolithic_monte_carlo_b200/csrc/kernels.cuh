@@ -369,6 +369,42 @@ __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
     }
 }
 
+// ---- deterministic walk of simulate_last_bars (M:3619-3639): first bar after the candidate whose low/high reaches
+// the stop or the target; the stop is tested first on a bar that reaches both.  One warp per candidate, the lanes
+// scan 32 bars at a time and the first hit is the lowest set ballot bit.  outcome: 0 tp, 1 stop, 2 open.
+__global__ void __launch_bounds__(kThreads) last_bars_kernel(const double* __restrict__ high, const double* __restrict__ low,
+                                                             int32_t n_bars, const int32_t* __restrict__ cand_bar,
+                                                             const uint8_t* __restrict__ cand_side,
+                                                             const double* __restrict__ cand_stop,
+                                                             const double* __restrict__ cand_target, int32_t n_cand,
+                                                             int32_t* __restrict__ out_outcome, int32_t* __restrict__ out_exit_bar) {
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int ci = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; ci < n_cand; ci += warps) {
+        const int side = cand_side[ci];
+        const double stop = cand_stop[ci], target = cand_target[ci];
+        int outcome = 2, exit_bar = -1;
+        for (int j0 = cand_bar[ci] + 1; j0 < n_bars; j0 += 32) {
+            const int j = j0 + lane;
+            bool stop_hit = false, target_hit = false;
+            if (j < n_bars) {
+                const double hh = high[j], ll = low[j];
+                stop_hit = (side == 0) ? (ll <= stop) : (hh >= stop);
+                target_hit = (side == 0) ? (hh >= target) : (ll <= target);
+            }
+            const unsigned any = __ballot_sync(0xffffffffu, stop_hit || target_hit);
+            if (any) {
+                const int first = __ffs(any) - 1;
+                const unsigned stops = __ballot_sync(0xffffffffu, stop_hit);
+                outcome = (stops >> first) & 1u ? 1 : 0;
+                exit_bar = j0 + first;
+                break;
+            }
+        }
+        if (lane == 0) { out_outcome[ci] = outcome; out_exit_bar[ci] = exit_bar; }
+    }
+}
+
 // ---- AccumulationBreakoutGuard regime per tick (M:1241-1356, fed by ingest_tick M:1857-1883 at M:2932) -------------
 // The regime depends on the bars only, never on the engine state, so it is a pre-pass over the resident close and
 // volume planes: reg[i][path] = regime evaluate_entry sees at tick i (the guard has been fed the one-tick minute bars

@@ -1016,6 +1016,46 @@ int qmmx_run_jitter(qmmx_ctx* c, const double* high, const double* low, int32_t 
     return QMMX_OK;
 }
 
+int qmmx_run_last_bars(qmmx_ctx* c, const double* high, const double* low, int32_t n_bars, const int32_t* cand_bar,
+                       const uint8_t* cand_side, const double* cand_stop, const double* cand_target, int32_t n_cand,
+                       int32_t* out_outcome, int32_t* out_exit_bar) {
+    ENTER(c);
+    if (!high || !low || n_bars < 1 || n_bars > 12000 || n_cand < 0 ||
+        (n_cand > 0 && (!cand_bar || !cand_side || !cand_stop || !cand_target || !out_outcome || !out_exit_bar)))
+        return fail(ctx, QMMX_E_BADARG, "run_last_bars: bad arguments (n_bars 1..12000)");
+    if (n_cand == 0) return QMMX_OK;
+    const size_t nb = (size_t)n_bars, nk = (size_t)n_cand;
+    uint8_t* arena = nullptr;                      // f64: high, low, stop, target | i32: bar, outcome, exit_bar | u8: side
+    const size_t bytes = (2 * nb + 2 * nk) * 8 + 3 * nk * 4 + nk + 64;
+    CK(cudaMalloc(&arena, bytes));
+    double* d64 = reinterpret_cast<double*>(arena);
+    int32_t* i32 = reinterpret_cast<int32_t*>(arena + (2 * nb + 2 * nk) * 8);
+    uint8_t* u8 = reinterpret_cast<uint8_t*>(i32 + 3 * nk);
+    cudaError_t e = cudaSuccess;
+    auto up = [&](const void* src, void* dst, size_t n) {
+        if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream);
+    };
+    up(high, d64, nb * 8); up(low, d64 + nb, nb * 8);
+    up(cand_stop, d64 + 2 * nb, nk * 8); up(cand_target, d64 + 2 * nb + nk, nk * 8);
+    up(cand_bar, i32, nk * 4); up(cand_side, u8, nk);
+    if (e == cudaSuccess) {
+        const int64_t blocks = std::min<int64_t>((nk * 32 + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        last_bars_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(d64, d64 + nb, n_bars, i32, u8, d64 + 2 * nb,
+                                                                         d64 + 2 * nb + nk, n_cand, i32 + nk, i32 + 2 * nk);
+        ctx->launches++;
+        e = cudaGetLastError();
+        cudaEventRecord(ctx->ev1, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_outcome, i32 + nk, nk * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_exit_bar, i32 + 2 * nk, nk * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(arena);
+    if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("run_last_bars: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
 int qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
                         const float* p, int64_t n, int32_t* level_table, int32_t* level_brute,
                         uint8_t* conf_mask, uint8_t* conf_brute, uint64_t* near_table, uint64_t* near_brute) {

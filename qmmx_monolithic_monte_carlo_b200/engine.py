@@ -76,6 +76,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_lr_score": (C.c_int, [vp, vp, i64, i32, vp, vp, i32, vp]),
         "qmmx_run_jitter": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, dbl, dbl, vp, i64, u64, u64,
                                       vp, vp, vp, vp, vp, vp, vp]),
+        "qmmx_run_last_bars": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp]),
         "qmmx_debug_classify": (C.c_int, [vp, vp, C.c_int, dbl, dbl, vp, i64, vp, vp, vp, vp, vp, vp]),
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
@@ -393,6 +394,20 @@ class MCEngine:
                                          trials, seed, trial_offset, _ptr(rn), _ptr(ru), _ptr(tot), _ptr(dd),
                                          _ptr(w), _ptr(lo), _ptr(op)))
         return dict(totals=tot, drawdowns=dd, wins=w, losses=lo, opens=op)
+
+    def run_last_bars(self, high, low, cands):
+        """Forward walk of `simulate_last_bars` (M:3619-3639) for cands = list of dict(i, side, stop, target).
+        Returns (outcome[K] 0 tp / 1 stop / 2 open, exit_bar[K] or -1)."""
+        high = np.ascontiguousarray(high, dtype=np.float64)
+        low = np.ascontiguousarray(low, dtype=np.float64)
+        cb = np.array([c["i"] for c in cands], dtype=np.int32)
+        cs = np.array([c["side"] for c in cands], dtype=np.uint8)
+        st = np.array([c["stop"] for c in cands], dtype=np.float64)
+        tg = np.array([c["target"] for c in cands], dtype=np.float64)
+        oc = np.full(len(cands), 2, dtype=np.int32); xb = np.full(len(cands), -1, dtype=np.int32)
+        self._ck(self._L.qmmx_run_last_bars(self._h, _ptr(high), _ptr(low), len(high), _ptr(cb), _ptr(cs), _ptr(st),
+                                            _ptr(tg), len(cands), _ptr(oc), _ptr(xb)))
+        return oc, xb
 
     def last_timing_ms(self) -> float:
         ms = C.c_float()

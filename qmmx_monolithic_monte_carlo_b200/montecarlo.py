@@ -3,6 +3,8 @@
 `monte_carlo(...)`  ~ `QMMXApp.simulate_monte_carlo` (qmmx_monolithic.py:3353-3538): candidate pass on the host
                       (O(n L), cheap), trials x candidates walk-forward on the device (`qmmx_run_jitter`),
                       summary with the reference's index rules and message text.
+`last_bars(...)`    ~ `QMMXApp.simulate_last_bars` (M:3540-3699): same candidate pass, deterministic forward walks on
+                      the device (`qmmx_run_last_bars`), the reference's rounding and summary rules.
 `run_paths(...)`    ~ the live engine (`evaluate_entry` + exit block) over many price paths.
 
 `levels` is the reference's list of dicts {color, type, index, price}; `bars` is the reference's list of
@@ -108,6 +110,67 @@ def monte_carlo(eng: MCEngine, bars, levels: Sequence[dict], *, contact_prox=0.0
                          (level_jitter_std, entry_slip_std, stop_slip_std, target_slip_std), trials,
                          seed=0 if seed is None else int(seed), replay=replay)
     return summarize(out["totals"], out["drawdowns"], out["wins"], out["losses"], out["opens"], len(cands))
+
+
+@dataclass
+class SimSummary:
+    """Fields of the reference's SIM/SUMMARY line and "Sim complete" box (M:3650-3693)."""
+    trades: int
+    wins: int
+    loss: int
+    open: int
+    total_R: float
+    avg_R: float
+    max_win_R: float
+    max_loss_R: float
+    max_profit_usd: float
+    max_loss_usd: float
+
+    def message(self) -> str:
+        return (f"Trades: {self.trades} | Wins: {self.wins} Loss: {self.loss} Open: {self.open}\n"
+                f"Total R: {self.total_R} | Avg R (closed): {self.avg_R}\n"
+                f"Max Profit: ${self.max_profit_usd} | Max Loss: ${self.max_loss_usd}\n"
+                f"Max Win (R): {self.max_win_R} | Max Loss (R): {self.max_loss_R}")
+
+
+def last_bars(eng: MCEngine, bars, levels: Sequence[dict], *, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25,
+              n=1200, touch_limit=2):
+    """Same arguments and defaults as `simulate_last_bars` (M:3540-3541) with with_gates=False: candidate pass on the
+    host, the forward walks on the device (`qmmx_run_last_bars`, stop tested before target), then the reference's
+    per-trade `round(., 2)` and summary rules (M:3641-3666).  Returns (trades, SimSummary); the trade dicts carry
+    the reference's keys plus `j` (exit bar, -1 when open)."""
+    rows, price, _ = sort_levels(levels)
+    c, h, l = _bar_arrays(bars, n)
+    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit)
+    outcome, exit_bar = eng.run_last_bars(h, l, cands) if cands else ((), ())
+    trades = []
+    for cand, oc, xb in zip(cands, outcome, exit_bar):
+        entry, stop, target = cand["entry"], cand["stop"], cand["target"]
+        if oc == 2:
+            name, exit_px, r = "open", float(c[-1]), 0.0
+        else:
+            name = "tp" if oc == 0 else "stop"
+            exit_px = target if oc == 0 else stop
+            risk = abs(entry - stop) or 1e-9
+            r = (abs(target - entry) / risk) if oc == 0 else -1.0
+        trades.append({"i": cand["i"], "j": int(xb), "side": "long" if cand["side"] == 0 else "short",
+                       "lvl": round(cand["lvl"], 2), "entry": round(entry, 2), "stop": round(stop, 2),
+                       "target": round(target, 2), "exit": round(exit_px, 2), "outcome": name, "R": round(r, 2),
+                       "prox": round(cand["prox"], 3), "touch#": cand["tc"]})
+    closed = [t for t in trades if t["outcome"] in ("tp", "stop")]
+
+    def usd(t):
+        return (t["exit"] - t["entry"]) * (1.0 if t["side"] == "long" else -1.0)
+    s = SimSummary(
+        trades=len(trades), wins=sum(1 for t in trades if t["outcome"] == "tp"),
+        loss=sum(1 for t in trades if t["outcome"] == "stop"), open=sum(1 for t in trades if t["outcome"] == "open"),
+        total_R=round(sum(t["R"] for t in trades), 2),
+        avg_R=round(sum(t["R"] for t in closed) / max(1, len(closed)), 2),
+        max_win_R=round(max((t["R"] for t in closed), default=0.0), 2),
+        max_loss_R=round(min((t["R"] for t in closed), default=0.0), 2),
+        max_profit_usd=round(max((usd(t) for t in closed), default=0.0), 2),
+        max_loss_usd=round(min((usd(t) for t in closed), default=0.0), 2))
+    return trades, s
 
 
 def run_paths(eng: MCEngine, close, levels: Sequence[dict], params, *, high=None, low=None, lr=None, policy=None):

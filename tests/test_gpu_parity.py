@@ -560,3 +560,48 @@ def test_gpu_regime_guard_gate(eng, variant):
     assert_trades_equal(tr, cnt, o["trades"], o["counts"])
     assert_agg_equal(res[0].agg, o["agg"])
     assert_agg_equal(eng.run_scan()[0].agg, o["agg"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", load_jitter_cases(), ids=lambda c: c["name"])
+def test_gpu_last_bars_dropin_matches_reference_rows(eng, case):
+    """Row a15: `montecarlo.last_bars` (device walk) reproduces the SIM/TRADE rows and the "Sim complete" text the
+    reference's `simulate_last_bars` wrote for the golden bars (tests/golden/jitter_mc.json)."""
+    from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    trades, s = MC.last_bars(eng, case["bars"], levels_by_name(case["levels"]), contact_prox=case["contact_prox"],
+                             n=case["n"], touch_limit=case["touch_limit"])
+    assert s.message() == case["sim_message"]
+    trows = [r[2] for r in case["sim_rows"] if r[1] == "TRADE"]
+    assert len(trows) == len(trades)
+    for txt, t in zip(trows, trades):
+        usd = (t["exit"] - t["entry"]) * (1.0 if t["side"] == "long" else -1.0)
+        assert txt == (f"{t['outcome'].upper():5s} | {t['side']:5s} @ {t['entry']:.2f} → {t['exit']:.2f} "
+                       f"| lvl {t['lvl']:.2f} | R={t['R']:+.2f} | ${usd:+.2f} | prox={t['prox']:.03f} touch#{t['touch#']}")
+
+
+@pytest.mark.gpu
+def test_gpu_last_bars_walk_equals_oracle_on_long_series(eng):
+    """12000 bars (the ABI maximum), ~hundreds of candidates, ties where one bar reaches stop and target."""
+    from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    rng = np.random.default_rng(15)
+    n = 12000
+    c = 648.9 + np.cumsum(rng.normal(0, 0.12, n))
+    spread = np.abs(rng.normal(0, 0.25, n))
+    bars = dict(o=c.tolist(), c=c.tolist(), h=(c + spread).tolist(), l=(c - spread).tolist())
+    lv = H.sort_levels(F.levels_30())
+    P = H.Params(contact_prox=0.1, stop_padding=0.2, tp_padding=0.15)
+    ref_trades, ref_s = H.simulate_last_bars(bars, lv, P, n=n, touch_limit=12)
+    trades, s = MC.last_bars(eng, bars, F.levels_30(), contact_prox=0.1, stop_padding=0.2, tp_padding=0.15, n=n,
+                             touch_limit=12)
+    assert len(trades) == len(ref_trades) >= 100
+    assert [(t["i"], t["j"], t["outcome"], t["R"], t["exit"]) for t in trades] == \
+           [(t["i"], t["j"], t["outcome"], t["R"], t["exit"]) for t in ref_trades]
+    assert {k: getattr(s, k) for k in ref_s} == ref_s
+    assert {t["outcome"] for t in trades} >= {"tp", "stop"}
+
+
+@pytest.mark.gpu
+def test_gpu_fp32_probe_is_plausible(eng):
+    """The FFMA-only probe behind bench.py's roofline_fp32: a B200 sustains tens of TFLOP/s, never above nominal."""
+    v = eng.measure_fp32_peak()
+    assert 20.0 < v < 90.0, v
