@@ -41,6 +41,7 @@ struct qmmx_ctx {
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
     unsigned long long* d_flat = nullptr; int flat_combos = 0;
     bool any_hl = false, any_tiny = false;
+    bool no_sweep = false;     // QMMX_NO_SWEEP=1: one launch per combo even for sweep-shaped parameter sets
     bool lean_ok = false;      // scan_lean.cuh's sign-encoded gate table is valid for these levels
     bool force_v1 = false;     // QMMX_SCAN_V1=1: run the first-generation lockstep kernel (A/B measurements)
     // resident bars
@@ -299,7 +300,61 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         if (multiday) { if (wide) LEAN2(true, HLv, PARv, true); else LEAN2(true, HLv, PARv, false); } \
         else { if (wide) LEAN2(false, HLv, PARv, true); else LEAN2(false, HLv, PARv, false); }        \
     } while (0)
+    // parameter sweeps: combos that differ only in stop/target padding and cooldown run 32 to a warp over one path
+    // (lean_sweep_kernel); groups too small to fill most of a warp keep the one-launch-per-combo kernels below
+    std::vector<char> swept((size_t)nc, 0);
+    if (lean && !par && !multiday && ctx->L > 0 && nc >= kSweepMinLanes && !ctx->no_sweep) {
+        auto plain = [&](int c) {
+            const DevCombo& D = ctx->h_combos[c];
+            const bool on_resident = cl && cl == ctx->d_close;
+            return !(D.flags & QMMX_F_USE_BLEND) && (D.flags & QMMX_F_DISABLE_POLICY_GATE) &&
+                   !(on_resident && (D.flags & QMMX_F_ENABLE_VETO) && ctx->d_vol) && !(on_resident && ctx->d_vol && ctx->d_regime) &&
+                   D.sp >= 0.0 && D.tp >= 0.0 && D.sp + D.tp > 0.0;
+        };
+        auto same_family = [&](const DevCombo& a, const DevCombo& b) {
+            return a.table == b.table && a.qmin == b.qmin && a.prox == b.prox && a.pmax == b.pmax && a.wr == b.wr && a.wm == b.wm &&
+                   a.vstrong == b.vstrong && a.vprox == b.vprox && a.overtouch == b.overtouch && a.spd == b.spd && a.flags == b.flags;
+        };
+        for (int c0 = 0; c0 < nc; ++c0) {
+            if (swept[c0] || !plain(c0)) continue;
+            std::vector<int> fam;
+            for (int c = c0; c < nc; ++c)
+                if (!swept[c] && plain(c) && same_family(ctx->h_combos[c0], ctx->h_combos[c])) fam.push_back(c);
+            for (size_t at = 0; at < fam.size(); at += 32) {
+                const int n = (int)std::min<size_t>(32, fam.size() - at);
+                if (n < kSweepMinLanes) break;
+                ScanArgs A;
+                fill_args(ctx, A, fam[at], cl, h, l, pitch, paths, steps);
+                SweepArgs W;
+                std::memset(&W, 0, sizeof(W));
+                for (int j = 0; j < n; ++j) {
+                    const DevCombo& D = ctx->h_combos[fam[at + j]];
+                    W.lane[j].sp = D.sp; W.lane[j].tp = D.tp; W.lane[j].cool_steps = D.cool_steps; W.lane[j].combo = fam[at + j];
+                    swept[fam[at + j]] = 1;
+                }
+                W.n_lanes = n;
+                W.mlmask = A.mlmask ? ctx->d_mlmask : nullptr;       // per-lane rows; the shared gate table carries no logistic sign
+                W.mask_stride = (int64_t)ctx->n_lr * kMaxLevels;
+                W.flat = ctx->d_flat;
+                A.mlmask = nullptr;
+                const size_t sw_smem = sweep_smem_bytes(ctx->L);
+                const dim3 sw_grid((unsigned)std::max<int64_t>(1, std::min<int64_t>((paths + kLeanWarps - 1) / kLeanWarps, (int64_t)ctx->sm_count)), 1, 1);
+#define SWEEP(HLv, Wv)                                                                        \
+    do {                                                                                      \
+        auto k = lean_sweep_kernel<HLv, Wv>;                                                  \
+        if ((rc = set_smem_attr(ctx, k, sw_smem)) != 0) return rc;                            \
+        k<<<sw_grid, kLeanThreads, sw_smem, ctx->stream>>>(A, W);                             \
+    } while (0)
+                if (hl) { if (wide) SWEEP(true, true); else SWEEP(true, false); }
+                else { if (wide) SWEEP(false, true); else SWEEP(false, false); }
+#undef SWEEP
+                ctx->launches++;
+                CK(cudaGetLastError());
+            }
+        }
+    }
     for (int c = 0; c < nc; ++c) {
+        if (swept[c]) continue;
         ScanArgs A;
         fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
         const bool parity = par && c == 0;
@@ -403,6 +458,7 @@ int qmmx_create(int device, qmmx_ctx** out) {
     if (prop.major < 10) return bail(QMMX_E_UNSUPPORTED);   // sm_100a cubin only
     ctx->sm_count = prop.multiProcessorCount;
     { const char* v1 = std::getenv("QMMX_SCAN_V1"); ctx->force_v1 = v1 && v1[0] == '1'; }
+    { const char* ns = std::getenv("QMMX_NO_SWEEP"); ctx->no_sweep = ns && ns[0] == '1'; }
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     ctx->stream = ctx->own_stream;

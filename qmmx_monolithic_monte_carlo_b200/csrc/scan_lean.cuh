@@ -121,11 +121,19 @@ __device__ inline void lean_setup(const ScanArgs& A) {
 }
 
 // SLOW = the blend gate, the OnlinePolicy gate or the volume veto is enabled (float64 slow paths compiled in)
-template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW>
+// SWEEP = the lanes of a warp are parameter combos of ONE path (lean_sweep_kernel): stop/target paddings, cooldown and
+// the logistic mask are per-lane members instead of launch constants.
+template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, bool SWEEP = false>
 struct LeanEngine {
     typedef typename LatchType<WIDE>::T latch_t;
     static constexpr int LPAD = WIDE ? 64 : 32;
     typedef LeanLayout<LPAD> Y;
+    double l_sp, l_tp;     // SWEEP only: this lane's STOP_PADDING / TP_PADDING
+    int l_cs;              // SWEEP only: this lane's cooldown in steps
+    uint32_t l_mask;       // SWEEP only: shared address of this lane's logistic-mask row (0 = gate off)
+    __device__ __forceinline__ double sp_(const ScanArgs& A) const { return SWEEP ? l_sp : A.combo.sp; }
+    __device__ __forceinline__ double tp_(const ScanArgs& A) const { return SWEEP ? l_tp : A.combo.tp; }
+    __device__ __forceinline__ int cs_(const ScanArgs& A) const { return SWEEP ? l_cs : A.combo.cool_steps; }
     uint32_t sb, st;       // shared addresses: table base; this thread's column of touch bytes
     float prev, d;         // last price; last non-zero price change (0 = direction unknown, M:1529-1538)
     int cool;              // first step at which an entry may be evaluated; kNoCool while in a position
@@ -173,8 +181,8 @@ struct LeanEngine {
         } else {                                                  // exit at the stop/target level itself (M:3636)
             const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
             double exit_px;
-            if (!is_short) exit_px = is_stop ? lp - A.combo.sp : lp + A.combo.tp;
-            else exit_px = is_stop ? lp + A.combo.sp : lp - A.combo.tp;
+            if (!is_short) exit_px = is_stop ? lp - sp_(A) : lp + tp_(A);
+            else exit_px = is_stop ? lp + sp_(A) : lp - tp_(A);
             const double e = (double)entry_price();
             tp = is_short ? (e - exit_px) : (exit_px - e);
             exit_f = (float)exit_px;
@@ -183,7 +191,7 @@ struct LeanEngine {
         }
         pnl += tp; pnl2 += tp * tp;
         a_inpos += i;                                             // IN_POSITION steps of this trade: i - entry bar
-        cool = i + A.combo.cool_steps;                            // M:2982, M:269-270; COOLDOWN steps are counted in finish
+        cool = i + cs_(A);                                        // M:2982, M:269-270; COOLDOWN steps are counted in finish
         if (win) c_ml += 1u << 16;
         if (PARITY) record_trade(&A, path, ntr, entry_bar, i, is_short ? 1 : 0, is_stop ? QMMX_EXIT_STOP : QMMX_EXIT_TARGET,
                                  pos & 0xff, entry_price(), exit_f, (float)tp);
@@ -218,6 +226,9 @@ struct LeanEngine {
         if (SLOW && A.regime) { const int rc = regime_gate(&A, side, i, path); if (rc) return rc; }      // M:1652-1666
         if (SLOW && A.vol) { const int vc = veto_check(&A, k, pf, side, i, path); if (vc) return vc; }   // M:1678-1705
         if (neg) { c_ml += 1u; return QMMX_ML_CONF_LOW; }         // M:1745-1755 (single day, AND mode)
+        if (SWEEP && l_mask) {                                    // the same gate with this lane's mask (depends on STOP_PADDING)
+            if ((lds_u32<0>(l_mask + k * 4) >> (side * 16 + (int)tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
+        }
         if (SLOW && (A.combo.flags & QMMX_F_USE_BLEND)) {         // M:1730-1742
             if (blend_fails(&A, k, pf, (int)tc, side, day_off)) return QMMX_COMBINED_LOW;
         } else if (MULTIDAY && A.mlmask) {
@@ -229,7 +240,11 @@ struct LeanEngine {
         if (SLOW && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {   // OnlinePolicy gate of the live loop (M:3046-3109)
             if (!policy_passes(&A, k, pf, side, i)) return QMMX_ONLINE_POLICY;
         }
-        lo_thr = g.z; hi_thr = g.w;                               // M:1669-1674
+        if (SWEEP) {                                              // M:1669-1674 with this lane's paddings (as lean_setup rounds them)
+            const double lp = lds_f64<Y::kPrice>(sb + k * 8);
+            lo_thr = __double2float_rd(side == 0 ? lp - l_sp : lp - l_tp);
+            hi_thr = __double2float_ru(side == 0 ? lp + l_tp : lp + l_sp);
+        } else { lo_thr = g.z; hi_thr = g.w; }                    // M:1669-1674
         pos = k | (side << 8);
         sgn = (uint32_t)side << 31;
         entry_s = __int_as_float(__float_as_int(pf) ^ sgn);
@@ -277,7 +292,7 @@ struct LeanEngine {
         // COOLDOWN steps (M:1516): every exit is followed by cool_steps - 1 of them, except that the last one may be cut
         // by the end of the path (only the last: no entry can follow an exit whose cooldown outlasts the path)
         const int n_exits = (int)((c_exit & 0xffffu) + (c_exit >> 16));
-        int n_cool = n_exits * max(A.combo.cool_steps - 1, 0);
+        int n_cool = n_exits * max(cs_(A) - 1, 0);
         if (!is_open() && n_exits > 0 && cool > A.steps) n_cool -= cool - A.steps;
         if (is_open()) {
             const bool is_short = sgn != 0u;
@@ -289,9 +304,12 @@ struct LeanEngine {
         }
         c_span = (uint32_t)a_inpos | ((uint32_t)n_cool << 16);
         if (PARITY && A.tcounts) A.tcounts[path] = ntr;
-        double fb = floor((pnl - A.hist_lo) * A.hist_inv_w);
-        const int bin = fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
-        atomicAdd(&g_S.hist[bin], 1u);
+        if (!SWEEP) atomicAdd(&g_S.hist[hist_bin(A)], 1u);        // the sweep kernel keeps one histogram per lane
+    }
+
+    __device__ __forceinline__ int hist_bin(const ScanArgs& A) const {
+        const double fb = floor((pnl - A.hist_lo) * A.hist_inv_w);
+        return fb < 0 ? 0 : (fb > QMMX_PNL_HIST_BINS - 1 ? QMMX_PNL_HIST_BINS - 1 : (int)fb);
     }
 };
 
@@ -517,6 +535,178 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boo
     }
     __syncthreads();
     block_flush_agg(A.flat, A.steps);
+}
+
+// ---- parameter sweep: the 32 lanes of a warp are 32 parameter combos of ONE path ------------------------------------
+// A sweep over stop/target paddings and cooldowns (BASELINE C4: 256 combos over the same resident bars) evaluates the
+// same prices under every combo.  With lane = combo, all lanes see the same price on the same step: the cell byte,
+// the "far from every level" case and the contact windows are warp-uniform, so the contact block runs on the ~20 % of
+// steps where the path touches a level instead of on every step (32 independent paths always have SOME lane near a
+// level).  Bars are read once per 32 combos: lane l loads step i0 + l of the path and each step is a warp shuffle.
+// Combos of one launch share the tables (levels, CONTACT_PROX, Q_MIN_PROB) and all flags; stop/target paddings, the
+// cooldown and the logistic mask (its feature |level - stop| is STOP_PADDING, M:1459) are per lane.
+struct SweepLane { double sp, tp; int32_t cool_steps, combo; };
+struct SweepArgs {
+    SweepLane lane[32];
+    int32_t n_lanes, pad;
+    const uint32_t* mlmask;            // [combo][mask_stride] or null (no model / gate off)
+    int64_t mask_stride;
+    unsigned long long* flat;          // [combo][QMMX_AGG_SLOTS]
+};
+
+// a warp-step of the sweep kernel costs about half of a warp-step of the per-combo kernel, whatever the lane count
+constexpr int kSweepMinLanes = 20;
+constexpr int kSwU = 11, kSwD = 6;     // per-lane tallies (uint32) and float64 sums of one CTA
+enum { SW_NPATHS, SW_OVER, SW_CONF, SW_ML, SW_DIR, SW_WINS, SW_STOP, SW_TGT, SW_INPOS, SW_COOL, SW_OPEN };
+enum { SWD_PNL, SWD_PNL2, SWD_PATH2, SWD_MTM, SWD_MAX, SWD_NEGMIN };
+
+template <int LPAD>
+struct SweepLayout {
+    typedef LeanLayout<LPAD> Y;
+    static constexpr int kRow = LPAD + 1;                                     // mask row stride in words: lanes land on distinct banks
+    static constexpr int kSMask = (Y::kEnd + 15) & ~15;                       // uint32 [32][kRow]
+    static constexpr int kSD = (kSMask + 32 * kRow * 4 + 7) & ~7;             // double [kSwD][32]
+    static constexpr int kSU = kSD + kSwD * 32 * 8;                           // uint32 [kSwU][32]
+    static constexpr int kSHist = kSU + kSwU * 32 * 4;                        // uint32 [QMMX_PNL_HIST_BINS][32]
+    static constexpr int kSEnd = kSHist + QMMX_PNL_HIST_BINS * 32 * 4;
+};
+inline size_t sweep_smem_bytes(int L) { return L > 32 ? (size_t)SweepLayout<64>::kSEnd : (size_t)SweepLayout<32>::kSEnd; }
+
+template <bool HL, bool WIDE>
+__global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __grid_constant__ ScanArgs A,
+                                                                     const __grid_constant__ SweepArgs W) {
+    constexpr int LPAD = WIDE ? 64 : 32;
+    typedef SweepLayout<LPAD> Z;
+    block_setup(A);
+    lean_setup<false, LPAD>(A);            // A.mlmask is null here: the gate table carries no logistic sign
+    uint32_t* smask = reinterpret_cast<uint32_t*>(g_cell + Z::kSMask);
+    double* sd = reinterpret_cast<double*>(g_cell + Z::kSD);
+    uint32_t* su = reinterpret_cast<uint32_t*>(g_cell + Z::kSU);
+    uint32_t* shist = reinterpret_cast<uint32_t*>(g_cell + Z::kSHist);
+    for (int t = threadIdx.x; t < 32 * Z::kRow; t += blockDim.x) {
+        const int ln = t / Z::kRow, k = t % Z::kRow;
+        smask[t] = (W.mlmask && ln < W.n_lanes && k < LPAD) ? W.mlmask[(size_t)W.lane[ln].combo * (size_t)W.mask_stride + k] : 0u;
+    }
+    const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
+    for (int t = threadIdx.x; t < kSwD * 32; t += blockDim.x) sd[t] = t >= SWD_MAX * 32 ? neg_inf : 0.0;
+    for (int t = threadIdx.x; t < kSwU * 32 + QMMX_PNL_HIST_BINS * 32; t += blockDim.x) su[t] = 0u;   // tallies + histogram (adjacent)
+    __syncthreads();
+
+    LeanEngine<false, HL, false, WIDE, false, true> E;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
+    const bool live = lane < W.n_lanes;
+    const int ln = live ? lane : 0;        // spare lanes shadow lane 0 and are not counted
+    E.l_sp = W.lane[ln].sp; E.l_tp = W.lane[ln].tp; E.l_cs = W.lane[ln].cool_steps;
+    E.l_mask = W.mlmask ? sb + Z::kSMask + ln * Z::kRow * 4 : 0u;
+    const size_t pitch = (size_t)A.pitch;
+    const int steps = A.steps;
+    // the 32 warps of a CTA walk 32 neighbouring paths: the 128-byte line of a step is shared through L1/L2
+    for (int64_t path = (int64_t)blockIdx.x * kLeanWarps + warp; path < A.paths; path += (int64_t)gridDim.x * kLeanWarps) {
+        E.reset(sb, path);
+        const float* pc = A.close + path;
+        const float* ph = HL ? A.high + path : nullptr;
+        const float* pl = HL ? A.low + path : nullptr;
+        float cv = lane < steps ? __ldg(pc + (size_t)lane * pitch) : 0.f, hv = 0.f, lv = 0.f;
+        if (HL && lane < steps) { hv = __ldg(ph + (size_t)lane * pitch); lv = __ldg(pl + (size_t)lane * pitch); }
+        {   // DIR_UNKNOWN prefix: index of the first close that differs from close[0]
+            const float p0 = __shfl_sync(0xffffffffu, cv, 0);
+            int j0 = steps;
+            unsigned m = __ballot_sync(0xffffffffu, lane < steps && cv != p0);
+            if (m) j0 = __ffs((int)m) - 1;
+            else {
+                for (int i0 = 32; i0 < steps; i0 += 32) {
+                    const int idx = i0 + lane;
+                    const float v = idx < steps ? __ldg(pc + (size_t)idx * pitch) : p0;
+                    m = __ballot_sync(0xffffffffu, v != p0);
+                    if (m) { j0 = i0 + __ffs((int)m) - 1; break; }
+                }
+            }
+            E.prologue(p0, j0);
+        }
+        for (int i0 = 0; i0 < steps; i0 += 32) {
+            const int nidx = i0 + 32 + lane;                      // next chunk in flight while this one is walked
+            float cn = 0.f, hn = 0.f, lnx = 0.f;
+            if (nidx < steps) {
+                cn = __ldg(pc + (size_t)nidx * pitch);
+                if (HL) { hn = __ldg(ph + (size_t)nidx * pitch); lnx = __ldg(pl + (size_t)nidx * pitch); }
+            }
+            const int n = min(32, steps - i0);
+            if (n == 32) {
+#pragma unroll 4
+                for (int u = 0; u < 32; ++u) {
+                    const float pf = __shfl_sync(0xffffffffu, cv, u);
+                    const float hh = HL ? __shfl_sync(0xffffffffu, hv, u) : 0.f, ll = HL ? __shfl_sync(0xffffffffu, lv, u) : 0.f;
+                    E.step(A, pf, hh, ll, i0 + u, 0);
+                }
+            } else {
+#pragma unroll 1
+                for (int u = 0; u < n; ++u) {
+                    const float pf = __shfl_sync(0xffffffffu, cv, u);
+                    const float hh = HL ? __shfl_sync(0xffffffffu, hv, u) : 0.f, ll = HL ? __shfl_sync(0xffffffffu, lv, u) : 0.f;
+                    E.step(A, pf, hh, ll, i0 + u, 0);
+                }
+            }
+            cv = cn; hv = hn; lv = lnx;
+        }
+        E.finish(A);
+        if (live) {
+            uint32_t* u = su + lane;
+            double* dd = sd + lane;
+            atomicAdd(u + SW_NPATHS * 32, 1u);
+            if (E.c_gate & 0xffffu) atomicAdd(u + SW_OVER * 32, E.c_gate & 0xffffu);
+            if (E.c_gate >> 16) atomicAdd(u + SW_CONF * 32, E.c_gate >> 16);
+            if (E.c_ml & 0xffffu) atomicAdd(u + SW_ML * 32, E.c_ml & 0xffffu);
+            if (E.c_ml >> 16) atomicAdd(u + SW_WINS * 32, E.c_ml >> 16);
+            if (E.c_dir) atomicAdd(u + SW_DIR * 32, E.c_dir);
+            if (E.c_exit & 0xffffu) atomicAdd(u + SW_STOP * 32, E.c_exit & 0xffffu);
+            if (E.c_exit >> 16) atomicAdd(u + SW_TGT * 32, E.c_exit >> 16);
+            if (E.c_span & 0xffffu) atomicAdd(u + SW_INPOS * 32, E.c_span & 0xffffu);
+            if (E.c_span >> 16) atomicAdd(u + SW_COOL * 32, E.c_span >> 16);
+            if (E.is_open()) atomicAdd(u + SW_OPEN * 32, 1u);
+            if (E.pnl != 0.0) { atomicAdd(dd + SWD_PNL * 32, E.pnl); atomicAdd(dd + SWD_PATH2 * 32, E.pnl * E.pnl); }
+            if (E.pnl2 != 0.0) atomicAdd(dd + SWD_PNL2 * 32, E.pnl2);
+            if (E.mtm != 0.0) atomicAdd(dd + SWD_MTM * 32, E.mtm);
+            atomic_max_f64(dd + SWD_MAX * 32, E.pnl); atomic_max_f64(dd + SWD_NEGMIN * 32, -E.pnl);
+            atomicAdd(shist + E.hist_bin(A) * 32 + lane, 1u);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    if (threadIdx.x < W.n_lanes) {        // one thread per combo folds the CTA's tallies into that combo's reduction buffer
+        const uint32_t* u = su + threadIdx.x;
+        const double* dd = sd + threadIdx.x;
+        unsigned long long* gu = W.flat + (size_t)W.lane[threadIdx.x].combo * QMMX_AGG_SLOTS;
+        double* gd = reinterpret_cast<double*>(gu + QMMX_AGG_NU);
+        const unsigned long long np = u[SW_NPATHS * 32];
+        if (np) {
+            const unsigned long long nsteps = np * (unsigned long long)steps;
+            const unsigned long long ntr = (unsigned long long)u[SW_STOP * 32] + u[SW_TGT * 32], nopen = u[SW_OPEN * 32];
+            const unsigned long long coded = (unsigned long long)u[SW_OVER * 32] + u[SW_CONF * 32] + u[SW_ML * 32] + u[SW_DIR * 32] +
+                                             u[SW_INPOS * 32] + u[SW_COOL * 32] + ntr + nopen;
+            auto add = [&](int slot, unsigned long long v) { if (v) atomicAdd(&gu[slot], v); };
+            add(U_NPATHS, np); add(U_NSTEPS, nsteps); add(U_NTRADES, ntr); add(U_NWINS, u[SW_WINS * 32]); add(U_NOPEN, nopen);
+            add(U_ENTRY + QMMX_OK_ENTRY, ntr + nopen);
+            add(U_ENTRY + QMMX_LEVEL_OVERTOUCHED, u[SW_OVER * 32]); add(U_ENTRY + QMMX_CONF_LOW, u[SW_CONF * 32]);
+            add(U_ENTRY + QMMX_ML_CONF_LOW, u[SW_ML * 32]); add(U_ENTRY + QMMX_DIR_UNKNOWN, u[SW_DIR * 32]);
+            add(U_ENTRY + QMMX_IN_POSITION, u[SW_INPOS * 32]); add(U_ENTRY + QMMX_COOLDOWN, u[SW_COOL * 32]);
+            add(U_ENTRY + QMMX_TOO_FAR, nsteps - coded);
+            add(U_EXIT + QMMX_EXIT_STOP, u[SW_STOP * 32]); add(U_EXIT + QMMX_EXIT_TARGET, u[SW_TGT * 32]);
+            add(U_EXIT + QMMX_EXIT_OPEN, nopen);
+            if (dd[SWD_PNL * 32] != 0.0) atomicAdd(&gd[D_SUM_PNL], dd[SWD_PNL * 32]);
+            if (dd[SWD_PNL2 * 32] != 0.0) atomicAdd(&gd[D_SUM_PNL2], dd[SWD_PNL2 * 32]);
+            if (dd[SWD_PATH2 * 32] != 0.0) atomicAdd(&gd[D_SUM_PATH2], dd[SWD_PATH2 * 32]);
+            if (dd[SWD_MTM * 32] != 0.0) atomicAdd(&gd[D_SUM_MTM], dd[SWD_MTM * 32]);
+            atomic_max_f64(&gd[QMMX_AGG_ND + 0], dd[SWD_MAX * 32]);
+            atomic_max_f64(&gd[QMMX_AGG_ND + 1], dd[SWD_NEGMIN * 32]);
+        }
+    }
+    for (int t = threadIdx.x; t < QMMX_PNL_HIST_BINS * 32; t += blockDim.x) {
+        const int ln2 = t & 31;
+        const uint32_t v = shist[t];
+        if (v && ln2 < W.n_lanes)
+            atomicAdd(&W.flat[(size_t)W.lane[ln2].combo * QMMX_AGG_SLOTS + U_HIST + (t >> 5)], (unsigned long long)v);
+    }
 }
 
 }  // namespace qmmx

@@ -605,3 +605,42 @@ def test_gpu_fp32_probe_is_plausible(eng):
     """The FFMA-only probe behind bench.py's roofline_fp32: a B200 sustains tens of TFLOP/s, never above nominal."""
     v = eng.measure_fp32_peak()
     assert 20.0 < v < 90.0, v
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
+def test_gpu_sweep_kernel_equals_per_combo_kernels(eng, hl, monkeypatch):
+    """Parameter sweeps run 32 combos to a warp over one path (lean_sweep_kernel).  77 combos = two full warps of lanes
+    + a 13-combo tail that stays on the per-combo kernel, a second family (other CONTACT_PROX) of 24 lanes, LR gate
+    on (its mask depends on STOP_PADDING, so it differs per lane).  Against the per-combo kernels (QMMX_NO_SWEEP=1)
+    on every aggregate, and against the C oracle on a few combos."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    grid = [abi.make_params(contact_prox=0.1, stop_padding=sp, tp_padding=tp, cooldown_s=cd, exit_on_hl=hl)
+            for sp in (0.10, 0.2, 0.35, 0.5, 0.85, 0.0, 1.5) for tp in (0.15, 0.25, 0.5) for cd in (0, 60, 300, 7200)][:77]
+    grid += [abi.make_params(contact_prox=0.05, q_min_prob=0.5, stop_padding=0.1 + 0.03 * i, cooldown_s=120, exit_on_hl=hl)
+             for i in range(24)]
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    g = abi.make_gbm(sub_steps=4 if hl else 1)
+    P, T = 3001, 395                       # ragged: not a multiple of the warp count, last chunk of 11 steps
+    monkeypatch.setenv("QMMX_NO_SWEEP", "1")
+    plain = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_NO_SWEEP")
+    try:
+        out = []
+        for e in (eng, plain):
+            configure(e, price, solid, grid, lr)
+            e.gen_gbm(11, 0, P, T, g)
+            n0 = e.launch_count()
+            out.append(e.run_scan())
+            launches = e.launch_count() - n0
+            if e is eng:
+                assert launches < len(grid) // 2          # 2 + 1 sweep launches + the 13-combo tail (+ the reduction)
+        for a, b in zip(*out):
+            assert_agg_equal(a.agg, b.agg)
+        c, h, l = eng.download_bars(P, T, hl=hl)
+        for ci in (0, 31, 32, 76, 77, 100):
+            o = CO.run_paths(c, price, solid, grid[ci], lr=lr, high=h if hl else None, low=l if hl else None, n_threads=4)
+            assert_agg_equal(out[0][ci].agg, o["agg"])
+        assert len({r.n_trades for r in out[0]}) > 20        # the combos really differ
+    finally:
+        plain.close()
