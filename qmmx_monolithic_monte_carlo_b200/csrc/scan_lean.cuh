@@ -288,6 +288,23 @@ struct LeanEngine {
         }
     }
 
+    // level whose contact zone holds p, or kFar: the cell byte of step(), fully resolved
+    __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
+        const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase) >> A.cell_shift, (uint32_t)(A.cell_ncell - 1));
+        uint32_t v = lds_u8<Y::kCell>(sb + c);
+        if (v >= kMixBase && v != kFar) {
+            if (v == kMixed) {
+                if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
+                else v = classify_zones(pf);
+            } else {
+                const float2 r = lds_f2<Y::kMix>(sb + (v - kMixBase) * 8);
+                const uint32_t lohi = (uint32_t)__float_as_int(r.y);
+                v = pf <= r.x ? (lohi & 0xffu) : (lohi >> 8);
+            }
+        }
+        return v;
+    }
+
     __device__ __forceinline__ void finish(const ScanArgs& A) {
         // COOLDOWN steps (M:1516): every exit is followed by cool_steps - 1 of them, except that the last one may be cut
         // by the end of the path (only the last: no entry can follow an exit whose cooldown outlasts the path)
@@ -624,6 +641,11 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
             }
             E.prologue(p0, j0);
         }
+        // Each lane classifies ONE step of the 32-step chunk (price change, contact zone); three ballots then tell the
+        // whole warp which steps can matter.  While no lane holds a position the walk jumps from contact step to contact
+        // step; while some lane does, every step is an exit test (two compares) and nothing else.
+        float carry_p = __shfl_sync(0xffffffffu, cv, 0);          // price before the chunk's first step (close[0] at the start)
+        uint32_t carry_side = 0u;                                 // side of the last non-zero price change so far
         for (int i0 = 0; i0 < steps; i0 += 32) {
             const int nidx = i0 + 32 + lane;                      // next chunk in flight while this one is walked
             float cn = 0.f, hn = 0.f, lnx = 0.f;
@@ -632,23 +654,38 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
                 if (HL) { hn = __ldg(ph + (size_t)nidx * pitch); lnx = __ldg(pl + (size_t)nidx * pitch); }
             }
             const int n = min(32, steps - i0);
-            if (n == 32) {
-#pragma unroll 4
-                for (int u = 0; u < 32; ++u) {
-                    const float pf = __shfl_sync(0xffffffffu, cv, u);
-                    const float hh = HL ? __shfl_sync(0xffffffffu, hv, u) : 0.f, ll = HL ? __shfl_sync(0xffffffffu, lv, u) : 0.f;
-                    E.step(A, pf, hh, ll, i0 + u, 0);
+            const float up = __shfl_up_sync(0xffffffffu, cv, 1);
+            const float df = lane < n ? cv - (lane == 0 ? carry_p : up) : 0.f;
+            const unsigned nz = __ballot_sync(0xffffffffu, df != 0.f), ng = __ballot_sync(0xffffffffu, df < 0.f);
+            const uint32_t vv = lane < n ? E.classify(A, cv) : (uint32_t)kFar;
+            const unsigned cm = __ballot_sync(0xffffffffu, vv != kFar);
+            int u = 0;
+            while (u < n) {
+                __syncwarp();
+                if (!__any_sync(0xffffffffu, E.cool == kNoCool)) {
+                    const unsigned rem = cm >> u;
+                    if (!rem) break;
+                    u += __ffs((int)rem) - 1;
                 }
-            } else {
-#pragma unroll 1
-                for (int u = 0; u < n; ++u) {
-                    const float pf = __shfl_sync(0xffffffffu, cv, u);
-                    const float hh = HL ? __shfl_sync(0xffffffffu, hv, u) : 0.f, ll = HL ? __shfl_sync(0xffffffffu, lv, u) : 0.f;
-                    E.step(A, pf, hh, ll, i0 + u, 0);
+                const int i = i0 + u;
+                const float pf = __shfl_sync(0xffffffffu, cv, u);
+                const float xl = HL ? __shfl_sync(0xffffffffu, lv, u) : pf, xh = HL ? __shfl_sync(0xffffffffu, hv, u) : pf;
+                const bool elig = i >= E.cool;                    // as step(): decided before this step's exit
+                const bool hit_lo = xl <= E.lo_thr, hit_hi = xh >= E.hi_thr;
+                if (hit_lo | hit_hi) E.do_exit(A, pf, hit_lo, hit_hi, i);
+                if ((cm >> u) & 1u) {
+                    const unsigned m = nz & (0xffffffffu >> (31 - u));
+                    const uint32_t side = m ? (ng >> (31 - __clz((int)m))) & 1u : carry_side;
+                    const uint32_t v = __shfl_sync(0xffffffffu, vv, u);
+                    if (elig) { E.d = side ? -1.f : 1.f; E.contact(A, (int)v, pf, i, 0); }
                 }
+                ++u;
             }
+            if (nz) carry_side = (ng >> (31 - __clz((int)nz))) & 1u;
+            carry_p = __shfl_sync(0xffffffffu, cv, n - 1);
             cv = cn; hv = hn; lv = lnx;
         }
+        E.prev = carry_p;                                         // last close (mark-to-market of an open position)
         E.finish(A);
         if (live) {
             uint32_t* u = su + lane;
