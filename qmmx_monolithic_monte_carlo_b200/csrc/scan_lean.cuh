@@ -659,6 +659,9 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
             const unsigned nz = __ballot_sync(0xffffffffu, df != 0.f), ng = __ballot_sync(0xffffffffu, df < 0.f);
             const uint32_t vv = lane < n ? E.classify(A, cv) : (uint32_t)kFar;
             const unsigned cm = __ballot_sync(0xffffffffu, vv != kFar);
+            // side of the last non-zero price change up to this lane's step (M:1529-1538, M:1645), packed beside the level
+            const unsigned mine = nz & (0xffffffffu >> (31 - lane));
+            const uint32_t vs = vv | ((mine ? (ng >> (31 - __clz((int)mine))) & 1u : carry_side) << 8);
             int u = 0;
             while (u < n) {
                 __syncwarp();
@@ -674,10 +677,8 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
                 const bool hit_lo = xl <= E.lo_thr, hit_hi = xh >= E.hi_thr;
                 if (hit_lo | hit_hi) E.do_exit(A, pf, hit_lo, hit_hi, i);
                 if ((cm >> u) & 1u) {
-                    const unsigned m = nz & (0xffffffffu >> (31 - u));
-                    const uint32_t side = m ? (ng >> (31 - __clz((int)m))) & 1u : carry_side;
-                    const uint32_t v = __shfl_sync(0xffffffffu, vv, u);
-                    if (elig) { E.d = side ? -1.f : 1.f; E.contact(A, (int)v, pf, i, 0); }
+                    const uint32_t w = __shfl_sync(0xffffffffu, vs, u);
+                    if (elig) { E.d = (w >> 8) ? -1.f : 1.f; E.contact(A, (int)(w & 0xffu), pf, i, 0); }
                 }
                 ++u;
             }
