@@ -642,5 +642,23 @@ def test_gpu_sweep_kernel_equals_per_combo_kernels(eng, hl, monkeypatch):
             o = CO.run_paths(c, price, solid, grid[ci], lr=lr, high=h if hl else None, low=l if hl else None, n_threads=4)
             assert_agg_equal(out[0][ci].agg, o["agg"])
         assert len({r.n_trades for r in out[0]}) > 20        # the combos really differ
+        for P2, T2 in ((1, 1), (5, 33), (40, 2)):            # degenerate shapes: one step, a chunk boundary, idle warps
+            got = []
+            for e in (eng, plain):
+                e.gen_gbm(12, 0, P2, T2, g)
+                got.append(e.run_scan())
+            for a, b in zip(*got):
+                assert_agg_equal(a.agg, b.agg)
+        if not hl:   # constant prices (no direction ever) and a first price change beyond the first 32-step chunk
+            close = F.host_gbm_closes(64, 100, seed=5)
+            close[:, :8] = np.float32(648.76)
+            close[:45, 8:16] = close[45, 8:16]
+            got = []
+            for e in (eng, plain):
+                e.upload_bars(close)
+                got.append(e.run_scan())
+            for a, b in zip(*got):
+                assert_agg_equal(a.agg, b.agg)
+            assert got[0][0].entry_hist["DIR_UNKNOWN"] >= 8 * 100 + 8 * 45
     finally:
         plain.close()
