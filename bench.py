@@ -282,6 +282,55 @@ def run_extra(args, name, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def run_jitter_bench(args, rank, local_rank, world):
+    """SURVEY 8(d) jitter-MC mode: the reference's own Monte Carlo (`simulate_monte_carlo`, M:3353-3538) — candidates
+    found on the host over one 390-bar day, trials x candidates forward walks on the device (Philox draws).  Unit:
+    candidate-trials/s (one jittered walk to its stop, target or the end of the day); the walks end at the first hit,
+    so bars-visited is data dependent and only its upper bound (n - candidate bar - 1 per walk) is printed beside it.
+    The reference spends ~6 us per candidate-trial in pure Python."""
+    import torch
+    from qmmx_monolithic_monte_carlo_b200 import engine as E, montecarlo as MC
+    torch.cuda.set_device(local_rank)
+    eng = E.MCEngine(local_rank, args.lib)
+    w = F.synthetic_window(390, seed=11)
+    c, h, l = (w[:, 3].astype(np.float64), w[:, 1].astype(np.float64), w[:, 2].astype(np.float64))
+    rows, price, _ = E.sort_levels(F.levels_30())
+    cands = MC.find_candidates(c, price, 0.10, 0.35, 0.25, 2)
+    trials = args.paths or (1 << 22)
+    sig = (0.02, 0.01, 0.0, 0.0)
+    units = trials * sum(len(c) - cd["i"] - 1 for cd in cands)
+    run = lambda: eng.run_jitter(h, l, cands, 0.35, 0.25, sig, trials, seed=7 + rank)
+    for _ in range(args.warmup):
+        run()
+    sampler = ClockSampler(local_rank); sampler.start()
+    l0 = eng.launch_count()
+    ks, t0 = [], time.perf_counter()
+    for _ in range(args.steps):
+        out = run()
+        ks.append(eng.last_timing_ms())
+    wall = (time.perf_counter() - t0) / args.steps
+    clocks = sampler.stop()
+    launches = eng.launch_count() - l0
+    k_ms = float(np.mean(ks))
+    if rank == 0:
+        s = MC.summarize(out["totals"], out["drawdowns"], out["wins"], out["losses"], out["opens"], len(cands))
+        print(json.dumps({
+            "metric": "jitter Monte Carlo candidate-trials/sec", "value": trials * len(cands) / (k_ms * 1e-3), "unit": "candidate-trials/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": k_ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"jitter MC: {trials} trials x {len(cands)} candidates over one 390-bar day, 30 levels",
+                       "timing": "device time of jitter_kernel (CUDA events on the ctx stream)",
+                       "candidate_trial_steps_upper_bound_per_s": units / (k_ms * 1e-3)},
+            "roofline": {"bound": "hbm", "achieved": 0.0, "peak": measured_peak_hbm()[0], "unit": "GB/s", "frac": 0.0, "traffic": None,
+                         "note": "high/low live in shared memory: no HBM bytes per step (SURVEY 8d); outputs are 32 B per trial"},
+            "e2e": {"value": trials * len(cands) / wall, "unit": "candidate-trials/s", "h2d_bytes_per_step": int(h.nbytes + l.nbytes),
+                    "d2h_bytes_per_step": int(trials * 28), "ms_per_step": wall * 1e3,
+                    "api": "MCEngine.run_jitter -> qmmx_run_jitter (host arrays in, per-trial totals out)"},
+            "clocks": clocks, "gpu_launches": launches,
+            "result_check": {"candidates": len(cands), "mean_R": s.mean, "var05": s.var05}}), flush=True)
+    eng.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -299,6 +348,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "ours" and args.workload == "mc":
+        run_jitter_bench(args, rank, local_rank, world)
+        return
     if args.impl == "ours" and args.workload in ("c3", "c4", "c5", "c5f", "c2hl"):
         run_extra(args, args.workload, rank, local_rank, world)
         return
