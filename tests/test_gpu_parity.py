@@ -662,3 +662,29 @@ def test_gpu_sweep_kernel_equals_per_combo_kernels(eng, hl, monkeypatch):
             assert got[0][0].entry_hist["DIR_UNKNOWN"] >= 8 * 100 + 8 * 45
     finally:
         plain.close()
+
+
+@pytest.mark.gpu
+def test_gpu_sweep_kernel_full_c4_size(eng, monkeypatch):
+    """BASELINE config 4 at full size (256 combos x 1M resident paths x 390): the sweep kernel's aggregates equal the
+    per-combo kernels' for every combo, and the counters of each combo partition its path-steps."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    grid = [abi.make_params(contact_prox=0.10, stop_padding=0.10 + 0.05 * i, tp_padding=tp, cooldown_s=cd)
+            for i in range(16) for tp in (0.15, 0.25, 0.35, 0.50) for cd in (0, 60, 300, 900)]
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    P, T = 1_000_000, 390
+    monkeypatch.setenv("QMMX_NO_SWEEP", "1")
+    plain = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_NO_SWEEP")
+    try:
+        out = []
+        for e in (eng, plain):
+            configure(e, price, solid, grid, lr)
+            e.gen_gbm(F.HOST_SEED, 0, P, T, abi.make_gbm())
+            out.append(e.run_scan())
+        for a, b in zip(*out):
+            assert_agg_equal(a.agg, b.agg, sums_rel=1e-12)
+            assert a.n_paths == P and a.n_steps == P * T == sum(a.entry_hist.values())
+            assert a.n_trades == a.exit_hist["STOP"] + a.exit_hist["TARGET"] and a.entry_hist["OK"] == a.n_trades + a.n_open
+    finally:
+        plain.close()
