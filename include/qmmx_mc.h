@@ -174,6 +174,10 @@ int  qmmx_set_stream(qmmx_ctx* ctx, void* cuda_stream);    /* run on a caller st
 /* levels in the reference's load_levels order (ORDER BY color, level_type, level_index): ties in the
  * nearest-level search go to the FIRST level in this order (Python min, M:1543). */
 int  qmmx_set_levels(qmmx_ctx* ctx, const double* price, const uint8_t* solid, int n_levels);
+/* one qmmx_params per parameter combination; every run reports one qmmx_agg per combo, in this order.  Combos that
+ * differ only in STOP_PADDING / TP_PADDING / cooldown (a sweep, 20 or more of them, no blend / policy / veto) are
+ * evaluated 32 to a warp over the same path by one launch; the results are identical to one launch per combo
+ * (environment QMMX_NO_SWEEP=1 forces the latter). */
 int  qmmx_set_params(qmmx_ctx* ctx, const qmmx_params* params, int n_combos);
 int  qmmx_set_lr(qmmx_ctx* ctx, const double* coef_intercept /* [n_days][5] */, int n_days);   /* n_days 0 = no model */
 int  qmmx_set_policy(qmmx_ctx* ctx, const double* w /* [n_days][3][7] */, int n_days);        /* n_days 0 = zero weights */
