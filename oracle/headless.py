@@ -58,6 +58,9 @@ class Params:
     exit_on_hl: bool = False          # [CHOICE] False: live exits on close (M:2966-3014)
     overtouch_limit: int = 4          # hard-coded M:1579
     steps_per_day: int = 390
+    online_retrain: bool = False      # OnlinePolicy learns from its own closed trades (M:3753-3803), see run_path
+    policy_lr: float = 0.03           # OnlinePolicy(lr=0.03, l2=1e-6), M:290
+    policy_l2: float = 1e-6
 
 
 @dataclass
@@ -101,6 +104,7 @@ class PathResult:
     entry_hist: List[int] = field(default_factory=lambda: [0] * N_ENTRY_CODES)
     exit_hist: List[int] = field(default_factory=lambda: [0] * N_EXIT_CODES)
     touch_counts: List[int] = field(default_factory=list)
+    policy_weights: Optional[dict] = None      # online_retrain: the OnlinePolicy entry heads at the end of the path
 
 
 def dot_py312(w: Sequence[float], x: Sequence[float]) -> float:
@@ -252,6 +256,18 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
     lr: per-day list of LRModel (or None = no model, M:1455); day = i // steps_per_day,
         clamped to the last entry.
     policy: per-day list of {"go_long","go_short","skip"} weight vectors (7 each).
+
+    online_retrain: every trade leaves TWO policy_events rows carrying its id: the PRE_OPEN row that
+    `evaluate_entry` writes on OK (M:1757-1768: proximity_abs, approach, touch_count, conf, ml_prob), which
+    `open_trade` attaches to the trade (M:1899-1911), and the {"x": x} row of the live loop (M:3139-3150).
+    `close_trade` labels both pnl > 0 (M:1936-1941) and `_retrain_from_labeled_events` (M:3753-3803, Tk timer
+    M:3824-3828) feeds the labelled rows, once each and in id order, to `update_entry` (M:357-363: one logistic SGD
+    step with L2 on the head of the action taken).  The retrain rebuilds the features from the row's keys: the first
+    row gives [1, min(1, |p - L|), 0, from_above, from_below, 0, 0] (no confluence, no minutes key), the second has
+    none of the keys (only "x"), so it trains on the defaults [1, 0, 0, 1, 0, 0, 0] -- reproduced here, it is what
+    the reference computes.  [CHOICE] the 2-minute timer is modelled as "before every tick": a label written at
+    tick i is learnt before tick i+1 is evaluated.  `policy` must then hold ONE
+    table: the initial weights; what is learnt carries over the day boundaries.
     """
     P = params
     L = len(levels)
@@ -273,10 +289,27 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
     w_rules, w_ml = w_rules / s, w_ml / s
 
     guard = RegimeGuard() if volume is not None else None    # always on in the reference; inert without volume
+    learn = bool(P.online_retrain) and not P.disable_policy_gate
+    if learn:
+        if policy is not None and len(policy) != 1:
+            raise ValueError("online_retrain starts from ONE weight table")
+        w0 = policy[0] if policy else {}
+        wlearn = {a: [float(v) for v in w0.get(a, [0.0] * 7)] for a in ("go_long", "go_short", "skip")}
+        policy = [wlearn]
+    pending = []            # closed trades whose two labelled rows are not trained yet: (action, label, |p - L| at entry, side)
     for i, p in enumerate(close):
         p = float(p)
         now = 60000 * i
         day = i // P.steps_per_day
+        for action, label, dist0, side0 in pending:                   # M:3771-3790 -> update_entry M:357-363
+            w = wlearn[action]
+            for xr in ([1.0, min(1.0, dist0), 0.0, 1.0 if side0 == 1 else 0.0, 1.0 if side0 == 0 else 0.0, 0.0, 0.0],
+                       [1.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0]):          # PRE_OPEN row, then the {"x": ...} row
+                pred = sigmoid_policy(dot_py312(w, xr))
+                grad = [(pred - label) * xi + P.policy_l2 * wi for wi, xi in zip(w, xr)]     # M:339
+                for q in range(7):
+                    w[q] -= P.policy_lr * grad[q]
+        pending = []
         if guard is not None and i >= 1:                          # ingest_tick closes bar i-1 (M:2932, M:1864-1870)
             cb = float(close[i - 1])
             guard.push(60000 * (i - 1), cb, cb, cb, float(volume[i - 1] or 0.0))
@@ -408,6 +441,8 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
                 res.trades.append(Trade(pos["entry_bar"], i, side, pos["level"], reason,
                                         entry, exit_px, pnl))
                 res.exit_hist[reason] += 1
+                if learn:
+                    pending.append(("go_long" if side == 0 else "go_short", 1 if pnl > 0 else 0, pos["dist"], side))   # M:1936
                 pos = None
         elif ok_extras is not None:
             side, k, stop, target, dist = ok_extras
@@ -427,7 +462,7 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
             if not pass_gate:
                 code = E["ONLINE_POLICY"]
             else:
-                pos = dict(side=side, entry=p, stop=stop, target=target, level=k, entry_bar=i)
+                pos = dict(side=side, entry=p, stop=stop, target=target, level=k, entry_bar=i, dist=dist)
         res.codes.append(code)
         res.entry_hist[code] += 1
 
@@ -438,6 +473,7 @@ def run_path(close: Sequence[float], levels: Sequence[Level], params: Params, *,
                                 pos["entry"], last, 0.0, mtm))
         res.exit_hist[X["OPEN"]] += 1
     res.touch_counts = touch
+    res.policy_weights = wlearn if learn else None
     return res
 
 

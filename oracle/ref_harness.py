@@ -151,7 +151,7 @@ def make_sklearn_model(coef, intercept):
 
 
 def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy_w=None,
-                         disable_policy_gate=True, steps_per_day=390, volume=None):
+                         disable_policy_gate=True, steps_per_day=390, volume=None, online_retrain=False):
     """Run the real `evaluate_entry` over one close series with the live loop's order.
 
     Transcribes `_engine_loop` (`qmmx_monolithic.py:2927-3016`, `3044-3115`) with the
@@ -165,11 +165,22 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
               min(i+1, 240) bars `{t,o,h,l,c,v}` (Appendix A), which is what `_calc_volume_slope` reads.
               When the soft veto fires the reference raises NameError (`VETO` is undefined, M:1705,
               Appendix C) AFTER writing its policy_events row; the step code is taken from that row.
+    online_retrain: the live loop's learning path run for real: an entry that passes the policy gate files the
+              policy_events row of M:3139-3150 (features_json {"x": x}, trade id), the engine's own `close_trade` labels it
+              (M:1936-1941) and the unbound `QMMXApp._retrain_from_labeled_events` (M:3753-3803) is called before every
+              tick on the reference's own `OnlinePolicy`; `policy_w` is then ONE weight table, the initial weights.
     Returns dict(codes=[...str per step], trades=[...], touch_counts=...).
     """
     q, conn, eng = make_engine(levels, settings)
     eng.model = lr_model if not isinstance(lr_model, list) else None
     policy = q.OnlinePolicy()
+    if online_retrain:
+        policy.build_features(proximity_abs=0.0, volume_trend=0.0, approach="from_above", confluence=False,
+                              minutes_since_open=0)               # fixes the dimension and zero-fills the heads (M:321-327)
+        if policy_w is not None:
+            w0 = policy_w[0] if isinstance(policy_w, list) else policy_w
+            policy.w_entry = {k: list(map(float, v)) for k, v in w0.items()}
+        app = types.SimpleNamespace(conn=conn, policy=policy, _log_ui=lambda *a, **k: None, _save_policy=lambda: None)
     cool_s = eng.Q_SIGNAL_COOLDOWN_S
     codes, trades = [], []
     pos = None
@@ -181,6 +192,8 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
         prev_price = eng.state.last_price
         now_ms = 60000 * i
         eng.state.last_ts_ms = now_ms  # always fresh (Appendix A [CHOICE])
+        if online_retrain:
+            q.QMMXApp._retrain_from_labeled_events(app, max_rows=1000)      # Tk timer body, M:3824-3828
         if volume is not None:
             # the live loop feeds every tick to ingest_tick before evaluate_entry (M:2932): it rolls the one-tick minute
             # bar i-1 into acc_guard / touchmem (M:1857-1883, M:1813-1855)
@@ -238,7 +251,7 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
                 x = policy.build_features(proximity_abs=abs(price - lvl_price), volume_trend=0.0,
                                           approach=approach, confluence=(len(cluster) > 1),
                                           minutes_since_open=i % steps_per_day)
-                if w is not None:
+                if w is not None and not online_retrain:
                     policy.w_entry = {k: list(v) for k, v in w.items()}
                 scores = policy.score_entry(x)
                 chosen = "go_long" if side == "long" else "go_short"
@@ -246,7 +259,13 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
             if not pass_gate:
                 step_code = "ONLINE_POLICY"
             else:
-                eng.open_trade(extras["side"], price, extras["stop"], extras["target"], "sim")
+                tid = eng.open_trade(extras["side"], price, extras["stop"], extras["target"], "sim")
+                if online_retrain and not disable_policy_gate:
+                    conn.execute("INSERT INTO policy_events (ts, phase, action, features_json, trade_id, notes) "
+                                 "VALUES (?,?,?,?,?,?)",
+                                 (q.utcnow(), "entry", "go_long" if extras["side"] == "long" else "go_short",
+                                  json.dumps({"x": x}), tid, "sim"))                       # M:3139-3150
+                    conn.commit()
                 pos = dict(side=extras["side"], stop=extras["stop"], target=extras["target"],
                            entry=price, entry_bar=i, level=tuple(extras["level"]))
         codes.append(step_code)
@@ -263,6 +282,7 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
             r = json.loads(fj).get("reason", "UNKNOWN_REASON")
             fold[r] = fold.get(r, 0) + 1
     return dict(codes=codes, trades=trades, skip_rows=skip_rows, policy_skip_rows=policy_skip_rows,
+                policy_weights={k: list(v) for k, v in policy.w_entry.items()},
                 touch_counts=dict(eng.state.level_touch_counts),
                 touchmem_touches=dict(eng.touchmem.touch), touchmem_edge_taps=len(eng.touchmem.edge_taps),
                 regime=eng.acc_guard.regime)

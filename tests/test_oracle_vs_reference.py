@@ -25,7 +25,8 @@ def _check(levels, params, closes, lr=None, pol=None, volume=None):
     for j in range(closes.shape[1]):
         vj = None if volume is None else [float(x) for x in volume[:, j]]
         ref = rh.drive_reference_path(closes[:, j], levels, settings_for(params), lr_model=models,
-                                      policy_w=pol, disable_policy_gate=P.disable_policy_gate, volume=vj)
+                                      policy_w=pol, disable_policy_gate=P.disable_policy_gate, volume=vj,
+                                      online_retrain=P.online_retrain)
         o = H.run_path(closes[:, j], lv, P, lr=lr, policy=pol, volume=vj)
         assert [H.ENTRY_CODES[c] for c in o.codes] == ref["codes"]
         assert len(o.trades) == len(ref["trades"])
@@ -34,6 +35,8 @@ def _check(levels, params, closes, lr=None, pol=None, volume=None):
                    (b.entry_bar, b.exit_bar, H.EXIT_CODES[b.reason], lv[b.level].key, ("long", "short")[b.side])
             assert a["pnl"] == b.pnl and a["entry"] == b.entry and a["exit"] == b.exit
         assert {lv[i].key: t for i, t in enumerate(o.touch_counts) if t} == ref["touch_counts"]
+        if P.online_retrain:
+            assert o.policy_weights == ref["policy_weights"]        # every float64 weight, bit for bit
         # the reason histogram (what the product's results sink keeps) == log_analyzer's fold of the policy_events rows:
         # action='skip' rows for the gate reasons, action='policy_skip' rows for 904 / soft veto (M:1658, M:1694; the veto
         # row carries the bare veto code).  ONLINE_POLICY rows are written by the GUI loop (M:3097), not by the engine.
@@ -103,6 +106,29 @@ def test_regime_guard_against_reference():
         n904 += sum(1 for c in o.codes if H.ENTRY_CODES[c] == "ACC_BREAKOUT_GATE")
         regimes |= set(H.regime_series(closes[:, j], vol[:, j]))
     assert n904 >= 3 and regimes == {0, 1, 2, 3}
+
+
+def test_online_policy_retrain_against_reference():
+    """the reference's OnlinePolicy learning from its own closed trades, driven for real (rows, labels,
+    `_retrain_from_labeled_events`), against the oracle: per-tick codes, trades and every learnt weight identical.
+    Three days per path, so that the learning (a bias step per trade, whatever the entry looked like -- the retrain
+    reads feature keys the rows do not have) turns the gate against one side and ONLINE_POLICY skips appear."""
+    closes = F.host_gbm_closes(4, 3 * 390, seed=404)
+    pol = [{"go_long": [0.55, -0.3, 0.0, 0.0, 0.0, 0.05, -0.1], "go_short": [0.5, -0.2, 0.0, 0.0, 0.0, 0.05, 0.05],
+            "skip": [-0.6, 0.2, 0.0, 0.0, 0.1, -0.1, 0.1]}]
+    params = dict(contact_prox=0.1, cooldown_s=60, disable_policy_gate=False, online_retrain=True)
+    _check(F.levels_30(), params, closes, pol=pol)
+    lv = H.sort_levels(F.levels_30())
+    n_pol, moved, changed = 0, 0.0, 0
+    for j in range(closes.shape[1]):
+        o = H.run_path(closes[:, j], lv, H.Params(**params), policy=pol)
+        n_pol += sum(1 for c in o.codes if H.ENTRY_CODES[c] == "ONLINE_POLICY")
+        moved += abs(o.policy_weights["go_long"][0] - 0.55) + abs(o.policy_weights["go_short"][0] - 0.5)
+        assert o.policy_weights["skip"] == pol[0]["skip"]            # only the head of the action taken learns
+        assert o.policy_weights["go_long"][1] != -0.3                # L2 decay and the proximity feature move it
+        frozen = H.run_path(closes[:, j], lv, H.Params(**dict(params, online_retrain=False)), policy=pol)
+        changed += frozen.codes != o.codes                           # the learning changes decisions
+    assert n_pol > 0 and moved > 0.1 and changed >= 2
 
 
 def test_touch_memory_is_inert_in_the_reference():
