@@ -83,6 +83,10 @@ enum { QMMX_EXIT_STOP = 0, QMMX_EXIT_TARGET, QMMX_EXIT_ESCALATE, QMMX_EXIT_OPEN 
 #define QMMX_F_EXIT_ON_HL           (1u << 4)  /* exits tested on bar low/high, stop first (M:3621-3636) */
 #define QMMX_F_TINY_PRICES          (1u << 5)  /* prices below 2^-5 may occur: evaluate the +-1e-9 direction guard
                                                   (M:1529-1537) in float64 on every tick instead of the fp32 shortcut */
+#define QMMX_F_ONLINE_RETRAIN       (1u << 6)  /* the OnlinePolicy go_long / go_short heads learn from the path's own closed
+                                                 * trades (update_entry M:357-363 through _retrain_from_labeled_events
+                                                 * M:3753-3803, lr 0.03, l2 1e-6 of M:290): qmmx_set_policy gives ONE table, the
+                                                 * initial weights; needs the policy gate on, one combo, resident bars */
 
 typedef struct qmmx_params {
     uint32_t struct_size;      /* = sizeof(qmmx_params) */
@@ -206,6 +210,9 @@ int  qmmx_download_bars(qmmx_ctx* ctx, float* close, float* high, float* low);
  * its own data. */
 int  qmmx_upload_volume(qmmx_ctx* ctx, const float* volume, int64_t paths, int32_t steps);
 int  qmmx_download_volume(qmmx_ctx* ctx, float* volume);
+/* QMMX_F_ONLINE_RETRAIN: the learnt go_long / go_short heads of every path after the last qmmx_run_scan,
+ * out[path][14] float64 (go_long[7], go_short[7]); the skip head never learns (its rows carry no label) */
+int  qmmx_download_policy_weights(qmmx_ctx* ctx, double* out, int64_t paths);
 /* volume of the window bars ([window_len] fp32, NULL clears): the next qmmx_gen_bootstrap with the same
  * window_len also writes a volume plane (a resampled bar carries the volume of the window bar it came from) */
 int  qmmx_set_bootstrap_volume(qmmx_ctx* ctx, const float* window_volume, int32_t window_len);

@@ -89,14 +89,21 @@ def run_paths(close, levels_price, levels_solid, params: "abi.Params", *, high=N
     trades = np.zeros((paths, max_trades), dtype=abi.TRADE_DTYPE) if max_trades > 0 else None
     counts = np.zeros(paths, dtype=np.int32) if max_trades > 0 else None
     agg = abi.Agg()
+    polw = None
+    if params.flags & abi.F_ONLINE_RETRAIN:        # learnt go_long / go_short heads per path
+        polw = np.zeros((paths, 14), dtype=np.float64)
+        lib().oq_set_policy_weights_out.argtypes = [C.c_void_p]
+        lib().oq_set_policy_weights_out(_ptr(polw))
     rc = lib().oq_run_paths_v(_ptr(close), _ptr(high), _ptr(low), _ptr(volume), paths, steps, _ptr(lp), _ptr(ls), len(lp),
                             C.byref(params), _ptr(lr_a), 0 if lr_a is None else len(lr_a),
                             _ptr(pol_a), 0 if pol_a is None else len(pol_a),
                             float(hist_range[0]), float(hist_range[1]),
                             _ptr(codes), _ptr(trades), _ptr(counts), max_trades, C.byref(agg), n_threads)
+    if polw is not None:
+        lib().oq_set_policy_weights_out(None)
     if rc != 0:
         raise RuntimeError(f"oq_run_paths failed: {rc}")
-    return dict(agg=agg, codes=codes, trades=trades, counts=counts)
+    return dict(agg=agg, codes=codes, trades=trades, counts=counts, policy_weights=polw)
 
 
 def regime_series(close, volume):

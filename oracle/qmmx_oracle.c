@@ -119,6 +119,18 @@ void oq_regime_series(const float* close, const float* volume, int64_t paths, in
 double oq_volume_slope(const float* volume, int64_t paths, int64_t path, int i) { return volume_slope_at(volume, paths, path, i); }
 
 /* M:20-26 */
+static double* g_polw_out = NULL;
+
+static double sigmoid_policy(double x);
+
+/* OnlinePolicy.update_entry (M:357-363) -> _sgd_update (M:337-341): one logistic SGD step with L2, lr 0.03, l2 1e-6 (M:290) */
+static void policy_sgd(double* w, const double* x, int label) {
+    const double pred = sigmoid_policy(dot_py312(w, x, 7));
+    double grad[7];
+    for (int q = 0; q < 7; ++q) grad[q] = (pred - (double)label) * x[q] + 1e-6 * w[q];
+    for (int q = 0; q < 7; ++q) w[q] -= 0.03 * grad[q];
+}
+
 static double sigmoid_policy(double x) {
     if (x < -50) return 0.0;
     if (x > 50) return 1.0;
@@ -175,6 +187,8 @@ static void run_range(job_t* J) {
     const int blend = (P->flags & QMMX_F_USE_BLEND) != 0;
     const int no_pol = (P->flags & QMMX_F_DISABLE_POLICY_GATE) != 0;
     const int hl = (P->flags & QMMX_F_EXIT_ON_HL) != 0;
+    /* the two labelled policy_events rows of a closed trade train the head of its action (oracle/headless.py run_path) */
+    const int learn = !no_pol && (P->flags & QMMX_F_ONLINE_RETRAIN) != 0;
     const double inv_w = (double)QMMX_PNL_HIST_BINS / (J->hist_hi - J->hist_lo);
     qmmx_agg* A = &J->agg;
     memset(A, 0, sizeof(*A));
@@ -192,6 +206,8 @@ static void run_range(job_t* J) {
         memset(touch, 0, sizeof(touch)); memset(latch, 0, sizeof(latch));
         double p = 0.0;
         guard_t G; memset(&G, 0, sizeof(G));
+        double wl[14]; double pdist = 0.0;
+        for (int q = 0; q < 14; ++q) wl[q] = (learn && J->n_pol > 0) ? J->pol[q] : 0.0;
         for (int i = 0; i < J->steps; ++i) {
             p = (double)J->close[(int64_t)i * J->paths + path];
             if (J->volume && i >= 1) guard_push(&G, J->close, J->volume, J->paths, path, i - 1);   /* ingest_tick, M:2932 */
@@ -309,6 +325,12 @@ static void run_range(job_t* J) {
                     A->n_trades++; if (pnl > 0) A->n_wins++;
                     A->exit_hist[reason]++;
                     A->sum_pnl += pnl; A->sum_pnl2 += pnl * pnl; path_pnl += pnl;
+                    if (learn) {      /* PRE_OPEN row (M:1757-1768), then the {"x": x} row whose keys the retrain cannot read */
+                        const double xa[7] = {1.0, pdist < 1.0 ? pdist : 1.0, 0.0, pside == 1 ? 1.0 : 0.0, pside == 0 ? 1.0 : 0.0, 0.0, 0.0};
+                        const double xb[7] = {1.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0};
+                        policy_sgd(wl + 7 * pside, xa, pnl > 0 ? 1 : 0);
+                        policy_sgd(wl + 7 * pside, xb, pnl > 0 ? 1 : 0);
+                    }
                     in_pos = 0;
                 }
             } else if (ok) {
@@ -325,14 +347,14 @@ static void run_range(job_t* J) {
                     x[0] = 1.0; x[1] = pa < 1.0 ? pa : 1.0; x[2] = 0.0;
                     x[3] = side == 1 ? 1.0 : 0.0; x[4] = side == 0 ? 1.0 : 0.0;
                     x[5] = cluster > 1 ? 1.0 : 0.0; x[6] = tod < 1.0 ? tod : 1.0;
-                    const double s_go = sigmoid_policy(dot_py312(w + 7 * (side == 0 ? 0 : 1), x, 7));
+                    const double s_go = sigmoid_policy(dot_py312(learn ? wl + 7 * side : w + 7 * (side == 0 ? 0 : 1), x, 7));
                     const double s_skip = sigmoid_policy(dot_py312(w + 14, x, 7));
                     pass = (s_go >= 0.60) && (s_skip < 0.55);
                 }
                 if (!pass) code = QMMX_ONLINE_POLICY;
                 else {
                     in_pos = 1; pside = side; plevel = k; pentry = p; pstop = stop; ptarget = target;
-                    pentry_bar = i;
+                    pentry_bar = i; pdist = fabs(J->lprice[k] - p);
                 }
             }
             A->entry_hist[code]++;
@@ -352,6 +374,7 @@ static void run_range(job_t* J) {
             A->n_open++; A->exit_hist[QMMX_EXIT_OPEN]++; A->sum_open_mtm += mtm;
         }
         if (J->tcounts) J->tcounts[path] = ntr;
+        if (learn && g_polw_out) memcpy(g_polw_out + path * 14, wl, sizeof(wl));
         A->n_paths++;
         A->sum_path_pnl2 += path_pnl * path_pnl;
         if (path_pnl > A->max_path_pnl) A->max_path_pnl = path_pnl;
@@ -365,6 +388,9 @@ static void run_range(job_t* J) {
 }
 
 static void* thread_main(void* arg) { run_range((job_t*)arg); return NULL; }
+
+/* QMMX_F_ONLINE_RETRAIN: where the next oq_run_paths* call leaves the learnt go_long / go_short heads, [path][14] (NULL = nowhere) */
+void oq_set_policy_weights_out(double* out) { g_polw_out = out; }
 
 /* Batch run over `[step][path]` fp32 bars; n_threads pthreads each take a contiguous path range. */
 int oq_run_paths_v(const float* close, const float* high, const float* low, const float* volume, int64_t paths, int32_t steps,

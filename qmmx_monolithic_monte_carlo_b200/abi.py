@@ -33,6 +33,7 @@ F_USE_BLEND = 1 << 2
 F_DISABLE_POLICY_GATE = 1 << 3
 F_EXIT_ON_HL = 1 << 4
 F_TINY_PRICES = 1 << 5
+F_ONLINE_RETRAIN = 1 << 6
 
 GBM_ROUND_CENTS = 1 << 0
 
@@ -85,11 +86,12 @@ def make_params(*, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25, q_min_
                 cooldown_s=8, enable_veto=False, veto_vol_strong=0.25, veto_prox=0.06,
                 disable_ml_gate=False, use_blend=False, w_rules=0.7, w_ml=0.3,
                 disable_policy_gate=True, exit_on_hl=False, overtouch_limit=4,
-                steps_per_day=390, tiny_prices=False) -> Params:
+                steps_per_day=390, tiny_prices=False, online_retrain=False) -> Params:
     """Engine settings with the reference's defaults (qmmx_monolithic.py:1371-1386, 1711-1715)."""
     flags = ((F_ENABLE_VETO if enable_veto else 0) | (F_DISABLE_ML_GATE if disable_ml_gate else 0)
              | (F_USE_BLEND if use_blend else 0) | (F_DISABLE_POLICY_GATE if disable_policy_gate else 0)
-             | (F_EXIT_ON_HL if exit_on_hl else 0) | (F_TINY_PRICES if tiny_prices else 0))
+             | (F_EXIT_ON_HL if exit_on_hl else 0) | (F_TINY_PRICES if tiny_prices else 0)
+             | (F_ONLINE_RETRAIN if online_retrain else 0))
     return Params(C.sizeof(Params), flags, float(contact_prox), float(stop_padding), float(tp_padding),
                   float(q_min_prob), float(w_rules), float(w_ml), float(veto_vol_strong), float(veto_prox),
                   int(cooldown_s), int(overtouch_limit), int(steps_per_day), 0)

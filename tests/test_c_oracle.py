@@ -7,6 +7,7 @@ import pytest
 from oracle import c_oracle as CO
 from oracle import headless as H
 from qmmx_monolithic_monte_carlo_b200 import abi
+from qmmx_monolithic_monte_carlo_b200 import engine as E
 from qmmx_monolithic_monte_carlo_b200 import fixtures as F
 from tests.golden_util import load_engine_cases, oracle_inputs
 
@@ -208,3 +209,23 @@ def test_c_oracle_regime_guard_matches_headless():
         o = H.run_path(closes[:, j], lv, H.Params(**kw), volume=[float(x) for x in vol[:, j]])
         assert o.codes == r["codes"][:, j].tolist(), j
     assert r["agg"].entry_hist[abi.ENTRY_CODES.index("ACC_BREAKOUT_GATE")] >= 5
+
+
+def test_c_oracle_online_policy_retrain_matches_headless():
+    """the C restatement of the OnlinePolicy learning path against oracle/headless.py (itself pinned against
+    the reference in test_oracle_vs_reference.py): per-tick codes and every learnt float64 weight identical."""
+    closes = F.host_gbm_closes(6, 3 * 390, seed=404)
+    pol = [{"go_long": [0.55, -0.3, 0.0, 0.0, 0.0, 0.05, -0.1], "go_short": [0.5, -0.2, 0.0, 0.0, 0.0, 0.05, 0.05],
+            "skip": [-0.6, 0.2, 0.0, 0.0, 0.1, -0.1, 0.1]}]
+    pa = np.array([[pol[0]["go_long"], pol[0]["go_short"], pol[0]["skip"]]])
+    rows, price, solid = E.sort_levels(F.levels_30())
+    kw = dict(contact_prox=0.1, cooldown_s=60, disable_policy_gate=False, online_retrain=True)
+    o = CO.run_paths(closes, price, solid, abi.make_params(**kw), policy=pa, want_codes=True, max_trades=64)
+    lv = H.sort_levels(F.levels_30())
+    n_pol = 0
+    for j in range(closes.shape[1]):
+        h = H.run_path(closes[:, j], lv, H.Params(**kw), policy=pol)
+        assert list(o["codes"][:, j]) == h.codes
+        assert (h.policy_weights["go_long"] + h.policy_weights["go_short"]) == list(o["policy_weights"][j])
+        n_pol += h.codes.count(H.ENTRY_CODES.index("ONLINE_POLICY"))
+    assert n_pol > 0
