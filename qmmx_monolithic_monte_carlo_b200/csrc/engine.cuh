@@ -36,6 +36,7 @@ struct ScanArgs {
     const float* close; const float* high; const float* low;   // [steps][pitch] fp32
     const uint8_t* regime;        // AccumulationBreakoutGuard regime per tick [steps][pitch] (regime_kernel), or null
     const float* vol;             // per-bar volume [steps][pitch], or null: the soft veto is inert (M:1796-1811)
+    double* polw;                 // QMMX_F_ONLINE_RETRAIN: learnt go_long / go_short heads [14][pitch], or null
     int64_t pitch, paths;
     int32_t steps, combo_index;
     const DevTables* tables;                                    // the table of this combo
@@ -216,7 +217,7 @@ __device__ __noinline__ int veto_check(const ScanArgs* A, int k, float pf, int s
 }
 
 // rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
-__device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i) {
+__device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i, int64_t path) {
     if (A->n_pol <= 0) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return false; }   // zero weights: sigmoid(0) = 0.5 < 0.60
     const int spd = A->combo.spd;
     const double lp = g_S.cold[k].price;
@@ -227,11 +228,52 @@ __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, i
     const double x5 = (g_S.cold[k].flags & kLvConfl06) ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
     const int day = i / spd;
     const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < A->n_pol ? day : A->n_pol - 1);
-    const double z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
+    double z_side;
+    if (A->polw) {                      // the head of this side as this path has learnt it so far
+        double wl[QMMX_POLICY_DIM];
+#pragma unroll
+        for (int q = 0; q < QMMX_POLICY_DIM; ++q) wl[q] = A->polw[(size_t)(side * QMMX_POLICY_DIM + q) * (size_t)A->pitch + (size_t)path];
+        z_side = dot_py312(wl, x1, x3, x4, x5, x6);
+    } else z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
     const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x1, x3, x4, x5, x6);
     const bool pass = (z_side >= A->z_go) && (z_sk < A->z_skip);
     if (!pass) smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]);
     return pass;
+}
+
+// M:20-26
+__device__ __forceinline__ double sigmoid_policy(double x) {
+    if (x < -50.0) return 0.0;
+    if (x > 50.0) return 1.0;
+    return 1.0 / (1.0 + exp(-x));
+}
+
+// QMMX_F_ONLINE_RETRAIN, at the close of a trade: the trade's two labelled policy_events rows train the head of its
+// action (update_entry M:357-363 / _sgd_update M:337-341, lr 0.03, l2 1e-6 of M:290), in row order: the PRE_OPEN row
+// of evaluate_entry (M:1757-1768 -> features [1, min(1, |p - L|), 0, from_above, from_below, 0, 0]), then the live
+// loop's {"x": x} row (M:3139-3150), whose keys _retrain_from_labeled_events cannot read: [1, 0, 0, 1, 0, 0, 0].
+// Restated from oracle/headless.py run_path; exp() is CUDA's (<= 1 ulp from libm's), so the learnt weights are
+// compared with a tolerance and the decisions they drive exactly.
+__device__ __noinline__ void policy_learn(const ScanArgs* A, int64_t path, int side, double dist, bool win) {
+    double w[QMMX_POLICY_DIM];
+    double* g = A->polw + (size_t)(side * QMMX_POLICY_DIM) * (size_t)A->pitch + (size_t)path;
+#pragma unroll
+    for (int q = 0; q < QMMX_POLICY_DIM; ++q) w[q] = g[(size_t)q * (size_t)A->pitch];
+    const double y = win ? 1.0 : 0.0;
+#pragma unroll 1
+    for (int row = 0; row < 2; ++row) {
+        const double x1 = row == 0 ? (dist < 1.0 ? dist : 1.0) : 0.0;
+        const double x3 = row == 0 ? (side == 1 ? 1.0 : 0.0) : 1.0, x4 = row == 0 ? (side == 0 ? 1.0 : 0.0) : 0.0;
+        const double pred = sigmoid_policy(dot_py312(w, x1, x3, x4, 0.0, 0.0));
+#pragma unroll
+        for (int q = 0; q < QMMX_POLICY_DIM; ++q) {
+            const double xq = q == 0 ? 1.0 : q == 1 ? x1 : q == 3 ? x3 : q == 4 ? x4 : 0.0;
+            const double grad = (pred - y) * xq + 1e-6 * w[q];
+            w[q] -= 0.03 * grad;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < QMMX_POLICY_DIM; ++q) g[(size_t)q * (size_t)A->pitch] = w[q];
 }
 
 // parity mode: one trade record
@@ -318,7 +360,7 @@ struct PathEngine {
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
         if (!(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {
-            if (!policy_passes(&A, k, pf, side, i)) return QMMX_ONLINE_POLICY;
+            if (!policy_passes(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
         }
         // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
         // thresholds (M:1669-1674) were rounded per level at CTA setup:

@@ -498,6 +498,12 @@ __global__ void init_flat_kernel(unsigned long long* flat, int n_combos) {
     }
 }
 
+// QMMX_F_ONLINE_RETRAIN: every path starts from the go_long / go_short heads of the one policy table ([3][7] float64)
+__global__ void polw_init_kernel(double* __restrict__ polw, const double* __restrict__ pol, int64_t pitch) {
+    const int64_t n = 14 * pitch, stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += stride) polw[t] = pol[t / pitch];
+}
+
 // ---- FP32 issue-rate probe ("measure an FMA-only microbenchmark on the box and use that") ------------
 // 16 independent FFMA chains per thread; 2 flop per FFMA. The result is stored so that nothing is eliminated.
 __global__ void __launch_bounds__(1024, 1) fp32_probe_kernel(float* out, int iters, float a, float b) {

@@ -54,6 +54,7 @@ struct qmmx_ctx {
     // staging for qmmx_run_scan_host
     float* d_stage[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
     int64_t stage_elems = 0;
+    double* d_polw = nullptr; int64_t polw_pitch = 0, polw_paths = 0;   // QMMX_F_ONLINE_RETRAIN: learnt heads [14][pitch]
     float* d_ratios = nullptr; size_t ratios_cap = 0;     // bootstrap return ratios (qmmx_gen_bootstrap)
     bool ran = false;
 };
@@ -359,6 +360,23 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         fill_args(ctx, A, c, cl, h, l, pitch, paths, steps);
         const bool parity = par && c == 0;
         if (parity) { A.trades = par->trades; A.tcounts = par->tcounts; A.codes = par->codes; A.max_trades = par->max_trades; }
+        if ((A.combo.flags & QMMX_F_ONLINE_RETRAIN) && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {
+            // the learnt heads are per path and per combo: one combo, the ctx's resident bars, the lean kernels
+            const bool band = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
+            if (nc != 1 || !cl || cl != ctx->d_close || !lean || !band || ctx->n_pol != 1)
+                return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN needs one combo, one policy table, resident bars and the lean scan kernel");
+            if (!ctx->d_polw || ctx->polw_pitch != pitch) {
+                if (ctx->d_polw) cudaFree(ctx->d_polw);
+                ctx->d_polw = nullptr;
+                CK(cudaMalloc(&ctx->d_polw, (size_t)14 * (size_t)pitch * sizeof(double)));
+                ctx->polw_pitch = pitch;
+            }
+            ctx->polw_paths = paths;
+            polw_init_kernel<<<(unsigned)std::min<int64_t>((14 * pitch + 255) / 256, 65535), 256, 0, ctx->stream>>>(ctx->d_polw, ctx->d_pol, pitch);
+            ctx->launches++;
+            CK(cudaGetLastError());
+            A.polw = ctx->d_polw;
+        }
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE) || A.vol != nullptr || A.regime != nullptr;
         // the lean exit block assumes a single price cannot hit both thresholds: stop below / target above the level
         const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
@@ -480,7 +498,7 @@ int qmmx_destroy(qmmx_ctx* ctx) {
     free_bars(ctx);
     for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
     cudaFree(ctx->d_tables); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
-    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios);
+    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios); cudaFree(ctx->d_polw);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
     cudaStreamDestroy(ctx->own_stream); cudaStreamDestroy(ctx->copy_stream);
@@ -780,6 +798,13 @@ int qmmx_run_scan(qmmx_ctx* c, qmmx_agg* agg_out, qmmx_trade* trades_out, int32_
     return qmmx_fetch_agg(ctx, agg_out);
 }
 
+// QMMX_F_ONLINE_RETRAIN keeps per-path weights beside resident bars: the fused (register-only) paths do not carry them
+static bool any_retrain(const qmmx_ctx* ctx) {
+    for (const DevCombo& D : ctx->h_combos)
+        if ((D.flags & QMMX_F_ONLINE_RETRAIN) && !(D.flags & QMMX_F_DISABLE_POLICY_GATE)) return true;
+    return false;
+}
+
 int qmmx_run_scan_host(qmmx_ctx* c, const float* close, const float* high, const float* low, int64_t paths,
                        int32_t steps, int64_t chunk_paths, qmmx_agg* agg_out) {
     ENTER(c);
@@ -826,6 +851,7 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     if (paths < 0 || steps < 0) return fail(ctx, QMMX_E_BADARG, "negative size");
     if ((rc = prepare(ctx)) != 0) return rc;
     if (ctx->any_tiny) return fail(ctx, QMMX_E_UNSUPPORTED, "TINY_PRICES is not available in the fused GBM kernel");
+    if (any_retrain(ctx)) return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN runs over resident bars (qmmx_run_scan)");
     if (ctx->any_hl && gbm->sub_steps != 4) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs sub_steps = 4 (OHLC bars)");
     const GbmDev g = make_gbm(gbm, seed, path_offset);
     const size_t smem = scan_smem_bytes(ctx);
@@ -884,6 +910,7 @@ int qmmx_run_fused_bootstrap_async(qmmx_ctx* c, uint64_t seed, uint64_t path_off
     int rc = prepare(ctx);
     if (rc != 0) return rc;
     if (ctx->any_tiny || !ctx->lean_ok) return fail(ctx, QMMX_E_UNSUPPORTED, "fused bootstrap needs the lean engine (no TINY_PRICES, positive level prices)");
+    if (any_retrain(ctx)) return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN runs over resident bars (qmmx_run_scan)");
     if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
     std::vector<float> ratios(3 * (size_t)nret);
     for (int t = 1; t < window_len; ++t) {
@@ -1149,6 +1176,18 @@ int qmmx_last_timing(qmmx_ctx* c, float* ms) {
     if (!ctx->ran || !ms) return fail(ctx, QMMX_E_STATE, "nothing has run");
     CK(cudaEventSynchronize(ctx->ev1));
     CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return QMMX_OK;
+}
+
+int qmmx_download_policy_weights(qmmx_ctx* c, double* out, int64_t paths) {
+    ENTER(c);
+    if (!out || paths < 0) return fail(ctx, QMMX_E_BADARG, "download_policy_weights: bad arguments");
+    if (!ctx->d_polw || paths != ctx->polw_paths) return fail(ctx, QMMX_E_STATE, "no ONLINE_RETRAIN scan of that many paths has run");
+    std::vector<double> tmp((size_t)14 * (size_t)ctx->polw_pitch);
+    CK(cudaMemcpyAsync(tmp.data(), ctx->d_polw, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int64_t p = 0; p < paths; ++p)
+        for (int q = 0; q < 14; ++q) out[p * 14 + q] = tmp[(size_t)q * (size_t)ctx->polw_pitch + (size_t)p];
     return QMMX_OK;
 }
 

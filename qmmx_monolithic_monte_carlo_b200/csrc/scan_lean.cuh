@@ -189,6 +189,10 @@ struct LeanEngine {
             win = tp > 0;
             c_exit += is_stop ? 1u : (1u << 16);
         }
+        if (SLOW && A.polw) {                                     // QMMX_F_ONLINE_RETRAIN: learn from this trade (engine.cuh policy_learn)
+            const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
+            policy_learn(&A, path, is_short ? 1 : 0, fabs(lp - (double)entry_price()), win);
+        }
         pnl += tp; pnl2 += tp * tp;
         a_inpos += i;                                             // IN_POSITION steps of this trade: i - entry bar
         cool = i + cs_(A);                                        // M:2982, M:269-270; COOLDOWN steps are counted in finish
@@ -238,7 +242,7 @@ struct LeanEngine {
             if ((m >> (side * 16 + (int)tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         if (SLOW && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {   // OnlinePolicy gate of the live loop (M:3046-3109)
-            if (!policy_passes(&A, k, pf, side, i)) return QMMX_ONLINE_POLICY;
+            if (!policy_passes(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
         }
         if (SWEEP) {                                              // M:1669-1674 with this lane's paddings (as lean_setup rounds them)
             const double lp = lds_f64<Y::kPrice>(sb + k * 8);

@@ -81,6 +81,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
         "qmmx_measure_fp32_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
+        "qmmx_download_policy_weights": (C.c_int, [vp, vp, i64]),
     }
     for name, (res, args) in protos.items():
         fn = getattr(L, name)          # AttributeError here = header/library mismatch
@@ -413,6 +414,12 @@ class MCEngine:
         ms = C.c_float()
         self._ck(self._L.qmmx_last_timing(self._h, C.byref(ms)))
         return float(ms.value)
+
+    def download_policy_weights(self, paths: int) -> np.ndarray:
+        """ONLINE_RETRAIN: the go_long[7] + go_short[7] heads each path has learnt in the last run_scan, `[paths][14]` f64."""
+        out = np.empty((paths, 14), dtype=np.float64)
+        self._ck(self._L.qmmx_download_policy_weights(self._h, _ptr(out), paths))
+        return out
 
     def measure_fp32_peak(self) -> float:
         """FFMA-only TFLOP/s of this device, measured now (the FP32 roofline denominator of SURVEY 8(d))."""

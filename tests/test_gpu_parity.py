@@ -688,3 +688,46 @@ def test_gpu_sweep_kernel_full_c4_size(eng, monkeypatch):
             assert a.n_trades == a.exit_hist["STOP"] + a.exit_hist["TARGET"] and a.entry_hist["OK"] == a.n_trades + a.n_open
     finally:
         plain.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
+def test_gpu_online_policy_retrain(eng, hl):
+    """SURVEY 8f-4 on the device: every path's OnlinePolicy go heads learn from its own closed trades (policy_learn,
+    two SGD steps per trade as the reference's two labelled rows give).  Per-tick codes, trade records and all integer
+    aggregates equal the C oracle's; the learnt float64 weights agree to 1e-12 relative (CUDA exp vs libm exp differ by
+    at most one ulp per update).  The learning must matter: ONLINE_POLICY skips appear and a frozen policy decides
+    differently."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    pol = np.array([[[0.55, -0.3, 0.0, 0.0, 0.0, 0.05, -0.1], [0.5, -0.2, 0.0, 0.0, 0.0, 0.05, 0.05],
+                     [-0.6, 0.2, 0.0, 0.0, 0.1, -0.1, 0.1]]])
+    kw = dict(contact_prox=0.1, cooldown_s=60, disable_policy_gate=False, exit_on_hl=hl)
+    P, T = 2053, 3 * 390
+    g = abi.make_gbm(sub_steps=4 if hl else 1)
+    params = abi.make_params(online_retrain=True, **kw)
+    configure(eng, price, solid, params, pol=pol)
+    eng.gen_gbm(77, 0, P, T, g)
+    c, h, l = eng.download_bars(P, T, hl=hl)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=(T, P))
+    w = eng.download_policy_weights(P)
+    o = CO.run_paths(c, price, solid, params, policy=pol, high=h, low=l, want_codes=True, max_trades=64, n_threads=8)
+    assert np.array_equal(codes, o["codes"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert np.allclose(w, o["policy_weights"], rtol=1e-12, atol=0)
+    assert res[0].entry_hist["ONLINE_POLICY"] > 0 and np.abs(w - pol[0, :2].reshape(1, 14)).max() > 0.1
+    # aggregate-only run (no parity outputs) gives the same aggregates and weights
+    agg2 = eng.run_scan()[0].agg
+    assert list(agg2.entry_hist) == list(o["agg"].entry_hist) and list(agg2.exit_hist) == list(o["agg"].exit_hist)
+    assert agg2.n_wins == o["agg"].n_wins and list(agg2.pnl_hist) == list(o["agg"].pnl_hist)
+    assert np.array_equal(eng.download_policy_weights(P), w)
+    frozen = abi.make_params(online_retrain=False, **kw)
+    configure(eng, price, solid, frozen, pol=pol)
+    assert eng.run_scan()[0].n_trades != res[0].n_trades
+    # what the flag cannot do fails loudly
+    configure(eng, price, solid, [params, params], pol=pol)
+    with pytest.raises(E.QmmxError):
+        eng.run_scan()
+    configure(eng, price, solid, params, pol=pol)
+    with pytest.raises(E.QmmxError):
+        eng.run_fused_gbm(1, 0, 100, 390, g)
