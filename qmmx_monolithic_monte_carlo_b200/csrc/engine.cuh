@@ -216,7 +216,9 @@ __device__ __noinline__ int veto_check(const ScanArgs* A, int k, float pf, int s
     return 0;
 }
 
-// rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed
+// rare: OnlinePolicy gate of the live loop (M:3046-3109); true = entry allowed.  LEARNT: the head of the entry's side is
+// the one this path has learnt so far (QMMX_F_ONLINE_RETRAIN, A->polw) instead of the table's.
+template <bool LEARNT>
 __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, int side, int i, int64_t path) {
     if (A->n_pol <= 0) { smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]); return false; }   // zero weights: sigmoid(0) = 0.5 < 0.60
     const int spd = A->combo.spd;
@@ -229,7 +231,7 @@ __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, i
     const int day = i / spd;
     const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < A->n_pol ? day : A->n_pol - 1);
     double z_side;
-    if (A->polw) {                      // the head of this side as this path has learnt it so far
+    if (LEARNT) {
         double wl[QMMX_POLICY_DIM];
 #pragma unroll
         for (int q = 0; q < QMMX_POLICY_DIM; ++q) wl[q] = A->polw[(size_t)(side * QMMX_POLICY_DIM + q) * (size_t)A->pitch + (size_t)path];
@@ -360,7 +362,7 @@ struct PathEngine {
         }
         // evaluate_entry returned OK; OnlinePolicy gate of the live loop (M:3046-3109)
         if (!(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {
-            if (!policy_passes(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
+            if (!policy_passes<false>(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
         }
         // open_trade (M:3112-3115, M:1888-1897): entry at the tick price; first exit test on the next tick.
         // thresholds (M:1669-1674) were rounded per level at CTA setup:

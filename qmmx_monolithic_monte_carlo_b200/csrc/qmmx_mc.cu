@@ -294,8 +294,18 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         if ((rc = set_smem_attr(ctx, k, lean_smem)) != 0) return rc;                          \
         k<<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A);                            \
     } while (0)
+#define LEAN3L(MDv, HLv, PARv, Wv)                                                            \
+    do {                                                                                      \
+        auto k = lean_scan_kernel<MDv, HLv, PARv, Wv, true, true>;                            \
+        if ((rc = set_smem_attr(ctx, k, lean_smem)) != 0) return rc;                          \
+        k<<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A);                            \
+    } while (0)
 #define LEAN2(MDv, HLv, PARv, Wv)                                                             \
-    do { if (PARv || slow) LEAN3(MDv, HLv, PARv, Wv, true); else LEAN3(MDv, HLv, false, Wv, false); } while (0)
+    do {                                                                                      \
+        if (A.polw) LEAN3L(MDv, HLv, PARv, Wv);                                               \
+        else if (PARv || slow) LEAN3(MDv, HLv, PARv, Wv, true);                               \
+        else LEAN3(MDv, HLv, false, Wv, false);                                               \
+    } while (0)
 #define LEAN(HLv, PARv)                                                                       \
     do {                                                                                      \
         if (multiday) { if (wide) LEAN2(true, HLv, PARv, true); else LEAN2(true, HLv, PARv, false); } \
@@ -402,6 +412,7 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
 #undef LEAN
 #undef LEAN2
 #undef LEAN3
+#undef LEAN3L
     return QMMX_OK;
 }
 

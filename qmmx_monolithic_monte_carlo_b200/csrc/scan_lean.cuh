@@ -123,7 +123,9 @@ __device__ inline void lean_setup(const ScanArgs& A) {
 // SLOW = the blend gate, the OnlinePolicy gate or the volume veto is enabled (float64 slow paths compiled in)
 // SWEEP = the lanes of a warp are parameter combos of ONE path (lean_sweep_kernel): stop/target paddings, cooldown and
 // the logistic mask are per-lane members instead of launch constants.
-template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, bool SWEEP = false>
+// LEARN = QMMX_F_ONLINE_RETRAIN: an exit also trains this path's OnlinePolicy head (its own kernels: the call costs the
+// other SLOW kernels 13-18 % in spills when it is merely compiled in)
+template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, bool SWEEP = false, bool LEARN = false>
 struct LeanEngine {
     typedef typename LatchType<WIDE>::T latch_t;
     static constexpr int LPAD = WIDE ? 64 : 32;
@@ -189,7 +191,7 @@ struct LeanEngine {
             win = tp > 0;
             c_exit += is_stop ? 1u : (1u << 16);
         }
-        if (SLOW && A.polw) {                                     // QMMX_F_ONLINE_RETRAIN: learn from this trade (engine.cuh policy_learn)
+        if (LEARN && A.polw) {                                     // QMMX_F_ONLINE_RETRAIN: learn from this trade (engine.cuh policy_learn)
             const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
             policy_learn(&A, path, is_short ? 1 : 0, fabs(lp - (double)entry_price()), win);
         }
@@ -242,7 +244,7 @@ struct LeanEngine {
             if ((m >> (side * 16 + (int)tc)) & 1u) { c_ml += 1u; return QMMX_ML_CONF_LOW; }
         }
         if (SLOW && !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE)) {   // OnlinePolicy gate of the live loop (M:3046-3109)
-            if (!policy_passes(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
+            if (!policy_passes<LEARN>(&A, k, pf, side, i, path)) return QMMX_ONLINE_POLICY;
         }
         if (SWEEP) {                                              // M:1669-1674 with this lane's paddings (as lean_setup rounds them)
             const double lp = lds_f64<Y::kPrice>(sb + k * 8);
@@ -337,8 +339,8 @@ struct LeanEngine {
 // Bars are [step][pitch]: one coalesced 128-byte line per warp, step and field; 2U rows are kept in flight per
 // thread in registers (register double buffer) -- at 1024 threads per SM a warp returns to the loop every ~0.3 us,
 // HBM latency is ~0.8 us.
-template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, int U>
-__device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW>& E, const ScanArgs& A,
+template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, int U, bool LEARN = false>
+__device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW, false, LEARN>& E, const ScanArgs& A,
                                                int64_t path) {
     const size_t pitch = (size_t)A.pitch;
     const float* pc = A.close + path;
@@ -391,12 +393,12 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
     }
 }
 
-template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW>
+template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kernel(const __grid_constant__ ScanArgs A) {
     block_setup(A);
     lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
-    LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW> E;
+    LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW, false, LEARN> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // through a shuffle so that ptxas keeps the base in a register instead of rebuilding it from SR_CgaCtaId at every use
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
@@ -405,7 +407,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(sb, path);
-        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, 2>(E, A, path); E.finish(A); }
+        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, 2, LEARN>(E, A, path); E.finish(A); }
         __syncwarp();
         warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.is_open());
     }
