@@ -478,7 +478,11 @@ def main():
                          "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch "
                                            "(profiles/r1_ncu_lean_scan_close_summary.txt)",
                          "kernel": "lean_scan_kernel<MULTIDAY=0,HL=0,PARITY=0,WIDE=0,SLOW=0>", "kernel_ms": k_ms,
-                         "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
+                         "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                         "binding_limit": {"what": "instruction issue, not HBM", "issue_active_pct": 85.4,
+                                           "warp_instructions_per_warp_step": 91.5, "active_lanes_per_instruction": 15.4,
+                                           "source": "ncu --set full of this kernel on this command, "
+                                                     "profiles/r1_ncu_lean_scan_close_summary.txt (static, not re-measured per run)"}},
             "roofline_fp32": fp32_roofline(eng, paths * STEPS_PER_PATH / (k_ms * 1e-3), 12),
             "clocks": clocks, "gpu_launches": int(launches),
             "result_check": {"n_trades": res.n_trades, "n_wins": res.n_wins, "sum_pnl": res.sum_pnl},
