@@ -16,6 +16,10 @@
 //    shared-memory float2 per (level, side, touch count): pass <=> x <= p <= |y|; the sign of y and the
 //    in-range bit select the reason code (tables built per CTA from the exact host intervals).
 //  * touch counters are one byte per (level, thread) in shared memory, rows rotated over the banks.
+//
+// Kernels: lean_scan_kernel (resident bars; LEARN variants train the per-path OnlinePolicy heads), lean_fused_gbm_kernel
+// and lean_fused_boot_kernel (bars generated and consumed in registers), lean_sweep_kernel (a parameter sweep: the
+// 32 lanes of a warp are 32 combos of ONE path, steps are classified 32 at a time and far steps are skipped).
 #pragma once
 #include "kernels.cuh"
 
