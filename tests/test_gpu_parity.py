@@ -731,3 +731,65 @@ def test_gpu_online_policy_retrain(eng, hl):
     configure(eng, price, solid, params, pol=pol)
     with pytest.raises(E.QmmxError):
         eng.run_fused_gbm(1, 0, 100, 390, g)
+
+
+def _levels_48(seed=9):
+    """48 levels (the 64-level kernel variants: 64-bit latch, 104 KB of tables), clustered so that windows overlap."""
+    rng = np.random.default_rng(seed)
+    price = np.round(np.concatenate([rng.uniform(641.0, 657.0, 40), 648.9 + rng.normal(0, 0.08, 8)]), 2)
+    return [dict(color=("blue", "orange", "black", "teal")[i % 4], type="solid" if i % 3 else "dashed", index=i // 4,
+                 price=float(p)) for i, p in enumerate(price)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
+def test_gpu_wide_level_sets(eng, hl, monkeypatch):
+    """More than 32 levels selects the WIDE kernel variants everywhere: scan (parity outputs), fused GBM, sweep,
+    online retrain -- each against the C oracle or against its generate-then-scan twin."""
+    rows, price, solid = E.sort_levels(_levels_48())
+    assert len(price) == 48
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    g = abi.make_gbm(sub_steps=4 if hl else 1)
+    P, T = 4099, 390
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=hl)
+    configure(eng, price, solid, params, lr)
+    eng.gen_gbm(31, 5, P, T, g)
+    c, h, l = eng.download_bars(P, T, hl=hl)
+    res, tr, cnt, codes = eng.run_scan(trades=48, codes=True, paths_steps=(T, P))
+    o = CO.run_paths(c, price, solid, params, lr=lr, high=h, low=l, want_codes=True, max_trades=48, n_threads=8)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    assert_agg_equal(eng.run_fused_gbm(31, 5, P, T, g)[0].agg, eng.run_scan()[0].agg, sums_rel=1e-12)
+    # sweep (lanes = combos) on 64-level tables
+    grid = [abi.make_params(contact_prox=0.1, stop_padding=0.1 + 0.05 * i, tp_padding=tp, cooldown_s=cd, exit_on_hl=hl)
+            for i in range(6) for tp in (0.15, 0.4) for cd in (0, 300)]
+    monkeypatch.setenv("QMMX_NO_SWEEP", "1")
+    plain = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_NO_SWEEP")
+    try:
+        out = []
+        for e in (eng, plain):
+            configure(e, price, solid, grid, lr)
+            e.gen_gbm(31, 5, P, T, g)
+            out.append(e.run_scan())
+        for a, b in zip(*out):
+            assert_agg_equal(a.agg, b.agg, sums_rel=1e-12)
+        assert_agg_equal(out[0][7].agg, CO.run_paths(c, price, solid, grid[7], lr=lr, high=h, low=l, n_threads=8)["agg"])
+    finally:
+        plain.close()
+    # online retrain on 64-level tables, three days with per-day LR tables (MULTIDAY + LEARN variant)
+    pol = np.array([[[0.55, -0.3, 0.0, 0.0, 0.0, 0.05, -0.1], [0.5, -0.2, 0.0, 0.0, 0.0, 0.05, 0.05],
+                     [-0.6, 0.2, 0.0, 0.0, 0.1, -0.1, 0.1]]])
+    lr3 = np.array([[0.2, -0.5, -0.45, 0.35, 1.0], [0.1, -0.4, -0.3, 0.2, 0.9], [0.3, -0.6, -0.5, 0.4, 1.1]])
+    pr = abi.make_params(contact_prox=0.1, cooldown_s=60, disable_policy_gate=False, online_retrain=True, exit_on_hl=hl)
+    configure(eng, price, solid, pr, lr3, pol)
+    P2, T2 = 1031, 3 * 390
+    eng.gen_gbm(32, 0, P2, T2, g)
+    c, h, l = eng.download_bars(P2, T2, hl=hl)
+    res, tr, cnt, codes = eng.run_scan(trades=64, codes=True, paths_steps=(T2, P2))
+    o = CO.run_paths(c, price, solid, pr, lr=lr3, policy=pol, high=h, low=l, want_codes=True, max_trades=64, n_threads=8)
+    assert np.array_equal(codes, o["codes"])
+    assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+    assert_agg_equal(res[0].agg, o["agg"])
+    assert np.allclose(eng.download_policy_weights(P2), o["policy_weights"], rtol=1e-12, atol=0)
