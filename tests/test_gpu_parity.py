@@ -793,3 +793,38 @@ def test_gpu_wide_level_sets(eng, hl, monkeypatch):
     assert_trades_equal(tr, cnt, o["trades"], o["counts"])
     assert_agg_equal(res[0].agg, o["agg"])
     assert np.allclose(eng.download_policy_weights(P2), o["policy_weights"], rtol=1e-12, atol=0)
+
+
+@pytest.mark.gpu
+def test_gpu_wide_level_sets_float64_gates_and_bootstrap(eng):
+    """The remaining 64-level variants: OnlinePolicy gate (frozen weights), blend gate, soft veto + regime gate on a volume
+    plane (the float64 SLOW kernels), and the fused block bootstrap, all against the oracle / the generate-then-scan twin."""
+    rows, price, solid = E.sort_levels(_levels_48())
+    rng = np.random.default_rng(12)
+    lr, pol = _lr_tables(rng, 2)
+    P, T = 2051, 2 * 390
+    for kw in (dict(disable_policy_gate=False), dict(use_blend=True), dict(enable_veto=True, veto_prox=0.08, exit_on_hl=True)):
+        hl = bool(kw.get("exit_on_hl"))
+        params = abi.make_params(contact_prox=0.1, cooldown_s=60, **kw)
+        configure(eng, price, solid, params, lr, pol)
+        eng.gen_gbm(41, 0, P, T, abi.make_gbm(sub_steps=4 if hl else 1))
+        c, h, l = eng.download_bars(P, T, hl=hl)
+        vol = None
+        if kw.get("enable_veto"):
+            vol = (1e5 * np.exp(0.5 * np.cumsum(rng.normal(0, 0.35, size=c.shape), axis=0))).astype(np.float32)
+            eng.upload_volume(vol)
+        res, tr, cnt, codes = eng.run_scan(trades=48, codes=True, paths_steps=(T, P))
+        o = CO.run_paths(c, price, solid, params, lr=lr, policy=pol, high=h, low=l, volume=vol, want_codes=True,
+                         max_trades=48, n_threads=8)
+        assert np.array_equal(codes, o["codes"]), kw
+        assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+        assert_agg_equal(res[0].agg, o["agg"])
+    g = abi.make_gbm(sub_steps=4)
+    wc, wh, wl = CO.gen_gbm(5, 0, 1, 40, g, ohlc=True)
+    wo = np.concatenate([[g.s0], wc[:-1, 0]]).astype(np.float32)
+    window = np.stack([wo, wh[:, 0], wl[:, 0], wc[:, 0]], axis=1)
+    configure(eng, price, solid, abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=True), lr)
+    fused = eng.run_fused_bootstrap(9, 7, 20_011, T, window, 5)[0].agg
+    eng.gen_bootstrap(9, 7, 20_011, T, window, 5)
+    assert_agg_equal(fused, eng.run_scan()[0].agg, sums_rel=1e-12)
+    assert fused.n_trades > 0
