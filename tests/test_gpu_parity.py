@@ -828,3 +828,29 @@ def test_gpu_wide_level_sets_float64_gates_and_bootstrap(eng):
     eng.gen_bootstrap(9, 7, 20_011, T, window, 5)
     assert_agg_equal(fused, eng.run_scan()[0].agg, sums_rel=1e-12)
     assert fused.n_trades > 0
+
+
+@pytest.mark.gpu
+def test_gpu_wide_level_sets_first_generation_kernels(monkeypatch):
+    """The first-generation kernels (the TINY_PRICES path, QMMX_SCAN_V1=1) on 48 levels, scan and fused, against the oracle."""
+    rows, price, solid = E.sort_levels(_levels_48())
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    monkeypatch.setenv("QMMX_SCAN_V1", "1")
+    v1 = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_SCAN_V1")
+    try:
+        for hl in (False, True):
+            g = abi.make_gbm(sub_steps=4 if hl else 1)
+            params = abi.make_params(contact_prox=0.1, cooldown_s=120, exit_on_hl=hl)
+            configure(v1, price, solid, params, lr)
+            P, T = 3001, 390
+            v1.gen_gbm(51, 0, P, T, g)
+            c, h, l = v1.download_bars(P, T, hl=hl)
+            res, tr, cnt, codes = v1.run_scan(trades=48, codes=True, paths_steps=(T, P))
+            o = CO.run_paths(c, price, solid, params, lr=lr, high=h, low=l, want_codes=True, max_trades=48, n_threads=8)
+            assert np.array_equal(codes, o["codes"])
+            assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+            assert_agg_equal(res[0].agg, o["agg"])
+            assert_agg_equal(v1.run_fused_gbm(51, 0, P, T, g)[0].agg, o["agg"], sums_rel=1e-9)
+    finally:
+        v1.close()
