@@ -638,6 +638,9 @@ def test_gpu_sweep_kernel_equals_per_combo_kernels(eng, hl, monkeypatch):
         for a, b in zip(*out):
             assert_agg_equal(a.agg, b.agg)
         c, h, l = eng.download_bars(P, T, hl=hl)
+        # the host pipeline (chunked H2D + scan per chunk) sweeps each chunk and adds up to the same aggregates
+        for a, b in zip(eng.run_scan_host(c, h if hl else None, l if hl else None, chunk_paths=1024), out[0]):
+            assert_agg_equal(a.agg, b.agg, sums_rel=1e-12)
         for ci in (0, 31, 32, 76, 77, 100):
             o = CO.run_paths(c, price, solid, grid[ci], lr=lr, high=h if hl else None, low=l if hl else None, n_threads=4)
             assert_agg_equal(out[0][ci].agg, o["agg"])
