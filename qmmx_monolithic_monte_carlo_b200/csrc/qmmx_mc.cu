@@ -149,7 +149,9 @@ int prepare(qmmx_ctx* ctx) {
         double wr = P.w_rules, wm = P.w_ml, s = wr + wm;                // M:1714-1719
         if (s <= 0) { wr = 1.0; wm = 0.0; s = 1.0; }
         D.wr = wr / s; D.wm = wm / s;
-        D.cool_steps = P.cooldown_s <= 0 ? 0 : (P.cooldown_s + 59) / 60;
+        // first step after an exit at step i that may evaluate an entry: i + ceil(cooldown_s / 60), and never the exit
+        // tick itself (evaluate_entry ran before the exit, M:2936 / M:2966), so a zero cooldown counts as one step
+        D.cool_steps = P.cooldown_s <= 0 ? 1 : (P.cooldown_s + 59) / 60;
         D.overtouch = P.overtouch_limit; D.spd = P.steps_per_day; D.table = t;
         D.flags = P.flags & 0xffffu;
         const bool ml_on = !(P.flags & QMMX_F_DISABLE_ML_GATE) && ctx->n_lr > 0;

@@ -266,12 +266,14 @@ struct LeanEngine {
     }
 
     __device__ __forceinline__ void step(const ScanArgs& A, float pf, float hh, float ll, int i, int day_off) {
-        const bool elig = i >= cool;
         int code = QMMX_TOO_FAR;
-        if (PARITY) code = (cool == kNoCool) ? QMMX_IN_POSITION : (elig ? QMMX_TOO_FAR : QMMX_COOLDOWN);
+        if (PARITY) code = (cool == kNoCool) ? QMMX_IN_POSITION : (i >= cool ? QMMX_TOO_FAR : QMMX_COOLDOWN);
         const float xl = HL ? ll : pf, xh = HL ? hh : pf;
         const bool hit_lo = xl <= lo_thr, hit_hi = xh >= hi_thr;
         if (hit_lo | hit_hi) do_exit(A, pf, hit_lo, hit_hi, i);
+        // decided after the exit on purpose (one live copy of `cool`): an exit leaves cool = i + cool_steps > i, so the
+        // exit tick itself is never eligible, exactly as when the test is made before the exit (cool_steps >= 1, qmmx_mc.cu)
+        const bool elig = i >= cool;
         const float diff = pf - prev;
         if (diff != 0.f) d = diff;
         prev = pf;

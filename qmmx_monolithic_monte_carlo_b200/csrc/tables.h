@@ -56,7 +56,7 @@ static_assert(sizeof(DevTables) % 16 == 0, "DevTables stride");
 struct DevCombo {                       // one parameter combination (qmmx_params, preprocessed)
     double sp, tp, qmin, prox, pmax, wr, wm;
     double vstrong, vprox;              // VETO_VOL_STRONG, VETO_PROX (M:1381-1382)
-    int32_t cool_steps;                 // ceil(cooldown_s / 60): now_ms < until_ms  <=>  step < exit_step + cool_steps
+    int32_t cool_steps;                 // max(1, ceil(cooldown_s / 60)): first eligible step after an exit at step i is i + cool_steps
     int32_t overtouch;
     int32_t spd;                        // steps per day
     int32_t table;
