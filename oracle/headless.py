@@ -491,15 +491,86 @@ def nearest_level_first(levels: Sequence[Level], px: float):
     return k, dist
 
 
-def find_candidates(bars_c: Sequence[float], levels: Sequence[Level], params: Params, *,
-                    touch_limit: int, gate_order: str = "mc"):
-    """Candidate pass of `simulate_monte_carlo` (M:3385-3442) with with_gates=False.
+class SimGates:
+    """`MonolithicEngine.evaluate_entry` (M:1492-1771) as the two simulators drive it (M:3414-3426, M:3582-3607).
 
-    gate_order is kept for the gated variants ("mc": touch limit before gates,
-    "sim": gates before touch limit); the ungated detector is identical in both.
+    The simulators call the gate on a FRESH engine: no open trade (M:1508 never fires), `cooldown_until_ms`
+    = 0 against a wall-clock `now_ms` (M:1516 never fires), `last_ts_ms = now_ms` (fresh), `state.last_direction` = None
+    and never updated (only the live loop writes it, M:2952-2955), so a flat close is DIR_UNKNOWN (M:1538).  What DOES
+    persist from candidate to candidate is the engine's own contact latch and per-level touch count (M:1557-1587):
+    they are advanced only by the candidates that reach the gate.  The accumulation guard is never fed by the simulators
+    (`ingest_tick` is the live loop's, M:2932), so its regime stays "unknown" and M:1589-1621 / M:1652-1666 are inert; the
+    bars carry no volume (M:234), so the soft veto never fires (M:1773-1794 with slope 0).
+    evaluate() returns (allowed, reason, message, side, k): `reason` is the step code (sub-reasons ML_CONF_LOW /
+    COMBINED_LOW kept apart), `message` the reference's own text (the SIM audit row GATE_SKIP quotes it, M:3596-3597).
+    """
+
+    def __init__(self, levels: Sequence[Level], params: Params, lr: Optional[LRModel] = None):
+        self.levels, self.P, self.lr = levels, params, lr
+        self.touch = [0] * len(levels)
+        self.latch = [False] * len(levels)
+        w_rules, w_ml = float(params.w_rules), float(params.w_ml)
+        s = w_rules + w_ml
+        if s <= 0:
+            w_rules, w_ml, s = 1.0, 0.0, 1.0
+        self.w_rules, self.w_ml = w_rules / s, w_ml / s
+
+    def evaluate(self, p: float, prev: Optional[float]):
+        P, levels = self.P, self.levels
+        prox, qmin = float(P.contact_prox), float(P.q_min_prob or 0.0)
+        d = 0
+        if prev is not None:                                          # M:1529-1537, last_direction is None
+            if p > prev + 1e-9:
+                d = 1
+            elif p < prev - 1e-9:
+                d = 2
+        if d == 0:
+            return False, "DIR_UNKNOWN", "Flat tick; cannot infer approach.", None, None
+        k, dist = nearest_level_first(levels, p)
+        lv = levels[k]
+        if dist > prox:                                               # unreachable from the simulators (same test, M:3398)
+            return False, "TOO_FAR", (f"Nearest level {lv.key[0]}/{lv.key[1]}[{lv.key[2]}] @{lv.price:.2f} "
+                                      f"too far ({dist:.2f})."), None, k
+        if not self.latch[k]:                                         # M:1562-1566
+            self.touch[k] += 1
+            self.latch[k] = True
+        for j in range(len(levels)):                                  # M:1572-1576
+            if j != k and self.latch[j] and abs(levels[j].price - p) > prox:
+                self.latch[j] = False
+        tc = self.touch[k]
+        if tc >= P.overtouch_limit:                                   # M:1579
+            return False, "LEVEL_OVERTOUCHED", f"Level over-touched (#{tc}).", None, k
+        conf = compute_confidence(dist, lv.solid, tc, prox)
+        if conf < qmin:                                               # M:1628
+            return False, "CONF_LOW", f"Confidence {conf:.2f} < min {qmin:.2f}.", None, k
+        side = 0 if d == 1 else 1
+        stop = lv.price - P.stop_padding if side == 0 else lv.price + P.stop_padding
+        mlp, ok_ml = conf, True
+        if not P.disable_ml_gate and self.lr is not None:             # M:1454-1466
+            prob = lr_prob(self.lr, 1.0, abs(lv.price - stop), float(tc), 1.0 if d == 1 else 0.0)
+            ok_ml, mlp = prob >= qmin, prob
+        if P.use_blend:                                               # M:1730-1742
+            blended = self.w_rules * conf + self.w_ml * mlp
+            if blended < qmin:
+                return False, "COMBINED_LOW", f"Blended {blended:.2f} < min {qmin:.2f}", side, k
+        elif (not P.disable_ml_gate) and not ok_ml:                   # M:1745-1755
+            return False, "ML_CONF_LOW", f"ML prob {mlp:.2f} < min {qmin:.2f}", side, k
+        return True, "OK", "Entry allowed.", side, k
+
+
+def find_candidates(bars_c: Sequence[float], levels: Sequence[Level], params: Params, *,
+                    touch_limit: int, gate_order: str = "mc", with_gates: bool = False,
+                    lr: Optional[LRModel] = None, skips: Optional[list] = None):
+    """Candidate pass of `simulate_monte_carlo` (M:3385-3442, gate_order="mc": the per-level touch limit is applied
+    BEFORE the gate, so a bar the limit drops never reaches the engine and a bar the gate drops still uses up the
+    limit) and of `simulate_last_bars` (M:3566-3612, gate_order="sim": the gate runs FIRST, the touch limit counts only
+    the bars it let through).  with_gates=True runs `evaluate_entry` per surviving bar on one fresh engine (SimGates);
+    the Monte Carlo then takes level and side from the gate's extras (M:3425-3426), the deterministic sim keeps its
+    own.  `skips` collects (i, reason, message, prox) of the bars the gate refused (the sim's GATE_SKIP audit rows).
     Returns list of dict(i, side, k, lvl, entry, stop, target, prox, tc).
     """
     prox, sp, tp = float(params.contact_prox), float(params.stop_padding), float(params.tp_padding)
+    gates = SimGates(levels, params, lr) if with_gates else None
     cands = []
     touch_counts = {}
     prev_c = None
@@ -515,11 +586,27 @@ def find_candidates(bars_c: Sequence[float], levels: Sequence[Level], params: Pa
             continue
         side = 0 if c > prev_c else 1
         key = round(lvl, 4)
-        tc = touch_counts.get(key, 0) + 1
-        if tc > touch_limit:
-            prev_c = c
-            continue
-        touch_counts[key] = tc
+        if gate_order == "mc":
+            tc = touch_counts.get(key, 0) + 1
+            if tc > touch_limit:
+                prev_c = c
+                continue
+            touch_counts[key] = tc
+        if gates is not None:
+            ok, reason, msg, g_side, g_k = gates.evaluate(c, prev_c)
+            if not ok:
+                if skips is not None:
+                    skips.append((i, reason, msg, proximity_abs))
+                prev_c = c
+                continue
+            if gate_order == "mc":                                    # M:3425-3426 (same level: same first-wins argmin)
+                side, k, lvl = g_side, g_k, levels[g_k].price
+        if gate_order != "mc":
+            tc = touch_counts.get(key, 0) + 1
+            if tc > touch_limit:
+                prev_c = c
+                continue
+            touch_counts[key] = tc
         if side == 0:
             stop, target = lvl - sp, lvl + tp
         else:
@@ -580,8 +667,9 @@ def mc_summary(totals, worst_dds, win_counts, loss_counts, open_counts):
 
 def jitter_monte_carlo(bars, levels, params: Params, *, n=600, touch_limit=1, trials=500,
                        entry_slip_std=0.01, level_jitter_std=0.02, stop_slip_std=0.0,
-                       target_slip_std=0.0, seed=None, draws=None):
-    """`simulate_monte_carlo` (M:3353-3538), with_gates=False, on bars = dict(o,h,l,c lists).
+                       target_slip_std=0.0, seed=None, draws=None, with_gates=False, lr=None):
+    """`simulate_monte_carlo` (M:3353-3538) on bars = dict(o,h,l,c lists); with_gates as the reference's argument
+    (its default is True and its only call site passes True, M:2662).
 
     Random source: Python `random.Random(seed)` exactly as the reference (M:3489), or
     `draws` = (normals[trials][K][4] unscaled N(0,1), uniforms[trials][K]) to replay
@@ -591,7 +679,7 @@ def jitter_monte_carlo(bars, levels, params: Params, *, n=600, touch_limit=1, tr
     c = list(bars["c"])[-n:]
     h = list(bars["h"])[-n:]
     l = list(bars["l"])[-n:]
-    cands = find_candidates(c, levels, params, touch_limit=touch_limit)
+    cands = find_candidates(c, levels, params, touch_limit=touch_limit, gate_order="mc", with_gates=with_gates, lr=lr)
     if not cands:
         return None
     sp, tp = float(params.stop_padding), float(params.tp_padding)
@@ -632,12 +720,14 @@ def jitter_monte_carlo(bars, levels, params: Params, *, n=600, touch_limit=1, tr
     return out
 
 
-def simulate_last_bars(bars, levels, params: Params, *, n=1200, touch_limit=2):
-    """`simulate_last_bars` (M:3540-3699), with_gates=False: stop tested before target."""
+def simulate_last_bars(bars, levels, params: Params, *, n=1200, touch_limit=2, with_gates=False, lr=None, skips=None):
+    """`simulate_last_bars` (M:3540-3699): stop tested before target; with_gates as the reference's argument (default
+    False; the GUI button passes True, M:2655-2657).  `skips` collects the GATE_SKIP rows (M:3594-3597)."""
     c = list(bars["c"])[-n:]
     h = list(bars["h"])[-n:]
     l = list(bars["l"])[-n:]
-    cands = find_candidates(c, levels, params, touch_limit=touch_limit)
+    cands = find_candidates(c, levels, params, touch_limit=touch_limit, gate_order="sim", with_gates=with_gates, lr=lr,
+                            skips=skips)
     trades = []
     for cand in cands:
         side, stop, target, entry = cand["side"], cand["stop"], cand["target"], cand["entry"]

@@ -131,33 +131,52 @@ def synth_ohlc(n, seed, sigma=0.15, sub=4):
 
 
 def gen_jitter_cases():
+    """with_gates=False cases (the detector alone) and with_gates=True cases (the reference's own default, M:3353, and
+    what its GUI buttons pass, M:2655-2663): every run builds a fresh engine.  `gates` holds the engine settings a gated
+    case was run under (strings as written with settings_set) and the logistic model, if any."""
     out = []
-    for name, n, seed, trials, tl, levels_name, prox in [
-        ("mc_n390_fix30", 390, 21, 500, 1, "fix30", 0.1),
-        ("mc_n120_fix30", 120, 22, 500, 1, "fix30", 0.1),
-        ("mc_n390_blue4_tl2", 390, 23, 300, 2, "blue4", 0.1),
-        ("mc_n600_fix30_prox05", 600, 24, 200, 1, "fix30", 0.05),
+    for name, n, seed, trials, tl, levels_name, prox, gates in [
+        ("mc_n390_fix30", 390, 21, 500, 1, "fix30", 0.1, None),
+        ("mc_n120_fix30", 120, 22, 500, 1, "fix30", 0.1, None),
+        ("mc_n390_blue4_tl2", 390, 23, 300, 2, "blue4", 0.1, None),
+        ("mc_n600_fix30_prox05", 600, 24, 200, 1, "fix30", 0.05, None),
+        ("gated_n390_fix30", 390, 21, 500, 1, "fix30", 0.1, dict()),
+        ("gated_n600_fix30_tl3", 600, 25, 300, 3, "fix30", 0.1, dict()),
+        ("gated_n1200_fix30_tl6_overtouch", 1200, 26, 100, 6, "fix30", 0.1, dict(sigma=0.05)),
+        ("gated_n390_blue4_qmin075", 390, 23, 300, 2, "blue4", 0.1, dict(q_min_prob=0.75)),
+        ("gated_n600_fix30_lr_and", 600, 27, 200, 2, "fix30", 0.1, dict(lr=LR_A)),
+        ("gated_n600_fix30_lr_blend", 600, 28, 200, 2, "fix30", 0.1, dict(lr=LR_B, use_blend=True, w_rules=0.6, w_ml=0.5)),
+        ("gated_n390_fix30_flat_ticks", 390, 29, 100, 4, "fix30", 0.1, dict(sigma=0.02)),
     ]:
-        bars = synth_ohlc(n, seed)
+        g = gates or {}
+        bars = synth_ohlc(n, seed, sigma=g.get("sigma", 0.15))
         levels = levels_by_name(levels_name)
         settings = {"CONTACT_PROX": repr(prox), "ENABLE_VETO": "0"}
+        if "q_min_prob" in g:
+            settings["Q_MIN_PROB"] = repr(g["q_min_prob"])
+        if g.get("use_blend"):
+            settings.update(USE_BLEND="1", W_RULES=repr(g["w_rules"]), W_ML=repr(g["w_ml"]))
+        model = rh.make_sklearn_model(g["lr"]["coef"], g["lr"]["intercept"]) if "lr" in g else None
+        wg = gates is not None
         dict_bars = [dict(t=60000 * i, o=bars["o"][i], h=bars["h"][i], l=bars["l"][i], c=bars["c"][i])
                      for i in range(n)]
-        mc = rh.run_reference_monte_carlo(dict_bars, levels, settings, n=n, touch_limit=tl, trials=trials,
-                                          with_gates=False, seed=seed)
-        sim_msg, sim_rows = rh.run_reference_last_bars(dict_bars, levels, settings, n=n, touch_limit=tl,
-                                                       with_gates=False)
+        mc = rh.run_reference_monte_carlo(dict_bars, levels, settings, lr_model=model, n=n, touch_limit=tl, trials=trials,
+                                          with_gates=wg, seed=seed)
+        sim_msg, sim_rows = rh.run_reference_last_bars(dict_bars, levels, settings, lr_model=model, n=n, touch_limit=tl,
+                                                       with_gates=wg)
         out.append(dict(name=name, n=n, seed=seed, trials=trials, touch_limit=tl, levels=levels_name,
-                        contact_prox=prox, bars=bars, mc_message=mc[2] if mc else None,
+                        contact_prox=prox, with_gates=wg, gates={k: v for k, v in g.items() if k != "sigma"},
+                        bars=bars, mc_message=mc[2] if mc else None,
                         sim_message=sim_msg[2] if sim_msg else None,
                         sim_rows=[list(r) for r in sim_rows]))
-        print(name, (mc[2] if mc else None))
+        print(name, (mc[2] if mc else None), "| GATE_SKIP rows:", sum(1 for r in sim_rows if r[1].startswith("GATE_SKIP")))
     with open(os.path.join(GOLD, "jitter_mc.json"), "w") as f:
-        json.dump(dict(source="reference QMMXApp.simulate_monte_carlo / simulate_last_bars (with_gates=False)",
+        json.dump(dict(source="reference QMMXApp.simulate_monte_carlo / simulate_last_bars, with_gates False and True",
                        cases=out), f)
 
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    gen_engine_cases()
+    if "--jitter-only" not in sys.argv:
+        gen_engine_cases()
     gen_jitter_cases()

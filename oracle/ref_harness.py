@@ -288,9 +288,11 @@ def drive_reference_path(closes, levels, settings=None, *, lr_model=None, policy
                 regime=eng.acc_guard.regime)
 
 
-def run_reference_monte_carlo(bars, levels, settings=None, **kw):
-    """Unbound `QMMXApp.simulate_monte_carlo` (`qmmx_monolithic.py:3353-3538`); returns text."""
+def run_reference_monte_carlo(bars, levels, settings=None, lr_model=None, **kw):
+    """Unbound `QMMXApp.simulate_monte_carlo` (`qmmx_monolithic.py:3353-3538`); returns text.  A FRESH engine per run
+    (with_gates=True leaves touch counts and latches dirty); lr_model: None or an object with predict_proba."""
     q, conn, eng = make_engine(levels, settings)
+    eng.model = lr_model
     eng.recent_bars = [dict(b) for b in bars]
     fake = SimpleNamespace(engine=eng, conn=conn, _log_ui=lambda *a, **k: None)
     _captured_messages.clear()
@@ -298,12 +300,13 @@ def run_reference_monte_carlo(bars, levels, settings=None, **kw):
     return _captured_messages[-1] if _captured_messages else None
 
 
-def run_reference_last_bars(bars, levels, settings=None, **kw):
+def run_reference_last_bars(bars, levels, settings=None, lr_model=None, **kw):
     """Unbound `QMMXApp.simulate_last_bars` (`qmmx_monolithic.py:3540-3699`).
 
     Returns (messagebox tuple, list of audit rows (phase, code, message)).
     """
     q, conn, eng = make_engine(levels, settings)
+    eng.model = lr_model
     eng.recent_bars = [dict(b) for b in bars]
     fake = SimpleNamespace(engine=eng, conn=conn, _log_ui=lambda *a, **k: None)
     _captured_messages.clear()

@@ -15,4 +15,7 @@ for spec in "$@"; do
       python profiles/prof_case.py "$case" ${paths:-} > "$out.ncu.log" 2>&1 || { echo "NCU FAILED: $case"; tail -5 "$out.ncu.log"; continue; }
   python profiles/ncu_summary.py "$out.ncu-rep" > "$out.summary.txt" 2>&1
   head -3 "$out.summary.txt"
+  # per-SASS-instruction counters (needs -lineinfo): kept compressed; the report itself only when it is small
+  ncu -i "$out.ncu-rep" --page source --csv 2>/dev/null | gzip -9 > "$out.source.csv.gz"
+  if [ "$(stat -c %s "$out.ncu-rep")" -gt 12000000 ]; then rm -f "$out.ncu-rep"; fi
 done

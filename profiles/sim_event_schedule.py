@@ -179,3 +179,69 @@ if __name__ == "__main__":
     for R, win, K in ((32, None, 2), (32, None, 4), (32, None, 8), (64, None, 4), (32, 64, 4), (32, 64, 8), (32, 128, 4)):
         r = tile_rounds_b(c, i, x, R, win, K)
         print("B: tile R=%-3d window=%-5s K=%d  %.1f instr/step, %.3f rounds/step, %.1f lanes in C" % ((R, win, K) + r))
+
+
+def tile_rounds_c(contact, inpos, exits, R, window, KB=2, costs=(16, 75, 21, 19, 14.0, 7.0)):
+    """Structure C: contact rounds are batched (loop A: only the contact block, lanes that entered a position wait),
+    then the exit tests (loop B: up to KB iterations of two rows per lane, the exit block when a lane hits), and
+    again while a lane is behind.  costs = (head, contact, exit test, exit, phase 1 per step, chunk overhead per step),
+    taken from the SASS counters of the built kernel (profiles/)."""
+    V_, C_, S_, X_, P1_, OV_ = costs
+    steps, paths = contact.shape
+    w = paths // 32
+    ev = []
+    for p in range(w * 32):
+        l = []
+        for s in np.flatnonzero(contact[:, p] | inpos[:, p]):
+            if inpos[s, p]:
+                l.append((s, 0))
+                if exits[s, p]:
+                    l.append((s, 2))
+            else:
+                l.append((s, 1))
+        ev.append(l)
+    total, nA, nB = 0.0, 0, 0
+    for wi in range(w):
+        lanes = ev[wi * 32:(wi + 1) * 32]
+        ptr = [0] * 32
+        lag = window - R
+        cost = 0.0
+        for t0 in range(0, steps, R):
+            t1 = min(steps, t0 + R)
+            cost += (P1_ + OV_) * (t1 - t0)
+            must = steps if t1 == steps else max(0, t1 - lag)
+
+            def nxt(k):
+                return lanes[k][ptr[k]] if ptr[k] < len(lanes[k]) and lanes[k][ptr[k]][0] < t1 else (None, -1)
+            while any(ptr[k] < len(lanes[k]) and lanes[k][ptr[k]][0] < must for k in range(32)):
+                # loop A
+                while any(nxt(k)[1] == 1 and nxt(k)[0] < must for k in range(32)):
+                    cost += V_ + C_; nA += 1
+                    for k in range(32):
+                        if nxt(k)[1] == 1: ptr[k] += 1
+                cost += V_
+                # loop B
+                for it in range(KB):
+                    sl = [k for k in range(32) if nxt(k)[1] == 0]
+                    if not sl:
+                        break
+                    cost += S_; nB += 1
+                    hit = False
+                    for k in sl:
+                        for rr in range(2):               # two rows per iteration
+                            if nxt(k)[1] == 0:
+                                ptr[k] += 1
+                                if nxt(k)[1] == 2:
+                                    ptr[k] += 1; hit = True
+                                    break
+                    if hit:
+                        cost += X_
+        total += cost
+    return total / (w * steps), nA / (w * steps), nB / (w * steps)
+
+
+if __name__ == "__main__":
+    print("structure B with measured block costs (head 16, contact 75, exit test 21, exit 19, phase 1 14+7): %.1f" %
+          (lambda r: 21 + r[1] * (16 + 75 + 21 + 0.76 * 19))(tile_rounds_b(c, i, x, 8, 24, 2)))
+    for KB in (1, 2, 3):
+        print("C: chunk 8 window 24 KB=%d  %.1f instr/step, %.3f contact rounds/step, %.3f exit iterations/step" % ((KB,) + tile_rounds_c(c, i, x, 8, 24, KB)))

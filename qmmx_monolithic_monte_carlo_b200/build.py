@@ -16,7 +16,7 @@ INCLUDE = os.path.join(ROOT, "include")
 LIB = os.path.join(PKG, "libqmmx_mc.so")
 _OBJ_DIR = os.path.join(PKG, "build")
 
-SOURCES = ["qmmx_mc.cu", "kernels.cuh", "engine.cuh", "scan_lean.cuh", "tables.h", "tables_host.cpp", "tables_host.h"]
+SOURCES = ["qmmx_mc.cu", "kernels.cuh", "engine.cuh", "scan_lean.cuh", "scan_tile.cuh", "tables.h", "tables_host.cpp", "tables_host.h"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

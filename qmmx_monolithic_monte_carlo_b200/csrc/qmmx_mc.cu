@@ -12,6 +12,7 @@
 
 #include "kernels.cuh"
 #include "scan_lean.cuh"
+#include "scan_tile.cuh"
 #include "tables_host.h"
 
 using namespace qmmx;
@@ -44,6 +45,9 @@ struct qmmx_ctx {
     bool no_sweep = false;     // QMMX_NO_SWEEP=1: one launch per combo even for sweep-shaped parameter sets
     bool lean_ok = false;      // scan_lean.cuh's sign-encoded gate table is valid for these levels
     bool force_v1 = false;     // QMMX_SCAN_V1=1: run the first-generation lockstep kernel (A/B measurements)
+    bool no_tile = false;      // QMMX_NO_TILE=1: keep close-only scans on the lockstep lean kernel (A/B measurements)
+    bool no_tma = false;       // QMMX_NO_TMA=1: stage the tile kernel's rows with cp.async instead of TMA (A/B measurements)
+    void* encode_tiled = nullptr;   // cuTensorMapEncodeTiled, through cudaGetDriverEntryPoint (no libcuda link)
     // resident bars
     float *d_close = nullptr, *d_high = nullptr, *d_low = nullptr;
     float* d_vol = nullptr;                 // per-bar volume of the resident bars (library-owned), or null
@@ -260,6 +264,20 @@ int init_flat(qmmx_ctx* ctx) {
     return QMMX_OK;
 }
 
+// tensor map of one fp32 plane [steps][paths] (row pitch in elements) for the tile kernel's TMA staging
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool make_bar_tmap(const qmmx_ctx* ctx, CUtensorMap* map, const float* plane, int64_t pitch, int64_t paths, int32_t steps) {
+    if (!ctx->encode_tiled || ctx->no_tma || (pitch * 4) % 16 != 0 || ((uintptr_t)plane & 15) != 0 || paths < 1 || steps < 1) return false;
+    const cuuint64_t dim[2] = {(cuuint64_t)paths, (cuuint64_t)steps};
+    const cuuint64_t stride[1] = {(cuuint64_t)pitch * 4};
+    const cuuint32_t box[2] = {32u, (cuuint32_t)kChunk}, estr[2] = {1u, 1u};
+    return reinterpret_cast<EncodeTiledFn>(ctx->encode_tiled)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(plane), dim,
+                                                              stride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 struct ParityOut { qmmx_trade* trades = nullptr; int32_t* tcounts = nullptr; uint8_t* codes = nullptr; int32_t max_trades = 0; };
 
 // one launch per parameter combo (run constants travel as kernel parameters); parity outputs belong to combo 0
@@ -392,7 +410,30 @@ int launch_scan(qmmx_ctx* ctx, const float* cl, const float* h, const float* l, 
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE) || A.vol != nullptr || A.regime != nullptr;
         // the lean exit block assumes a single price cannot hit both thresholds: stop below / target above the level
         const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
-        if (lean && band_ok) {
+        if (lean && band_ok && !parity && !hl && !wide && !A.polw && !ctx->no_tile && pitch < ((int64_t)1 << 26)) {
+            // close-only exits, <= 32 levels: the tile-event kernel (scan_tile.cuh)
+            const size_t tsm = tile_smem_bytes();
+#define TILE(MDv, SLv)                                                                        \
+    do {                                                                                      \
+        auto k = tile_scan_kernel<MDv, SLv>;                                                  \
+        if ((rc = set_smem_attr(ctx, k, tsm)) != 0) return rc;                                \
+        k<<<lean_grid, kLeanThreads, tsm, ctx->stream>>>(A);                                  \
+    } while (0)
+#define TILE_TMA(MDv, SLv)                                                                    \
+    do {                                                                                      \
+        auto k = tile_scan_tma_kernel<MDv, SLv>;                                              \
+        if ((rc = set_smem_attr(ctx, k, tsm)) != 0) return rc;                                \
+        k<<<lean_grid, kLeanThreads, tsm, ctx->stream>>>(A, tmap);                            \
+    } while (0)
+            CUtensorMap tmap;
+            if (make_bar_tmap(ctx, &tmap, cl, pitch, paths, steps)) {
+                if (multiday) { if (slow) TILE_TMA(true, true); else TILE_TMA(true, false); }
+                else { if (slow) TILE_TMA(false, true); else TILE_TMA(false, false); }
+            } else if (multiday) { if (slow) TILE(true, true); else TILE(true, false); }
+            else { if (slow) TILE(false, true); else TILE(false, false); }
+#undef TILE_TMA
+#undef TILE
+        } else if (lean && band_ok) {
             if (!parity) { if (hl) LEAN(true, false); else LEAN(false, false); }
             else { if (hl) LEAN(true, true); else LEAN(false, true); }
         } else if (!parity) {
@@ -490,6 +531,15 @@ int qmmx_create(int device, qmmx_ctx** out) {
     ctx->sm_count = prop.multiProcessorCount;
     { const char* v1 = std::getenv("QMMX_SCAN_V1"); ctx->force_v1 = v1 && v1[0] == '1'; }
     { const char* ns = std::getenv("QMMX_NO_SWEEP"); ctx->no_sweep = ns && ns[0] == '1'; }
+    { const char* nt = std::getenv("QMMX_NO_TILE"); ctx->no_tile = nt && nt[0] == '1'; }
+    { const char* nt = std::getenv("QMMX_NO_TMA"); ctx->no_tma = nt && nt[0] == '1'; }
+    {
+        cudaDriverEntryPointQueryResult qres;
+        void* fn = nullptr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess) ctx->encode_tiled = fn;
+        else cudaGetLastError();       // no encoder: the tile kernel stages with cp.async
+    }
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(QMMX_E_CUDA);
     ctx->stream = ctx->own_stream;
@@ -898,7 +948,18 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
         } while (0)
         const bool multiday = ctx->n_lr > 1;
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
-        if (ctx->lean_ok && !ctx->force_v1 && A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0) {
+        const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
+        if (ctx->lean_ok && !ctx->force_v1 && band_ok && !hl && !wide && !ctx->no_tile) {
+            const size_t tsm = tile_smem_bytes();
+#define TFUSED(MDv, SLv)                                                                      \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, tile_fused_gbm_kernel<MDv, SLv>, tsm)) != 0) return rc;   \
+            tile_fused_gbm_kernel<MDv, SLv><<<lean_grid, kLeanThreads, tsm, ctx->stream>>>(A, g);  \
+        } while (0)
+            if (multiday) { if (slow) TFUSED(true, true); else TFUSED(true, false); }
+            else { if (slow) TFUSED(false, true); else TFUSED(false, false); }
+#undef TFUSED
+        } else if (ctx->lean_ok && !ctx->force_v1 && band_ok) {
             if (hl) { if (wide) LFUSED2(true, true); else LFUSED2(true, false); }
             else { if (wide) LFUSED2(false, true); else LFUSED2(false, false); }
         } else if (hl) { if (wide) FUSED(true, true); else FUSED(true, false); }

@@ -209,8 +209,8 @@ struct LeanEngine {
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
     }
 
-    __device__ __forceinline__ int contact(const ScanArgs& A, int k, float pf, int i, int day_off) {
-        const int side = d < 0.f ? 1 : 0;                         // M:1645: up -> long(0), down -> short(1)
+    // side: M:1645, up -> long (0), down -> short (1)
+    __device__ __forceinline__ int contact(const ScanArgs& A, int k, float pf, int i, int day_off, int side) {
         // latch + touch count (M:1562-1576)
         const latch_t bit = (latch_t)1 << k;
         const latch_t cand = WIDE ? (latch_t)lds_u64<Y::kCand>(sb + k * 8) : (latch_t)lds_u32<Y::kCand>(sb + k * 8);
@@ -292,7 +292,7 @@ struct LeanEngine {
                     v = pf <= r.x ? (lohi & 0xffu) : (lohi >> 8);
                 }
             }
-            if (v != kFar) code = contact(A, (int)v, pf, i, day_off);
+            if (v != kFar) code = contact(A, (int)v, pf, i, day_off, d < 0.f ? 1 : 0);
         }
         if (PARITY && A.codes) {
             if (A.n_levels == 0 && (code == QMMX_TOO_FAR || code == QMMX_DIR_UNKNOWN)) code = QMMX_NOLEVELS;
@@ -690,7 +690,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
                 if (hit_lo | hit_hi) E.do_exit(A, pf, hit_lo, hit_hi, i);
                 if ((cm >> u) & 1u) {
                     const uint32_t w = __shfl_sync(0xffffffffu, vs, u);
-                    if (elig) { E.d = (w >> 8) ? -1.f : 1.f; E.contact(A, (int)(w & 0xffu), pf, i, 0); }
+                    if (elig) E.contact(A, (int)(w & 0xffu), pf, i, 0, (int)(w >> 8));
                 }
                 ++u;
             }

@@ -12,6 +12,7 @@
 """
 from __future__ import annotations
 
+import math
 from dataclasses import dataclass, field
 from statistics import mean, median, pstdev
 from typing import Optional, Sequence
@@ -31,9 +32,95 @@ def _bar_arrays(bars, n):
     return c[-n:], h[-n:], l[-n:]
 
 
-def find_candidates(closes, level_prices, contact_prox, stop_padding, tp_padding, touch_limit):
-    """Candidate pass with_gates=False (M:3385-3442): nearest level to the close (first minimum wins), within
-    CONTACT_PROX, side by close-to-close move (flat => short), per-level touch limit keyed on round(level, 4)."""
+def _confidence(dist, solid, touch_count, prox):
+    """`compute_confidence` (M:1415-1427) with the direction known (+0.03 always)."""
+    base = max(0.0, 1.0 - (dist / max(1e-4, prox)))
+    base += 0.08 if solid else 0.02
+    if touch_count <= 1:
+        base += 0.10
+    elif touch_count == 2:
+        base -= 0.08
+    else:
+        base -= 0.08 * 2
+    base += 0.03
+    return max(0.0, min(1.0, base))
+
+
+class EntryGates:
+    """The engine gate as the simulators call it (`evaluate_entry`, M:1492-1771, from M:3414-3426 and M:3582-3607).
+
+    The reference runs it on the live engine object; the drop-in runs it on a fresh one: no open trade, no cooldown
+    (`cooldown_until_ms` = 0 against a wall-clock `now_ms`), `last_direction` unknown and never updated (only the live
+    loop writes it, M:2952-2955), accumulation guard never fed ("unknown": M:1589-1621 and M:1652-1666 inert), bars
+    without volume (soft veto inert, M:1773-1794).  What carries over from candidate to candidate is the engine's
+    contact latch and per-level touch count (M:1557-1587).  O(L) per call, a few hundred calls per run: host work.
+    """
+
+    def __init__(self, rows, prices, solid, *, contact_prox, stop_padding, q_min_prob=0.60, overtouch_limit=4, lr=None,
+                 disable_ml_gate=False, use_blend=False, w_rules=0.7, w_ml=0.3):
+        self.rows, self.price, self.solid = rows, [float(x) for x in prices], [bool(x) for x in solid]
+        self.prox, self.sp, self.qmin = float(contact_prox), float(stop_padding), float(q_min_prob or 0.0)
+        self.overtouch, self.lr = int(overtouch_limit), (None if lr is None else [float(x) for x in np.ravel(lr)])
+        self.disable_ml_gate, self.use_blend = bool(disable_ml_gate), bool(use_blend)
+        s = float(w_rules) + float(w_ml)                                  # M:1714-1719
+        self.w_rules, self.w_ml = (1.0, 0.0) if s <= 0 else (float(w_rules) / s, float(w_ml) / s)
+        self.touch = [0] * len(self.price)
+        self.latch = [False] * len(self.price)
+
+    def evaluate(self, p, prev):
+        """-> (allowed, reason, message, side, k); `message` is the reference's own text."""
+        lp, prox, qmin = self.price, self.prox, self.qmin
+        if prev is not None and p > prev + 1e-9:                          # M:1529-1537
+            up = True
+        elif prev is not None and p < prev - 1e-9:
+            up = False
+        else:
+            return False, "DIR_UNKNOWN", "Flat tick; cannot infer approach.", None, None
+        k = min(range(len(lp)), key=lambda j: abs(lp[j] - p))             # M:1543, first minimum wins
+        dist = abs(lp[k] - p)
+        if dist > prox:
+            r = self.rows[k]
+            return False, "TOO_FAR", (f"Nearest level {r['color']}/{r['type']}[{r['index']}] @{lp[k]:.2f} "
+                                      f"too far ({dist:.2f})."), None, k
+        if not self.latch[k]:                                             # M:1562-1566
+            self.touch[k] += 1
+            self.latch[k] = True
+        for j in range(len(lp)):                                          # M:1572-1576
+            if j != k and self.latch[j] and abs(lp[j] - p) > prox:
+                self.latch[j] = False
+        tc = self.touch[k]
+        if tc >= self.overtouch:                                          # M:1579
+            return False, "LEVEL_OVERTOUCHED", f"Level over-touched (#{tc}).", None, k
+        conf = _confidence(dist, self.solid[k], tc, prox)
+        if conf < qmin:                                                   # M:1628
+            return False, "CONF_LOW", f"Confidence {conf:.2f} < min {qmin:.2f}.", None, k
+        side = 0 if up else 1
+        mlp, ok_ml = conf, True
+        if not self.disable_ml_gate and self.lr is not None:              # M:1454-1466: x = [1, |L - stop|, touches, up]
+            stop = lp[k] - self.sp if side == 0 else lp[k] + self.sp
+            w = self.lr
+            z = w[4]
+            for wi, xi in zip(w[:4], (1.0, abs(lp[k] - stop), float(tc), 1.0 if up else 0.0)):
+                z = z + wi * xi
+            mlp = 1.0 / (1.0 + math.exp(-z))                             # float64, left-to-right sum, libm exp (as build_ml_tables)
+            ok_ml = mlp >= qmin
+        if self.use_blend:                                                # M:1730-1742
+            blended = self.w_rules * conf + self.w_ml * mlp
+            if blended < qmin:
+                return False, "COMBINED_LOW", f"Blended {blended:.2f} < min {qmin:.2f}", side, k
+        elif not self.disable_ml_gate and not ok_ml:                      # M:1745-1755
+            return False, "ML_CONF_LOW", f"ML prob {mlp:.2f} < min {qmin:.2f}", side, k
+        return True, "OK", "Entry allowed.", side, k
+
+
+def find_candidates(closes, level_prices, contact_prox, stop_padding, tp_padding, touch_limit, *, gates=None,
+                    gate_order="mc", skips=None):
+    """Candidate pass of the two simulators: nearest level to the close (first minimum wins), within CONTACT_PROX,
+    side by close-to-close move (flat => short), per-level touch limit keyed on round(level, 4).
+    gates = an EntryGates (with_gates=True) or None.  gate_order "mc" = `simulate_monte_carlo` (M:3385-3442): the touch
+    limit comes BEFORE the gate and the candidate takes level and side from the gate's extras; "sim" =
+    `simulate_last_bars` (M:3566-3612): the gate comes first and only the bars it lets through count against the limit.
+    `skips` collects (i, reason, message, prox) of refused bars (the sim's GATE_SKIP audit rows, M:3594-3597)."""
     out, seen, prev = [], {}, None
     lp = [float(x) for x in level_prices]
     for i, c in enumerate(closes):
@@ -45,8 +132,24 @@ def find_candidates(closes, level_prices, contact_prox, stop_padding, tp_padding
                 side = 0 if c > prev else 1
                 key = round(lp[k], 4)
                 tc = seen.get(key, 0) + 1
-                if tc <= touch_limit:
-                    seen[key] = tc
+                ok = True
+                if gate_order == "mc":
+                    ok = tc <= touch_limit
+                    if ok:
+                        seen[key] = tc
+                if ok and gates is not None:
+                    allowed, reason, msg, g_side, g_k = gates.evaluate(c, prev)
+                    if not allowed:
+                        ok = False
+                        if skips is not None:
+                            skips.append((i, reason, msg, dist))
+                    elif gate_order == "mc":
+                        side, k = g_side, g_k                     # M:3425-3426
+                if ok and gate_order != "mc":
+                    ok = tc <= touch_limit
+                    if ok:
+                        seen[key] = tc
+                if ok:
                     out.append(dict(i=i, side=side, k=k, lvl=lp[k], entry=c, prox=dist, tc=tc,
                                     stop=lp[k] - stop_padding if side == 0 else lp[k] + stop_padding,
                                     target=lp[k] + tp_padding if side == 0 else lp[k] - tp_padding))
@@ -94,16 +197,24 @@ def summarize(totals, drawdowns, wins, losses, opens, n_cand) -> MCSummary:
                      mean(int(x) for x in opens), np.asarray(totals), np.asarray(drawdowns))
 
 
+def _gates(with_gates, rows, price, solid, contact_prox, stop_padding, gate_settings):
+    return EntryGates(rows, price, solid, contact_prox=contact_prox, stop_padding=stop_padding, **gate_settings) if with_gates else None
+
+
 def monte_carlo(eng: MCEngine, bars, levels: Sequence[dict], *, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25,
-                n=600, touch_limit=1, trials=500, entry_slip_std=0.01, level_jitter_std=0.02, stop_slip_std=0.0,
-                target_slip_std=0.0, seed: Optional[int] = None, replay=None) -> Optional[MCSummary]:
-    """Same arguments and defaults as `simulate_monte_carlo` (M:3353-3355) with with_gates=False.  The random
-    source is the device's Philox stream (key = seed), or `replay` = (normals[trials][K][4], uniforms[trials][K])
-    to reproduce host-drawn numbers exactly.  Returns None when no candidate is found (the reference shows
-    "No candidates found", M:3444-3446)."""
-    rows, price, _ = sort_levels(levels)
+                n=600, touch_limit=1, trials=500, with_gates=True, entry_slip_std=0.01, level_jitter_std=0.02,
+                stop_slip_std=0.0, target_slip_std=0.0, seed: Optional[int] = None, replay=None,
+                **gate_settings) -> Optional[MCSummary]:
+    """Same arguments and defaults as `simulate_monte_carlo` (M:3353-3355), `with_gates=True` included: every bar that
+    survives the touch limit goes through the engine gate (EntryGates; `gate_settings` = q_min_prob, overtouch_limit,
+    lr = coef[4] + intercept, disable_ml_gate, use_blend, w_rules, w_ml: the engine settings the reference reads from
+    its object).  The random source is the device's Philox stream (key = seed), or `replay` = (normals[trials][K][4],
+    uniforms[trials][K]) to reproduce host-drawn numbers exactly.  Returns None when no candidate is found (the
+    reference shows "No candidates found", M:3444-3446)."""
+    rows, price, solid = sort_levels(levels)
     c, h, l = _bar_arrays(bars, n)
-    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit)
+    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit, gate_order="mc",
+                            gates=_gates(with_gates, rows, price, solid, contact_prox, stop_padding, gate_settings))
     if not cands:
         return None
     out = eng.run_jitter(h, l, cands, stop_padding, tp_padding,
@@ -134,14 +245,21 @@ class SimSummary:
 
 
 def last_bars(eng: MCEngine, bars, levels: Sequence[dict], *, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25,
-              n=1200, touch_limit=2):
-    """Same arguments and defaults as `simulate_last_bars` (M:3540-3541) with with_gates=False: candidate pass on the
-    host, the forward walks on the device (`qmmx_run_last_bars`, stop tested before target), then the reference's
-    per-trade `round(., 2)` and summary rules (M:3641-3666).  Returns (trades, SimSummary); the trade dicts carry
-    the reference's keys plus `j` (exit bar, -1 when open)."""
-    rows, price, _ = sort_levels(levels)
+              n=1200, touch_limit=2, with_gates=False, gate_skips=None, **gate_settings):
+    """Same arguments and defaults as `simulate_last_bars` (M:3540-3541; `with_gates` defaults to False there, the GUI
+    button passes True, M:2655-2657): candidate pass on the host (the gate runs BEFORE the touch limit, M:3582-3607),
+    the forward walks on the device (`qmmx_run_last_bars`, stop tested before target), then the reference's per-trade
+    `round(., 2)` and summary rules (M:3641-3666).  Returns (trades, SimSummary); the trade dicts carry the reference's
+    keys plus `j` (exit bar, -1 when open).  `gate_skips` (a list) receives the SIM audit rows of the refused bars,
+    ("SIM", "GATE_SKIP:<code>", "<reason> prox=<d>") as M:3596-3597 writes them; `gate_settings` as in monte_carlo."""
+    rows, price, solid = sort_levels(levels)
     c, h, l = _bar_arrays(bars, n)
-    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit)
+    skips = []
+    cands = find_candidates(c, price, contact_prox, stop_padding, tp_padding, touch_limit, gate_order="sim", skips=skips,
+                            gates=_gates(with_gates, rows, price, solid, contact_prox, stop_padding, gate_settings))
+    if gate_skips is not None:       # the reference's code for the two sub-reasons is CONF_LOW (M:1742, M:1755)
+        gate_skips.extend(("SIM", "GATE_SKIP:" + ("CONF_LOW" if r in ("ML_CONF_LOW", "COMBINED_LOW") else r),
+                           f"{msg} prox={d:.03f}") for _, r, msg, d in skips)
     outcome, exit_bar = eng.run_last_bars(h, l, cands) if cands else ((), ())
     trades = []
     for cand, oc, xb in zip(cands, outcome, exit_bar):

@@ -229,3 +229,35 @@ def test_c_oracle_online_policy_retrain_matches_headless():
         assert (h.policy_weights["go_long"] + h.policy_weights["go_short"]) == list(o["policy_weights"][j])
         n_pol += h.codes.count(H.ENTRY_CODES.index("ONLINE_POLICY"))
     assert n_pol > 0
+
+
+@pytest.mark.parametrize("lr_on,cents,cool", [(True, False, 120), (False, True, 8), (True, True, 0)])
+def test_numpy_batch_oracle_equals_c_oracle(lr_on, cents, cool):
+    """oracle/numpy_batch.py (the NumPy batch headless reference of SURVEY 8d, timed by bench.py as a CPU baseline)
+    against the C oracle: every integer counter and both reason histograms equal, PnL sums to 1e-12."""
+    from oracle import numpy_batch as NB
+    lv = H.sort_levels(F.levels_30())
+    kw = dict(contact_prox=0.1, cooldown_s=cool)
+    close = F.host_gbm_closes(3000, 390, seed=41 + cool, round_cents=cents)
+    lr = H.LRModel([0.2, -0.5, -0.45, 0.35], 1.0) if lr_on else None
+    lr_a = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]]) if lr_on else None
+    o = CO.run_paths(close, [x.price for x in lv], [x.solid for x in lv], abi.make_params(**kw), lr=lr_a, n_threads=4)["agg"]
+    b = NB.run_batch(close, lv, H.Params(**kw), lr)
+    assert list(o.entry_hist) == b["entry_hist"].tolist() and list(o.exit_hist) == b["exit_hist"].tolist()
+    assert (o.n_trades, o.n_wins, o.n_open) == (b["n_trades"], b["n_wins"], b["n_open"])
+    assert b["sum_pnl"] == pytest.approx(o.sum_pnl, rel=1e-12, abs=1e-9)
+    assert b["sum_pnl2"] == pytest.approx(o.sum_pnl2, rel=1e-12, abs=1e-9)
+    assert o.n_trades > 1000 and (not lr_on or o.entry_hist[abi.ENTRY_CODES.index("ML_CONF_LOW")] > 0)
+
+
+def test_numpy_batch_oracle_matches_reference_golden():
+    from oracle import numpy_batch as NB
+    for case in ENGINE_CASES:
+        lv, P, lr, pol = oracle_inputs(case)
+        if P.use_blend or not P.disable_policy_gate or (lr and len(lr) > 1):
+            continue
+        P.enable_veto = False             # inert without volume (the golden run had it on with volume-less bars)
+        b = NB.run_batch(case["close"], lv, P, lr[0] if lr else None)
+        assert b["entry_hist"].tolist() == np.bincount(case["codes"].ravel(), minlength=20).tolist(), case["name"]
+        closed = [t for tr in case["trades"] for t in tr if t["reason"] != 3]
+        assert b["n_trades"] == len(closed)

@@ -383,9 +383,33 @@ def test_gpu_monte_carlo_dropin_message(eng):
     ref = H.jitter_monte_carlo(case["bars"], lv, P, n=n, touch_limit=case["touch_limit"], trials=trials,
                                draws=(normals, uniforms))
     got = MC.monte_carlo(eng, case["bars"], levels_by_name(case["levels"]), contact_prox=case["contact_prox"], n=n,
-                         touch_limit=case["touch_limit"], trials=trials, replay=(normals, uniforms))
+                         touch_limit=case["touch_limit"], trials=trials, with_gates=False, replay=(normals, uniforms))
     assert got.message() == format_mc_message(ref)
     assert got.candidates == ref["candidates"]
+
+
+@pytest.mark.parametrize("case", [c for c in load_jitter_cases() if c.get("with_gates")], ids=lambda c: c["name"])
+def test_gpu_monte_carlo_dropin_with_gates(eng, case):
+    """`montecarlo.monte_carlo(..., with_gates=True)` -- the reference's default and what its GUI passes (M:2662): the
+    gated candidate pass finds the reference's candidate count (read from its own MC text) and, with the oracle's draws
+    replayed, the device walk gives the oracle's summary text; the gate removed candidates the detector alone keeps."""
+    from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    from tests.golden_util import format_mc_message, jitter_case_setup
+    lv = H.sort_levels(levels_by_name(case["levels"]))
+    wg, P, lr, gs = jitter_case_setup(case)
+    n, trials = case["n"], 400
+    closes = list(case["bars"]["c"])[-n:]
+    cands = H.find_candidates(closes, lv, P, touch_limit=case["touch_limit"], with_gates=True, lr=lr)
+    ungated = H.find_candidates(closes, lv, P, touch_limit=case["touch_limit"])
+    assert [c["i"] for c in cands] != [c["i"] for c in ungated]
+    assert case["mc_message"].startswith(f"Candidates: {len(cands)} |")
+    rng = np.random.default_rng(4)
+    normals = rng.standard_normal((trials, len(cands), 4)); uniforms = rng.random((trials, len(cands)))
+    ref = H.jitter_monte_carlo(case["bars"], lv, P, n=n, touch_limit=case["touch_limit"], trials=trials,
+                               draws=(normals, uniforms), with_gates=True, lr=lr)
+    got = MC.monte_carlo(eng, case["bars"], levels_by_name(case["levels"]), contact_prox=case["contact_prox"], n=n,
+                         touch_limit=case["touch_limit"], trials=trials, replay=(normals, uniforms), **gs)   # with_gates defaults to True
+    assert got.message() == format_mc_message(ref) and got.candidates == len(cands)
 
 
 def test_gpu_full_size_properties(eng):
@@ -568,9 +592,13 @@ def test_gpu_last_bars_dropin_matches_reference_rows(eng, case):
     """Row a15: `montecarlo.last_bars` (device walk) reproduces the SIM/TRADE rows and the "Sim complete" text the
     reference's `simulate_last_bars` wrote for the golden bars (tests/golden/jitter_mc.json)."""
     from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
+    from tests.golden_util import jitter_case_setup
+    wg, P, lr, gs = jitter_case_setup(case)
+    skips = []
     trades, s = MC.last_bars(eng, case["bars"], levels_by_name(case["levels"]), contact_prox=case["contact_prox"],
-                             n=case["n"], touch_limit=case["touch_limit"])
+                             n=case["n"], touch_limit=case["touch_limit"], with_gates=wg, gate_skips=skips, **gs)
     assert s.message() == case["sim_message"]
+    assert [list(r) for r in skips] == [r for r in case["sim_rows"] if r[1].startswith("GATE_SKIP")]   # M:3594-3597
     trows = [r[2] for r in case["sim_rows"] if r[1] == "TRADE"]
     assert len(trows) == len(trades)
     for txt, t in zip(trows, trades):
@@ -857,3 +885,88 @@ def test_gpu_wide_level_sets_first_generation_kernels(monkeypatch):
             assert_agg_equal(v1.run_fused_gbm(51, 0, P, T, g)[0].agg, o["agg"], sums_rel=1e-9)
     finally:
         v1.close()
+
+
+# ---- tile-event kernels (scan_tile.cuh): the production close-only scan and fused GBM kernels -----------------------
+TILE_CASES = [
+    # (paths, steps, params, days, mode, cents, sigma)
+    (4999, 390, dict(contact_prox=0.1, cooldown_s=120), 1, "and", False, 0.15),
+    (1, 1, dict(contact_prox=0.1, cooldown_s=120), 1, "and", False, 0.15),
+    (33, 7, dict(contact_prox=0.1, cooldown_s=8), 1, "none", False, 0.15),
+    (257, 391, dict(contact_prox=0.1, cooldown_s=0), 1, "and", True, 0.15),
+    (2050, 9, dict(contact_prox=0.2, cooldown_s=300, overtouch_limit=2), 1, "none", True, 0.15),
+    (3001, 64, dict(contact_prox=0.05, cooldown_s=61, stop_padding=0.05, tp_padding=0.05), 1, "and", True, 0.15),
+    (3000, 1170, dict(contact_prox=0.1, cooldown_s=120), 3, "and", False, 0.10),
+    (3000, 1170, dict(contact_prox=0.1, cooldown_s=120, disable_policy_gate=False), 3, "and+policy", False, 0.10),
+    (2000, 780, dict(contact_prox=0.1, cooldown_s=120, use_blend=True, w_rules=0.6, w_ml=0.4), 2, "blend", False, 0.10),
+    (1500, 400, dict(contact_prox=0.1, cooldown_s=1800, stop_padding=2.5, tp_padding=2.0), 1, "none", False, 0.15),
+    (1000, 390, dict(contact_prox=0.1, cooldown_s=120), 1, "and", False, 0.004),      # long flat stretches in cents
+]
+
+
+@pytest.mark.parametrize("ci", range(len(TILE_CASES)))
+def test_gpu_tile_kernel_equals_oracle_and_lean(eng, ci, monkeypatch):
+    """The tile-event kernel (per-lane cursors in a 32-row ring, masks + rounds) against the C oracle and against the
+    lockstep lean kernel (QMMX_NO_TILE=1) on ragged path/step counts, flat and cent-rounded closes (runs of equal
+    prices: direction carried across chunks), zero and day-long cooldowns, trades that outlast many chunks, per-day
+    logistic masks, the blend and OnlinePolicy gates."""
+    paths, steps, kw, days, mode, cents, sigma = TILE_CASES[ci]
+    rng = np.random.default_rng(100 + ci)
+    lr, pol = _lr_tables(rng, days)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(**kw)
+    close = F.host_gbm_closes(paths, steps, seed=500 + ci, sigma=sigma, round_cents=cents)
+    if ci == 10:
+        close[5:40, ::3] = close[5, ::3]              # 35 equal closes in a row, inside a contact window for some
+        close[100:140, 1::3] = np.float32(648.76)
+    use_lr = lr if mode in ("and", "and+policy", "blend") else None
+    use_pol = pol if "policy" in mode else None
+    o = CO.run_paths(close, price, solid, params, lr=use_lr, policy=use_pol, n_threads=4)
+    monkeypatch.setenv("QMMX_NO_TILE", "1")
+    lean = E.MCEngine(0)
+    monkeypatch.delenv("QMMX_NO_TILE")
+    try:
+        for e in (eng, lean):
+            configure(e, price, solid, params, use_lr, use_pol)
+            e.upload_bars(close)
+            assert_agg_equal(e.run_scan()[0].agg, o["agg"])
+    finally:
+        lean.close()
+
+
+@pytest.mark.parametrize("cents", [False, True], ids=["raw", "cents"])
+def test_gpu_tile_fused_gbm_equals_generate_then_scan(eng, cents):
+    """Fused Philox GBM + tile scan == gen_gbm_kernel bars scanned by the tile kernel == the same bars through the
+    C oracle, for a ragged path count and a step count that is not a multiple of the chunk."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120)
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    g = abi.make_gbm(round_cents=cents)
+    configure(eng, price, solid, params, lr)
+    for P, T in ((70_001, 390), (4097, 397), (999, 5)):
+        fused = eng.run_fused_gbm(11, 1234, P, T, g)[0].agg
+        eng.gen_gbm(11, 1234, P, T, g)
+        scan = eng.run_scan()[0].agg
+        close = eng.download_bars(P, T)[0]
+        o = CO.run_paths(close, price, solid, params, lr=lr, n_threads=4)
+        assert_agg_equal(scan, o["agg"])
+        assert_agg_equal(fused, o["agg"])
+
+
+def test_gpu_tile_kernel_volume_and_regime_gates(eng):
+    """SLOW tile variant with the per-bar volume plane: soft veto (M:1678-1705) and the breakout regime gate (M:1652-1666)
+    read global planes by (step, path) from inside the rounds."""
+    rng = np.random.default_rng(21)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, enable_veto=True)
+    P, T = 3000, 390
+    close = F.host_gbm_closes(P, T, seed=77, sigma=0.05)
+    vol = rng.lognormal(10.0, 0.9, size=(T, P)).astype(np.float32)
+    configure(eng, price, solid, params)
+    eng.upload_bars(close)
+    eng.upload_volume(vol)
+    a = eng.run_scan()[0]
+    o = CO.run_paths(close, price, solid, params, volume=vol, n_threads=4)
+    assert_agg_equal(a.agg, o["agg"])
+    assert a.entry_hist["VETO_CONTRA_VOL_LONG"] + a.entry_hist["VETO_CONTRA_VOL_SHORT"] > 0
+    eng.upload_volume(None)

@@ -165,19 +165,25 @@ def test_montecarlo_host_side_matches_oracle():
     """Product candidate pass + summary (montecarlo.py) vs the oracle's, on the reference-generated bars."""
     from oracle import headless as H
     from qmmx_monolithic_monte_carlo_b200 import montecarlo as MC
-    from tests.golden_util import format_mc_message, levels_by_name, load_jitter_cases
+    from tests.golden_util import format_mc_message, jitter_case_setup, levels_by_name, load_jitter_cases
     for case in load_jitter_cases():
         lv = H.sort_levels(levels_by_name(case["levels"]))
-        P = H.Params(contact_prox=case["contact_prox"])
+        wg, P, lr, gs = jitter_case_setup(case)
         n = case["n"]
         c, h, l = MC._bar_arrays(case["bars"], n)
-        mine = MC.find_candidates(c, [x.price for x in lv], P.contact_prox, P.stop_padding, P.tp_padding,
-                                  case["touch_limit"])
-        ref = H.find_candidates(list(case["bars"]["c"])[-n:], lv, P, touch_limit=case["touch_limit"])
-        assert [(a["i"], a["side"], a["k"], a["entry"], a["stop"], a["target"]) for a in mine] == \
-               [(b["i"], b["side"], b["k"], b["entry"], b["stop"], b["target"]) for b in ref]
+        rows, price, solid = MC.sort_levels(levels_by_name(case["levels"]))
+        for order in ("mc", "sim"):       # touch limit before the gate (M:3405-3420) / after it (M:3582-3612)
+            skips, oskips = [], []
+            gates = MC.EntryGates(rows, price, solid, contact_prox=P.contact_prox, stop_padding=P.stop_padding, **gs) if wg else None
+            mine = MC.find_candidates(c, price, P.contact_prox, P.stop_padding, P.tp_padding, case["touch_limit"],
+                                      gates=gates, gate_order=order, skips=skips)
+            ref = H.find_candidates(list(case["bars"]["c"])[-n:], lv, P, touch_limit=case["touch_limit"], with_gates=wg,
+                                    lr=lr, gate_order=order, skips=oskips)
+            assert [(a["i"], a["side"], a["k"], a["entry"], a["stop"], a["target"], a["tc"]) for a in mine] == \
+                   [(b["i"], b["side"], b["k"], b["entry"], b["stop"], b["target"], b["tc"]) for b in ref]
+            assert skips == oskips and (len(skips) > 0) == wg
         s = H.jitter_monte_carlo(case["bars"], lv, P, n=n, touch_limit=case["touch_limit"], trials=case["trials"],
-                                 seed=case["seed"])
+                                 seed=case["seed"], with_gates=wg, lr=lr)
         if s is None:
             continue
         # summary rules: feed the oracle's per-trial outputs through the product summariser

@@ -4,7 +4,7 @@ import pytest
 
 from oracle import headless as H
 from tests.golden_util import (format_mc_message, levels_by_name, load_engine_cases,
-                               load_jitter_cases, oracle_inputs)
+                               load_jitter_cases, oracle_inputs, jitter_case_setup)
 
 ENGINE_CASES = load_engine_cases()
 JITTER_CASES = load_jitter_cases()
@@ -85,19 +85,29 @@ def test_shipped_online_policy_weights_probe():
 
 @pytest.mark.parametrize("case", JITTER_CASES, ids=[c["name"] for c in JITTER_CASES])
 def test_jitter_mc_matches_reference_text(case):
+    """with_gates False and True (M:3414-3426: touch limit first, then the engine gate on one engine whose latches and
+    touch counts carry over): same candidates => same Mersenne-Twister draws => the reference's text, character for
+    character."""
     lv = H.sort_levels(levels_by_name(case["levels"]))
-    P = H.Params(contact_prox=case["contact_prox"])
+    wg, P, lr, _ = jitter_case_setup(case)
     s = H.jitter_monte_carlo(case["bars"], lv, P, n=case["n"], touch_limit=case["touch_limit"],
-                             trials=case["trials"], seed=case["seed"])
+                             trials=case["trials"], seed=case["seed"], with_gates=wg, lr=lr)
     assert format_mc_message(s) == case["mc_message"]
 
 
 @pytest.mark.parametrize("case", JITTER_CASES, ids=[c["name"] for c in JITTER_CASES])
 def test_simulate_last_bars_matches_reference_rows(case):
     lv = H.sort_levels(levels_by_name(case["levels"]))
-    P = H.Params(contact_prox=case["contact_prox"])
-    trades, s = H.simulate_last_bars(case["bars"], lv, P, n=case["n"], touch_limit=case["touch_limit"])
+    wg, P, lr, _ = jitter_case_setup(case)
+    skips = []
+    trades, s = H.simulate_last_bars(case["bars"], lv, P, n=case["n"], touch_limit=case["touch_limit"], with_gates=wg,
+                                     lr=lr, skips=skips)
     rows = case["sim_rows"]
+    # the GATE_SKIP breadcrumbs (M:3594-3597): code, the gate's own message and the proximity, bar by bar
+    gate_rows = [(r[1], r[2]) for r in rows if r[1].startswith("GATE_SKIP")]
+    mine = [("GATE_SKIP:" + ("CONF_LOW" if r in ("ML_CONF_LOW", "COMBINED_LOW") else r), f"{msg} prox={d:.03f}")
+            for _, r, msg, d in skips]
+    assert mine == gate_rows and (len(gate_rows) > 0) == wg
     summary = [r for r in rows if r[1] == "SUMMARY"][0][2]
     expect = (f"N={case['n']} | trades={s['trades']} | wins={s['wins']} loss={s['loss']} open={s['open']} | "
               f"total_R={s['total_R']} avg_R(closed)={s['avg_R']} | "
