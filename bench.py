@@ -2,16 +2,21 @@
 
     python bench.py --gpus 1 --steps 20 --warmup 3            # our arm (libqmmx_mc.so, sm_100a)
     python bench.py --impl reference --gpus 1 --steps 3 ...   # the reference's CPU path (oracle port), host cores
-    torchrun --nproc-per-node N ... bench.py --gpus N ...     # one rank per GPU, paths sharded, one NCCL all-reduce
+    torchrun --nproc-per-node N ... bench.py --gpus N ...     # one rank per GPU, paths sharded, one NCCL all-gather + merge kernel
 
 A "step" = one pass of the engine scan over one batch of resident synthetic bars (BASELINE.json configs[1]:
 1M GBM paths x 390 one-minute closes per GPU, the 30-level Blue/Orange/Black/Teal x Solid/Dashed fixture, sklearn-
-form LR entry filter enabled) + the reduction of PnL moments and reason-code histograms (+ NCCL all-reduce, N>1).
-Prints ONE JSON line on rank 0.
+form LR entry filter enabled) + the reduction of PnL moments and reason-code histograms (+ the merge over ranks, N>1).
+Prints ONE JSON line on rank 0.  The same line carries, outside the timed region of the headline: `c3` (BASELINE
+configs[2], the target config: 100M Philox paths x 390 STRONG-scaled over the N GPUs, fused generate+scan, one merge at
+the end, with an aggregate digest that must not depend on N), `c4`, `c5f`, `mc` (configs[3], configs[4], the
+reference's own jitter Monte Carlo), in-run equality checks against the C oracle, the Python/NumPy CPU baselines and a
+pinned host-to-device copy probe.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import sys
@@ -29,9 +34,6 @@ from qmmx_monolithic_monte_carlo_b200 import abi, fixtures as F  # noqa: E402
 METRIC = "simulated path-steps/sec (390-step paths)"
 UNIT = "path-steps/s"
 STEPS_PER_PATH = 390
-# DRAM bytes of one lean_scan_kernel launch over 1M x 390 fp32 closes, from the committed ncu capture
-# (1.560352 GB read + 7.43 MB written; algorithmic bytes are 1.560000 GB: nothing is re-read)
-NCU_TRAFFIC_BYTES = 1.560352e9 + 7.427e6
 
 
 def workload(name: str):
@@ -113,6 +115,70 @@ def measured_peak_hbm():
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def agg_digest(results) -> str:
+    """sha256 over every INTEGER aggregate of every combo (counters, both reason histograms, the 256-bin PnL histogram):
+    identical for any number of ranks when the paths are the same (float64 sums depend on the summation order and stay
+    out)."""
+    h = hashlib.sha256()
+    for r in results:
+        a = r.agg
+        ints = [a.n_paths, a.n_steps, a.n_trades, a.n_wins, a.n_open] + list(a.entry_hist) + list(a.exit_hist) + list(a.pnl_hist)
+        h.update(np.array(ints, dtype=np.uint64).tobytes())
+    return h.hexdigest()[:24]
+
+
+def int_aggs_equal(a, b) -> bool:
+    return (all(getattr(a, f) == getattr(b, f) for f in ("n_paths", "n_steps", "n_trades", "n_wins", "n_open")) and
+            list(a.entry_hist) == list(b.entry_hist) and list(a.exit_hist) == list(b.exit_hist) and list(a.pnl_hist) == list(b.pnl_hist) and
+            abs(a.sum_pnl - b.sum_pnl) <= 1e-9 * max(1.0, abs(b.sum_pnl)))
+
+
+def shipped_capture():
+    """binding_limit numbers come from the committed ncu capture of the shipped build, not from literals"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_shipped_capture.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def bind_numa(local_rank: int, world: int):
+    """One rank per GPU: pin the process (and so the first-touch placement of its host bars) to the NUMA node of its GPU;
+    when the platform reports no node per GPU, spread the ranks over the nodes round-robin.  QMMX_NUMA=off disables it."""
+    info = {"policy": os.environ.get("QMMX_NUMA", "auto")}
+    if info["policy"] == "off" or not hasattr(os, "sched_setaffinity"):
+        return info
+    try:
+        nodes = sorted(int(d[4:]) for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit())
+        node = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+            bus = bus.decode() if isinstance(bus, bytes) else bus
+            with open("/sys/bus/pci/devices/%s/numa_node" % bus[-12:].lower()) as f:
+                node = int(f.read().strip())
+        except Exception:
+            node = None
+        info["gpu_node"] = node
+        if info["policy"] == "spread" or node is None or node < 0 or node not in nodes:
+            node = nodes[local_rank % len(nodes)] if (world > 1 and len(nodes) > 1) else None
+        if node is None:
+            return info
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            info.update(node=node, cpus=len(allowed))
+    except Exception as e:           # never fatal: the binding is an optimisation of the host-side copy
+        info["error"] = str(e)[:80]
+    return info
 
 
 def cpu_port_run(close, price, solid, params, lr, threads):
@@ -331,6 +397,165 @@ def run_jitter_bench(args, rank, local_rank, world):
     eng.close()
 
 
+def _timed(eng, stream, world, local_rank, torch, dist, D, run, merge=True):
+    """One launch sequence, device-timed on `stream`, one merge over the ranks at the end, max over ranks."""
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    run()
+    if world > 1 and merge:
+        D.allgather_merge_(eng, local_rank)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=f"cuda:{local_rank}")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sub_lines(args, eng, stream, rank, local_rank, world, torch, dist, D):
+    """BASELINE.json configs[2..4] and the reference's own Monte Carlo, each run once (after a warm-up launch) outside
+    the headline's timed region.  c3 is STRONG-scaled as BASELINE.json states it: `--c3-paths` (100M) global path ids
+    split by distributed.shard_range, so every integer aggregate -- and `agg_digest` -- must be the same at N = 1, 2, 4, 8."""
+    from oracle import c_oracle as CO
+    from qmmx_monolithic_monte_carlo_b200 import engine as E, montecarlo as MC
+    out = {}
+    rows, price, solid = E.sort_levels(F.levels_30())
+    fp32_peak = eng.measure_fp32_peak()
+    # ---- c3: the target config -----------------------------------------------------------------------------------
+    g = abi.make_gbm()
+    params = engine_params()
+    eng.set_levels(F.levels_30()); eng.set_params(params); eng.set_lr(lr_weights())
+    total = args.c3_paths
+    lo, hi = D.shard_range(total, rank, world)
+    eng.run_fused_gbm_async(F.HOST_SEED, lo, min(hi - lo, 1 << 20), STEPS_PER_PATH, g)          # warm-up launch
+    l0 = eng.launch_count()
+    ms = _timed(eng, stream, world, local_rank, torch, dist, D,
+                lambda: eng.run_fused_gbm_async(F.HOST_SEED, lo, hi - lo, STEPS_PER_PATH, g))
+    res = eng.fetch_agg()
+    assert res[0].n_paths == total and res[0].n_steps == total * STEPS_PER_PATH, (res[0].n_paths, total)
+    units = total * STEPS_PER_PATH
+    c3 = {"workload": f"C3: {total} Philox GBM paths x 390, strong-scaled over {world} GPU(s) by global path id, fused "
+                      "generate+scan (no bar traffic), one all-gather + merge at the end",
+          "value": units / (ms * 1e-3), "unit": UNIT, "ms": ms, "paths_total": total, "scaling": "strong",
+          "gpu_launches": int(eng.launch_count() - l0), "agg_digest": agg_digest(res),
+          "n_trades": res[0].n_trades, "n_wins": res[0].n_wins, "sum_pnl": res[0].sum_pnl,
+          "roofline_fp32": {"achieved": 24 * units / (ms * 1e-3) / 1e12 / world, "peak": fp32_peak, "unit": "TFLOP/s per GPU",
+                            "frac": 24 * units / (ms * 1e-3) / 1e12 / world / fp32_peak, "flop_per_path_step": 24}}
+    if rank == 0:     # the fused kernel against the C oracle on the bars the materialising generator writes for the same ids
+        S = 65_536
+        fused = eng.run_fused_gbm(F.HOST_SEED, 0, S, STEPS_PER_PATH, g)[0].agg
+        eng.gen_gbm(F.HOST_SEED, 0, S, STEPS_PER_PATH, g)
+        bars = eng.download_bars(S, STEPS_PER_PATH)[0]
+        o = CO.run_paths(bars, price, solid, params, lr=lr_weights(), n_threads=os.cpu_count() or 1)["agg"]
+        c3["oracle_check"] = {"paths": S, "what": "fused kernel == C oracle over qmmx_gen_gbm bars of path ids [0, 65536)",
+                              "equal": bool(int_aggs_equal(fused, o))}
+        assert c3["oracle_check"]["equal"], "C3: fused kernel aggregates differ from the oracle"
+    out["c3"] = c3
+    # ---- c4: 256-combo sweep over resident bars (weak: 1M paths per GPU) ----------------------------------------
+    P4 = args.paths or 1_000_000
+    grid = [abi.make_params(contact_prox=0.10, stop_padding=0.10 + 0.05 * i, tp_padding=tp, cooldown_s=cd)
+            for i in range(16) for tp in (0.15, 0.25, 0.35, 0.50) for cd in (0, 60, 300, 900)]
+    eng.set_params(grid)
+    eng.gen_gbm(F.HOST_SEED, rank * P4, P4, STEPS_PER_PATH, g)
+    eng.run_scan_async()
+    l0 = eng.launch_count()
+    ms = _timed(eng, stream, world, local_rank, torch, dist, D, eng.run_scan_async)
+    res = eng.fetch_agg()
+    units = len(grid) * P4 * world * STEPS_PER_PATH
+    out["c4"] = {"workload": f"C4: {len(grid)} stop/target x cooldown combos x {P4} resident GBM paths x 390 per GPU (weak)",
+                 "value": units / (ms * 1e-3), "unit": "combo-path-steps/s", "ms": ms, "scaling": "weak",
+                 "gpu_launches": int(eng.launch_count() - l0), "agg_digest": agg_digest(res), "combos": len(res),
+                 "n_trades_combo0": res[0].n_trades}
+    # ---- c5f: fused block bootstrap of a 40-bar window into 5-day paths, per-day LR tables (weak: 1.25M per GPU) ---
+    P5, days = (args.paths or 1_250_000), 5
+    rng = np.random.default_rng(5)
+    lr5 = np.column_stack([rng.normal(0.2, 0.2, days), rng.normal(-0.5, 0.2, days), rng.normal(-0.45, 0.1, days),
+                           rng.normal(0.35, 0.1, days), rng.normal(1.0, 0.1, days)])
+    eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True)); eng.set_lr(lr5)
+    window = F.synthetic_window(40)
+    T5 = days * STEPS_PER_PATH
+    eng.run_fused_bootstrap_async(F.HOST_SEED, rank * P5, min(P5, 1 << 17), T5, window, 5)
+    l0 = eng.launch_count()
+    ms = _timed(eng, stream, world, local_rank, torch, dist, D,
+                lambda: eng.run_fused_bootstrap_async(F.HOST_SEED, rank * P5, P5, T5, window, 5))
+    res = eng.fetch_agg()
+    units = P5 * world * T5
+    out["c5f"] = {"workload": f"C5 fused: block bootstrap (block 5) of a 40-bar window into {P5} x {days}-day paths per GPU (weak), "
+                              "per-day LR weights, exits on high/low",
+                  "value": units / (ms * 1e-3), "unit": UNIT, "ms": ms, "scaling": "weak",
+                  "gpu_launches": int(eng.launch_count() - l0), "agg_digest": agg_digest(res), "n_trades": res[0].n_trades}
+    # ---- mc: the reference's own jitter Monte Carlo (rank 0's GPU) -----------------------------------------------
+    if rank == 0:
+        w = F.synthetic_window(390, seed=11)
+        c, h, l = (w[:, 3].astype(np.float64), w[:, 1].astype(np.float64), w[:, 2].astype(np.float64))
+        gates = MC.EntryGates(rows, price, solid, contact_prox=0.10, stop_padding=0.35, lr=lr_weights()[0])
+        cands = MC.find_candidates(c, price, 0.10, 0.35, 0.25, 2, gates=gates, gate_order="mc")     # with_gates=True
+        trials = 1 << 22
+        eng.run_jitter(h, l, cands, 0.35, 0.25, (0.02, 0.01, 0.0, 0.0), 1 << 16, seed=7)
+        l0 = eng.launch_count()
+        o = eng.run_jitter(h, l, cands, 0.35, 0.25, (0.02, 0.01, 0.0, 0.0), trials, seed=7)
+        k_ms = eng.last_timing_ms()
+        sm = MC.summarize(o["totals"], o["drawdowns"], o["wins"], o["losses"], o["opens"], len(cands))
+        ref_t = python_reference_timing()
+        out["mc"] = {"workload": f"jitter MC (simulate_monte_carlo, with_gates=True): {trials} trials x {len(cands)} candidates over one 390-bar day",
+                     "value": trials * len(cands) / (k_ms * 1e-3), "unit": "candidate-trials/s", "ms": k_ms, "n_gpus": 1,
+                     "gpu_launches": int(eng.launch_count() - l0), "mean_R": sm.mean, "var05": sm.var05,
+                     "reference_python": (ref_t or {}).get("simulate_monte_carlo")}
+    return out
+
+
+def python_reference_timing():
+    try:
+        with open(os.path.join(ROOT, "profiles", "python_reference_timing.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def python_baselines(close, levels, lr):
+    """The Python/NumPy CPU baselines SURVEY 8(d) names, on bounded samples of the headline bars (rank 0, host cores):
+    the NumPy batch headless engine (oracle/numpy_batch.py), the scalar headless function (oracle/headless.run_path), and
+    -- measured in the build container, because the reference does not travel to the GPU box -- the unmodified
+    reference's own evaluate_entry."""
+    from oracle import headless as H, numpy_batch as NB
+    lv = H.sort_levels(levels)
+    P = H.Params(contact_prox=0.10, stop_padding=0.35, tp_padding=0.25, q_min_prob=0.60, cooldown_s=120)
+    m = H.LRModel(list(lr[0][:4]), float(lr[0][4])) if lr is not None else None
+    nb_paths = min(close.shape[1], 20_000)
+    sample = np.ascontiguousarray(close[:, :nb_paths])
+    t0 = time.perf_counter(); NB.run_batch(sample, lv, P, m); dt_nb = time.perf_counter() - t0
+    sc_paths = min(close.shape[1], 1000)
+    t0 = time.perf_counter()
+    for j in range(sc_paths):
+        H.run_path(close[:, j], lv, P, lr=[m] if m else None)
+    dt_sc = time.perf_counter() - t0
+    out = {"numpy_batch": {"value": nb_paths * STEPS_PER_PATH / dt_nb, "unit": UNIT, "cores": 1,
+                           "sample": f"first {nb_paths} paths, oracle/numpy_batch.py (vectorised over paths, Python loop over steps)"},
+           "headless_scalar": {"value": sc_paths * STEPS_PER_PATH / dt_sc, "unit": UNIT, "cores": 1,
+                               "sample": f"first {sc_paths} paths, oracle/headless.run_path (pure Python)"},
+           "host_cpu": cpu_model(), "host_logical_cores": os.cpu_count()}
+    ref = python_reference_timing()
+    if ref:
+        out["reference_evaluate_entry"] = {"value": ref["evaluate_entry"]["path_steps_per_s"], "unit": UNIT, "cores": 1,
+                                           "sample": f"{ref['evaluate_entry']['paths']} paths, " + ref["evaluate_entry"]["what"],
+                                           "measured_on": ref["measured_on"] + " (profiles/python_reference_timing.json)"}
+    return out
+
+
+def cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -339,6 +564,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--paths", type=int, default=0, help="override paths per GPU (debug)")
+    ap.add_argument("--c3-paths", type=int, default=100_000_000, help="global path count of the strong-scaled c3 sub-line")
+    ap.add_argument("--no-sub", action="store_true", help="skip the c3 / c4 / c5f / mc sub-lines")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--lib", default=None, help="alternate libqmmx_mc build (kernel tuning variants)")
@@ -372,6 +599,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    numa = bind_numa(local_rank, world)      # before the host bars exist: first touch puts them on the rank's node
     paths = wl["paths"]
     rows, price, solid = E.sort_levels(wl["levels"])
     params = engine_params()
@@ -393,8 +621,8 @@ def main():
 
     def step():
         eng.run_scan_async()
-        if world > 1:   # one NCCL all-gather of the aggregate vector + the library's merge kernel, same stream order
-            scratch[0] = D.allgather_merge_(eng, local_rank, scratch=scratch[0])
+        if world > 1:   # a step's result is the whole job's aggregates: one NCCL all-gather of the 2.3 KB vector + the
+            scratch[0] = D.allgather_merge_(eng, local_rank, scratch=scratch[0])      # library's merge kernel
 
     for _ in range(args.warmup):
         step()
@@ -456,12 +684,31 @@ def main():
             e2e = {"value": expect_paths * STEPS_PER_PATH / dt, "unit": UNIT, "h2d_bytes_per_step": int(close.nbytes),
                    "d2h_bytes_per_step": int(abi.AGG_SLOTS * 8), "ms_per_step": dt * 1e3,
                    "api": "MCEngine.run_scan_host -> qmmx_run_scan_host (pinned host bars, chunked H2D overlapped with the scan)"}
+            # ceiling of the host side: the same pinned bars as ONE plain copy per rank (qmmx_upload_bars: cudaMemcpy2DAsync
+            # with pitch == width), all ranks at once.  e2e cannot beat it; the gap is what the pipeline leaves on the table.
+            eng.upload_bars(close)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for _ in range(2):
+                eng.upload_bars(close)
+            pt = (time.perf_counter() - t0) / 2
+            tp = torch.tensor([pt], dtype=torch.float64, device=f"cuda:{local_rank}")
+            if world > 1:
+                dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+            pt = float(tp.item())
+            e2e["h2d_probe"] = {"gb_per_s_per_rank": close.nbytes / pt / 1e9, "gb_per_s_aggregate": close.nbytes * world / pt / 1e9,
+                                "ms": pt * 1e3, "what": "plain pinned H2D of the same bars, all ranks concurrently (slowest rank)",
+                                "e2e_over_probe": pt / dt}
+            e2e["numa"] = numa
         finally:
             eng.unpin(close)
 
     if rank == 0:
         peak, peak_src = measured_peak_hbm()
         k_ms = float(np.mean(kernel_ms))
+        cap = shipped_capture()
         alg_bytes = 4.0 * paths * STEPS_PER_PATH
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
         line = {
@@ -472,17 +719,22 @@ def main():
             "config": {"workload": wl["workload"], "paths_per_gpu": paths, "steps_per_path": STEPS_PER_PATH,
                        "levels": len(rows), "lr_filter": bool(wl["lr"]), "bars": "fp32 close [step][path], resident in HBM",
                        "l2": "inputs (1.56 GB per GPU) larger than the 126 MB L2; no flush needed",
-                       "parallelism": f"paths sharded over {world} GPU(s); one NCCL all-reduce of the aggregate vector"},
+                       "policy_gate": "off (DISABLE_POLICY_GATE=1, as in the reference's recorded run, SURVEY B.2)",
+                       "parallelism": f"paths sharded over {world} GPU(s); per step one NCCL all-gather of the 2.3 KB aggregate "
+                                      "vector + the library's merge kernel"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES if paths == 1_000_000 else None,
-                         "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch "
-                                           "(profiles/r1_ncu_lean_scan_close_summary.txt)",
-                         "kernel": "lean_scan_kernel<MULTIDAY=0,HL=0,PARITY=0,WIDE=0,SLOW=0>", "kernel_ms": k_ms,
+                         "traffic": (cap or {}).get("dram_bytes") if paths == 1_000_000 else None,
+                         "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch (%s)" %
+                                           (cap or {}).get("summary", "no committed capture"),
+                         "kernel": (cap or {}).get("kernel", "tile_scan_tma_kernel<MULTIDAY=0,SLOW=0>"), "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
-                         "binding_limit": {"what": "instruction issue, not HBM", "issue_active_pct": 85.4,
-                                           "warp_instructions_per_warp_step": 91.5, "active_lanes_per_instruction": 15.4,
-                                           "source": "ncu --set full of this kernel on this command, "
-                                                     "profiles/r1_ncu_lean_scan_close_summary.txt (static, not re-measured per run)"}},
+                         "binding_limit": {"what": "instruction issue (and the ALU pipe), not HBM",
+                                           "issue_active_pct": (cap or {}).get("issue_active_pct"),
+                                           "warp_instructions_per_warp_step": (cap or {}).get("warp_instructions_per_warp_step"),
+                                           "active_lanes_per_instruction": (cap or {}).get("active_lanes_per_instruction"),
+                                           "alu_pipe_pct": (cap or {}).get("alu_pipe_pct"),
+                                           "source": "committed ncu capture of the shipped build: %s at git %s (not re-measured per run)" %
+                                                     ((cap or {}).get("summary"), (cap or {}).get("git"))}},
             "roofline_fp32": fp32_roofline(eng, paths * STEPS_PER_PATH / (k_ms * 1e-3), 12),
             "clocks": clocks, "gpu_launches": int(launches),
             "result_check": {"n_trades": res.n_trades, "n_wins": res.n_wins, "sum_pnl": res.sum_pnl},
@@ -492,10 +744,24 @@ def main():
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             sample = min(paths, 262_144)
-            agg, dt = cpu_port_run(close[:, :sample], price, solid, params, lr, threads)
+            sample_bars = np.ascontiguousarray(close[:, :sample])      # contiguous BEFORE the timer starts
+            agg, dt = cpu_port_run(sample_bars, price, solid, params, lr, threads)
             line["cpu_baseline"] = {"value": sample * STEPS_PER_PATH / dt, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"first {sample} paths x {STEPS_PER_PATH} steps of the same bars, "
-                                              "oracle/qmmx_oracle.c with pthreads"}
+                                              "oracle/qmmx_oracle.c with pthreads", "host_cpu": cpu_model()}
+            # the GPU scan of the same sample must give the oracle's aggregates (every counter, both histograms, PnL sum)
+            eng.upload_bars(sample_bars)
+            g_agg = eng.run_scan()[0].agg
+            line["oracle_check"] = {"paths": sample, "what": "GPU scan == C oracle on the first 262144 paths of the timed bars",
+                                    "equal": bool(int_aggs_equal(g_agg, agg))}
+            assert line["oracle_check"]["equal"], "C2: GPU aggregates differ from the oracle on the sample"
+            line["python_baselines"] = python_baselines(close, wl["levels"], lr)
+    subs = None
+    if not args.no_sub and args.workload == "c2":
+        subs = sub_lines(args, eng, stream, rank, local_rank, world, torch, dist, D)
+    if rank == 0:
+        if subs:
+            line.update(subs)
         print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:

@@ -60,7 +60,8 @@ enum {
     QMMX_E_CUDA        = -2,
     QMMX_E_NOMEM       = -3,
     QMMX_E_STATE       = -4,   /* call order: levels/params/bars not set */
-    QMMX_E_UNSUPPORTED = -5
+    QMMX_E_UNSUPPORTED = -5,
+    QMMX_E_NCCL        = -6    /* libnccl.so.2 missing, or an NCCL call failed (qmmx_last_error has the text) */
 };
 
 /* entry decision codes: reason strings of M:246-257 plus the sub-reasons the reference writes
@@ -260,6 +261,22 @@ int  qmmx_agg_unpack(qmmx_ctx* ctx, const void* flat_host, int n_combos, qmmx_ag
  * ([n_parts][n_combos * QMMX_AGG_SLOTS] 8-byte slots, device memory), then this call reduces them into the ctx's
  * own buffer on the ctx stream (SUM counters, SUM sums, MAX extrema).  Asynchronous; qmmx_fetch_agg reads it. */
 int  qmmx_merge_flat(qmmx_ctx* ctx, const void* d_parts, int n_parts);
+
+/* Multi-GPU merge without torch (SURVEY 8b `qmmx_allreduce(ctx, nccl_comm)`; the reference itself is one process,
+ * 8e): ONE ncclAllGather of the flat buffer on the ctx stream, then qmmx_merge_flat, so that after the call every
+ * rank's buffer holds the whole job's aggregates (SUM counters, SUM sums, MAX extrema).  libnccl.so.2 is dlopen'ed on
+ * first use (the copy already loaded in the process, e.g. torch's, else the system one); nothing links against it.
+ * nccl_comm: the caller's ncclComm_t, or NULL to use the communicator made by qmmx_nccl_init.  Asynchronous on the
+ * ctx stream; qmmx_fetch_agg reads the result.
+ * qmmx_nccl_unique_id: rank 0 fills 128 bytes (ncclGetUniqueId) which the caller ships to the other ranks by any
+ * means (file, socket, MPI, torch.distributed); qmmx_nccl_init: every rank joins with the same id (ncclCommInitRank);
+ * the communicator lives until qmmx_destroy. */
+int  qmmx_nccl_unique_id(qmmx_ctx* ctx, void* id128_out);
+int  qmmx_nccl_init(qmmx_ctx* ctx, const void* id128, int world_size, int rank);
+int  qmmx_allreduce(qmmx_ctx* ctx, void* nccl_comm);
+/* the CUDA stream the ctx launches on (its own, or the one given to qmmx_set_stream): for callers that order their
+ * own work against it */
+int  qmmx_get_stream(qmmx_ctx* ctx, void** cuda_stream_out);
 
 /* batch logistic scoring, fp32 FMA: out[i][h] = sigmoid(w[h] . x[i]) (+ bias[h] if bias != NULL) */
 int  qmmx_lr_score(qmmx_ctx* ctx, const float* x /* [n][dim] */, int64_t n, int32_t dim,

@@ -15,7 +15,7 @@ LR_DIM = 5
 POLICY_HEADS = 3
 POLICY_DIM = 7
 
-OK, E_BADARG, E_CUDA, E_NOMEM, E_STATE, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5
+OK, E_BADARG, E_CUDA, E_NOMEM, E_STATE, E_UNSUPPORTED, E_NCCL = 0, -1, -2, -3, -4, -5, -6
 
 # reason codes of the reference (qmmx_monolithic.py:246-257) + policy_events sub-reasons
 ENTRY_CODES = [
@@ -87,7 +87,11 @@ def make_params(*, contact_prox=0.05, stop_padding=0.35, tp_padding=0.25, q_min_
                 disable_ml_gate=False, use_blend=False, w_rules=0.7, w_ml=0.3,
                 disable_policy_gate=True, exit_on_hl=False, overtouch_limit=4,
                 steps_per_day=390, tiny_prices=False, online_retrain=False) -> Params:
-    """Engine settings with the reference's defaults (qmmx_monolithic.py:1371-1386, 1711-1715)."""
+    """Engine settings with the reference's defaults (qmmx_monolithic.py:1371-1386, 1711-1715), with ONE deviation:
+    `disable_policy_gate` defaults to True here, while the reference reads DISABLE_POLICY_GATE with default "0" (gate
+    on, M:3090, M:2078).  The recorded run of the reference had `policy=False` and its shipped
+    OnlinePolicy weights can never pass the gate (B.6: sigmoid = 0.37 < 0.60), so the reference default means "no trade
+    ever"; pass disable_policy_gate=False together with set_policy(weights) to run the gate (float64 slow path)."""
     flags = ((F_ENABLE_VETO if enable_veto else 0) | (F_DISABLE_ML_GATE if disable_ml_gate else 0)
              | (F_USE_BLEND if use_blend else 0) | (F_DISABLE_POLICY_GATE if disable_policy_gate else 0)
              | (F_EXIT_ON_HL if exit_on_hl else 0) | (F_TINY_PRICES if tiny_prices else 0)

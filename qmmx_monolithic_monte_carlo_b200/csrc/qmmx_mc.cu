@@ -1,6 +1,7 @@
 // libqmmx_mc.so — C ABI (include/qmmx_mc.h) over the sm_100a kernels in kernels.cuh.
 // One ctx = one GPU = one compute stream (+ one copy stream for the host-bar pipeline).  No CPU fallback.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -60,7 +61,12 @@ struct qmmx_ctx {
     int64_t stage_elems = 0;
     double* d_polw = nullptr; int64_t polw_pitch = 0, polw_paths = 0;   // QMMX_F_ONLINE_RETRAIN: learnt heads [14][pitch]
     float* d_ratios = nullptr; size_t ratios_cap = 0;     // bootstrap return ratios (qmmx_gen_bootstrap)
-    bool ran = false;
+    bool ran = false;          // some kernel of this ctx has run (qmmx_last_timing)
+    bool agg_ran = false;      // d_flat holds the aggregates of a scan / fused run ...
+    int agg_combos = 0;        // ... of this many combos (qmmx_fetch_agg, qmmx_agg_device, qmmx_merge_flat check it)
+    // NCCL through dlopen (qmmx_allreduce)
+    void* nccl_comm = nullptr;             // communicator made by qmmx_nccl_init (owned)
+    unsigned long long* d_gather = nullptr; size_t gather_slots = 0;
 };
 
 namespace {
@@ -259,6 +265,7 @@ int compute_regime(qmmx_ctx* ctx) {
 int init_flat(qmmx_ctx* ctx) {
     const int nc = (int)ctx->params.size();
     init_flat_kernel<<<std::max(1, (nc * QMMX_AGG_SLOTS + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, nc);
+    ctx->agg_ran = true; ctx->agg_combos = nc;      // every scan / fused entry point starts here
     ctx->launches++;
     CK(cudaGetLastError());
     return QMMX_OK;
@@ -276,6 +283,51 @@ bool make_bar_tmap(const qmmx_ctx* ctx, CUtensorMap* map, const float* plane, in
     return reinterpret_cast<EncodeTiledFn>(ctx->encode_tiled)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(plane), dim,
                                                               stride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// ---- NCCL, loaded at run time -------------------------------------------------------------------------------------
+struct NcclId { char internal[128]; };
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+    int (*CommCount)(void*, int*) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl(qmmx_ctx* ctx) {
+    if (g_nccl.lib) return QMMX_OK;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);      // the copy the process already uses (torch's)
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW);
+    if (!h) return fail(ctx, QMMX_E_NCCL, std::string("dlopen libnccl.so.2: ") + dlerror());
+    NcclApi a;
+    a.lib = h;
+    a.GetUniqueId = reinterpret_cast<int (*)(void*)>(dlsym(h, "ncclGetUniqueId"));
+    a.CommInitRank = reinterpret_cast<int (*)(void**, int, NcclId, int)>(dlsym(h, "ncclCommInitRank"));
+    a.CommCount = reinterpret_cast<int (*)(void*, int*)>(dlsym(h, "ncclCommCount"));
+    a.AllGather = reinterpret_cast<int (*)(const void*, void*, size_t, int, void*, cudaStream_t)>(dlsym(h, "ncclAllGather"));
+    a.CommDestroy = reinterpret_cast<int (*)(void*)>(dlsym(h, "ncclCommDestroy"));
+    a.GetErrorString = reinterpret_cast<const char* (*)(int)>(dlsym(h, "ncclGetErrorString"));
+    if (!a.GetUniqueId || !a.CommInitRank || !a.CommCount || !a.AllGather || !a.CommDestroy || !a.GetErrorString)
+        return fail(ctx, QMMX_E_NCCL, "libnccl.so.2 lacks a required symbol");
+    g_nccl = a;
+    return QMMX_OK;
+}
+
+int nccl_fail(qmmx_ctx* ctx, const char* what, int rc) {
+    return fail(ctx, QMMX_E_NCCL, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?"));
+}
+
+// aggregates of a scan / fused run of the CURRENT parameter set are on the device
+int check_agg(qmmx_ctx* ctx) {
+    if (!ctx->agg_ran || !ctx->d_flat) return fail(ctx, QMMX_E_STATE, "no scan or fused run has produced aggregates");
+    if (ctx->dirty || ctx->agg_combos != (int)ctx->params.size())
+        return fail(ctx, QMMX_E_STATE, "levels / params / models changed since the last run: run again before reading aggregates");
+    return QMMX_OK;
 }
 
 struct ParityOut { qmmx_trade* trades = nullptr; int32_t* tcounts = nullptr; uint8_t* codes = nullptr; int32_t max_trades = 0; };
@@ -510,6 +562,7 @@ const char* qmmx_strerror(int status) {
         case QMMX_E_NOMEM: return "out of device memory";
         case QMMX_E_STATE: return "call order: levels / params / bars not set";
         case QMMX_E_UNSUPPORTED: return "unsupported configuration";
+        case QMMX_E_NCCL: return "NCCL unavailable or failed";
         default: return "unknown status";
     }
 }
@@ -561,7 +614,8 @@ int qmmx_destroy(qmmx_ctx* ctx) {
     free_bars(ctx);
     for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
     cudaFree(ctx->d_tables); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
-    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios); cudaFree(ctx->d_polw);
+    if (ctx->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->nccl_comm);
+    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios); cudaFree(ctx->d_polw); cudaFree(ctx->d_gather);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
     cudaStreamDestroy(ctx->own_stream); cudaStreamDestroy(ctx->copy_stream);
@@ -792,6 +846,7 @@ int qmmx_gen_bootstrap(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
     }
     if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("gen_bootstrap: ") + cudaGetErrorString(e));
     if (with_vol && (rc = compute_regime(ctx)) != 0) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
     ctx->ran = true;
     return QMMX_OK;
 }
@@ -811,7 +866,7 @@ int qmmx_run_scan_async(qmmx_ctx* c) {
 
 int qmmx_fetch_agg(qmmx_ctx* c, qmmx_agg* agg_out) {
     ENTER(c);
-    if (!ctx->ran || !ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    { int rc0 = check_agg(ctx); if (rc0 != 0) return rc0; }
     const int nc = (int)ctx->params.size();
     std::vector<unsigned long long> flat((size_t)nc * QMMX_AGG_SLOTS);
     CK(cudaMemcpyAsync(flat.data(), ctx->d_flat, flat.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1051,7 +1106,7 @@ int qmmx_run_fused_gbm(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, int64_t
 
 int qmmx_agg_device(qmmx_ctx* c, void** d_flat, size_t* bytes) {
     ENTER(c);
-    if (!ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    { int rc0 = check_agg(ctx); if (rc0 != 0) return rc0; }
     if (d_flat) *d_flat = ctx->d_flat;
     if (bytes) *bytes = ctx->params.size() * QMMX_AGG_SLOTS * 8;
     return QMMX_OK;
@@ -1059,12 +1114,67 @@ int qmmx_agg_device(qmmx_ctx* c, void** d_flat, size_t* bytes) {
 
 int qmmx_merge_flat(qmmx_ctx* c, const void* d_parts, int n_parts) {
     ENTER(c);
-    if (!ctx->d_flat) return fail(ctx, QMMX_E_STATE, "nothing has run");
+    { int rc0 = check_agg(ctx); if (rc0 != 0) return rc0; }
     if (!d_parts || n_parts < 1) return fail(ctx, QMMX_E_BADARG, "merge_flat: null parts");
     const int n = (int)ctx->params.size() * QMMX_AGG_SLOTS;
     merge_flat_kernel<<<std::max(1, (n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, static_cast<const unsigned long long*>(d_parts), n_parts, n);
     ctx->launches++;
     CK(cudaGetLastError());
+    return QMMX_OK;
+}
+
+int qmmx_nccl_unique_id(qmmx_ctx* c, void* id128_out) {
+    ENTER(c);
+    if (!id128_out) return fail(ctx, QMMX_E_BADARG, "id128_out is null");
+    int rc = load_nccl(ctx);
+    if (rc != 0) return rc;
+    NcclId id;
+    const int nr = g_nccl.GetUniqueId(&id);
+    if (nr != 0) return nccl_fail(ctx, "ncclGetUniqueId", nr);
+    std::memcpy(id128_out, &id, sizeof(id));
+    return QMMX_OK;
+}
+
+int qmmx_nccl_init(qmmx_ctx* c, const void* id128, int world_size, int rank) {
+    ENTER(c);
+    if (!id128 || world_size < 1 || rank < 0 || rank >= world_size) return fail(ctx, QMMX_E_BADARG, "nccl_init: bad id / world_size / rank");
+    int rc = load_nccl(ctx);
+    if (rc != 0) return rc;
+    if (ctx->nccl_comm) { g_nccl.CommDestroy(ctx->nccl_comm); ctx->nccl_comm = nullptr; }
+    NcclId id;
+    std::memcpy(&id, id128, sizeof(id));
+    const int nr = g_nccl.CommInitRank(&ctx->nccl_comm, world_size, id, rank);
+    if (nr != 0) { ctx->nccl_comm = nullptr; return nccl_fail(ctx, "ncclCommInitRank", nr); }
+    return QMMX_OK;
+}
+
+int qmmx_allreduce(qmmx_ctx* c, void* nccl_comm) {
+    ENTER(c);
+    { int rc0 = check_agg(ctx); if (rc0 != 0) return rc0; }
+    int rc = load_nccl(ctx);
+    if (rc != 0) return rc;
+    void* comm = nccl_comm ? nccl_comm : ctx->nccl_comm;
+    if (!comm) return fail(ctx, QMMX_E_STATE, "no communicator: pass an ncclComm_t or call qmmx_nccl_init first");
+    int world = 0;
+    int nr = g_nccl.CommCount(comm, &world);
+    if (nr != 0 || world < 1) return nccl_fail(ctx, "ncclCommCount", nr);
+    const size_t n = (size_t)ctx->agg_combos * QMMX_AGG_SLOTS;
+    if (ctx->gather_slots < n * (size_t)world) {
+        if (ctx->d_gather) cudaFree(ctx->d_gather);
+        ctx->d_gather = nullptr; ctx->gather_slots = 0;
+        CK(cudaMalloc(&ctx->d_gather, n * (size_t)world * 8));
+        ctx->gather_slots = n * (size_t)world;
+    }
+    // same stream as the scan kernels and the merge: the gather reads finished aggregates, the merge reads a landed gather
+    nr = g_nccl.AllGather(ctx->d_flat, ctx->d_gather, n, /*ncclUint64*/ 5, comm, ctx->stream);
+    if (nr != 0) return nccl_fail(ctx, "ncclAllGather", nr);
+    return qmmx_merge_flat(ctx, ctx->d_gather, world);
+}
+
+int qmmx_get_stream(qmmx_ctx* c, void** cuda_stream_out) {
+    ENTER(c);
+    if (!cuda_stream_out) return fail(ctx, QMMX_E_BADARG, "cuda_stream_out is null");
+    *cuda_stream_out = (void*)ctx->stream;
     return QMMX_OK;
 }
 

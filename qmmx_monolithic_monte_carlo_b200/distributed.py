@@ -1,4 +1,5 @@
-"""Multi-GPU plumbing: paths shard across ranks, one all-reduce of the aggregate vector at the end.
+"""Multi-GPU plumbing: paths shard across ranks, one merge of the aggregate vector at the end (an NCCL all-gather of
+2.3 KB per combo + the library's merge kernel; `allreduce_flat_` is the three-message all-reduce form for host tensors).
 
 The reference is single-process; its Monte Carlo trials share nothing but read-only bars
 (qmmx_monolithic.py:3491-3498), so ranks never exchange bars.  Each rank owns global path ids
@@ -77,17 +78,38 @@ def allreduce_flat_(flat_i64, group=None):
 
 
 def allgather_merge_(eng, device_index: int, group=None, scratch=None):
-    """The production N>1 merge: ONE NCCL all-gather of the 2.3 KB-per-combo vector, then the library's own merge
-    kernel (qmmx_merge_flat) on the ctx stream.  Returns the gather scratch tensor for reuse."""
+    """The N>1 merge through torch.distributed: ONE NCCL all-gather of the 2.3 KB-per-combo vector, then the library's
+    own merge kernel (qmmx_merge_flat).  The gather runs on torch's current stream and the scan and merge kernels on
+    the ctx stream, so the two are ordered explicitly here: torch's stream waits for the ctx stream before the gather
+    (the aggregates are final) and the ctx stream waits for torch's before the merge (the gather has landed).  Returns
+    the gather scratch tensor for reuse.  A caller without torch uses `MCEngine.allreduce` (qmmx_allreduce) instead."""
     import torch
     import torch.distributed as dist
     flat = device_flat_tensor(eng, device_index)
     world = dist.get_world_size(group)
     if scratch is None or scratch.shape != (world,) + tuple(flat.shape):
         scratch = torch.empty((world,) + tuple(flat.shape), dtype=torch.int64, device=flat.device)
+    cur = torch.cuda.current_stream(flat.device)
+    raw = eng.stream()
+    ctx_stream = cur if raw == cur.cuda_stream else torch.cuda.ExternalStream(raw, device=flat.device)
+    if ctx_stream is not cur:
+        cur.wait_stream(ctx_stream)
     dist.all_gather_into_tensor(scratch, flat, group=group)
+    if ctx_stream is not cur:
+        ctx_stream.wait_stream(cur)
     eng.merge_flat(scratch.data_ptr(), world)
     return scratch
+
+
+def nccl_init_from_torch(eng, group=None):
+    """Give the engine its own NCCL communicator (qmmx_nccl_init) using torch.distributed only to ship rank 0's
+    128-byte unique id; afterwards `eng.allreduce()` merges the ranks without touching torch."""
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    box = [eng.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    eng.nccl_init(box[0], world, rank)
 
 
 def device_flat_tensor(eng, device_index: int):

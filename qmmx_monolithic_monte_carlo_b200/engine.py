@@ -73,6 +73,10 @@ def load_library(path: Optional[str] = None):
         "qmmx_agg_device": (C.c_int, [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]),
         "qmmx_agg_unpack": (C.c_int, [vp, vp, C.c_int, vp]),
         "qmmx_merge_flat": (C.c_int, [vp, vp, C.c_int]),
+        "qmmx_nccl_unique_id": (C.c_int, [vp, vp]),
+        "qmmx_nccl_init": (C.c_int, [vp, vp, C.c_int, C.c_int]),
+        "qmmx_allreduce": (C.c_int, [vp, vp]),
+        "qmmx_get_stream": (C.c_int, [vp, C.POINTER(vp)]),
         "qmmx_lr_score": (C.c_int, [vp, vp, i64, i32, vp, vp, i32, vp]),
         "qmmx_run_jitter": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, dbl, dbl, vp, i64, u64, u64,
                                       vp, vp, vp, vp, vp, vp, vp]),
@@ -356,6 +360,29 @@ class MCEngine:
     def merge_flat(self, d_parts_ptr: int, n_parts: int):
         """Reduce all-gathered flat buffers (device pointer, [n_parts][n_combos * AGG_SLOTS]) into this ctx's."""
         self._ck(self._L.qmmx_merge_flat(self._h, C.c_void_p(d_parts_ptr), n_parts))
+
+    def nccl_unique_id(self) -> bytes:
+        """128 bytes from ncclGetUniqueId (rank 0 calls this and ships them to the other ranks)."""
+        buf = C.create_string_buffer(128)
+        self._ck(self._L.qmmx_nccl_unique_id(self._h, buf))
+        return buf.raw
+
+    def nccl_init(self, unique_id: bytes, world_size: int, rank: int):
+        """Join the library's own NCCL communicator (ncclCommInitRank; collective over all ranks)."""
+        if len(unique_id) != 128:
+            raise ValueError("an NCCL unique id is 128 bytes")
+        self._ck(self._L.qmmx_nccl_init(self._h, C.c_char_p(unique_id), world_size, rank))
+
+    def allreduce(self, nccl_comm: Optional[int] = None):
+        """`qmmx_allreduce`: one ncclAllGather + the merge kernel on the ctx stream; afterwards fetch_agg() on any rank
+        returns the whole job's aggregates.  nccl_comm: a raw ncclComm_t, or None for the communicator of nccl_init."""
+        self._ck(self._L.qmmx_allreduce(self._h, C.c_void_p(nccl_comm) if nccl_comm else None))
+
+    def stream(self) -> int:
+        """Raw cudaStream_t the ctx launches on."""
+        p = C.c_void_p()
+        self._ck(self._L.qmmx_get_stream(self._h, C.byref(p)))
+        return p.value or 0
 
     def unpack_flat(self, flat_host: np.ndarray):
         flat_host = np.ascontiguousarray(flat_host).view(np.uint64).reshape(-1, abi.AGG_SLOTS)
