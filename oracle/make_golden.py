@@ -37,27 +37,27 @@ POL_B = {"go_long": [0.45, 0.5, 0.0, 0.0, 0.1, -0.1, 0.2],
 # name, levels, params (headless.Params kwargs), lr per-day list, policy per-day list, gen kwargs
 CASES = [
     dict(name="c1_blue_solid", levels="blue4", params=dict(contact_prox=0.1, cooldown_s=120),
-         paths=8, steps=390, seed=11),
+         paths=32, steps=390, seed=11),
     dict(name="fixture30_default_cooldown", levels="fix30", params=dict(contact_prox=0.1, cooldown_s=8, enable_veto=True),
-         paths=8, steps=390, seed=12),
+         paths=32, steps=390, seed=12),
     dict(name="fixture30_cents", levels="fix30", params=dict(contact_prox=0.1, cooldown_s=120),
-         paths=8, steps=390, seed=13, round_cents=True),
+         paths=32, steps=390, seed=13, round_cents=True),
     dict(name="fixture30_lr_and", levels="fix30", params=dict(contact_prox=0.1, cooldown_s=120),
-         lr=[LR_A], paths=8, steps=390, seed=14),
+         lr=[LR_A], paths=32, steps=390, seed=14),
     dict(name="fixture30_lr_blend", levels="fix30",
          params=dict(contact_prox=0.1, cooldown_s=300, use_blend=True, w_rules=0.6, w_ml=0.5),
-         lr=[LR_A], paths=8, steps=390, seed=15, round_cents=True),
+         lr=[LR_A], paths=32, steps=390, seed=15, round_cents=True),
     dict(name="fixture30_policy", levels="fix30",
          params=dict(contact_prox=0.1, cooldown_s=60, disable_policy_gate=False),
-         lr=[LR_A], policy=[POL_A], paths=8, steps=390, seed=16),
+         lr=[LR_A], policy=[POL_A], paths=32, steps=390, seed=16),
     dict(name="fixture30_multiday_swap", levels="fix30",
          params=dict(contact_prox=0.1, cooldown_s=900, disable_policy_gate=False),
-         lr=[LR_A, LR_B, LR_A], policy=[POL_A, POL_B, POL_A], paths=4, steps=3 * 390, seed=17),
+         lr=[LR_A, LR_B, LR_A], policy=[POL_A, POL_B, POL_A], paths=16, steps=3 * 390, seed=17),
     dict(name="fixture30_tight_prox_wide_pads", levels="fix30",
          params=dict(contact_prox=0.05, stop_padding=0.85, tp_padding=0.5, cooldown_s=0, q_min_prob=0.55),
-         paths=8, steps=390, seed=18, sigma=0.30),
+         paths=32, steps=390, seed=18, sigma=0.30),
     dict(name="fixture30_flat_ticks", levels="fix30", params=dict(contact_prox=0.1, cooldown_s=120),
-         paths=6, steps=390, seed=19, round_cents=True, sigma=0.02),
+         paths=32, steps=390, seed=19, round_cents=True, sigma=0.02),
 ]
 
 SETTING_KEYS = dict(contact_prox="CONTACT_PROX", stop_padding="STOP_PADDING", tp_padding="TP_PADDING",

@@ -19,7 +19,8 @@ def main():
     for r in rows[2:]:
         print('== kernel:', r[h.index('Kernel Name')] if 'Kernel Name' in h else '?')
         for i, n in enumerate(h):
-            if n in KEYS or n.startswith('sm__inst_executed_pipe_') or (n.startswith('smsp__average_warps_issue_stalled') and n.endswith('per_issue_active.ratio')):
+            pipe = n.startswith('sm__inst_executed_pipe_') and (n.endswith('.sum') or n.endswith('.avg.pct_of_peak_sustained_active'))
+            if n in KEYS or pipe or (n.startswith('smsp__average_warps_issue_stalled') and n.endswith('per_issue_active.ratio')):
                 print(f'{n} = {r[i]} {units[i]}')
 
 if __name__ == '__main__':

@@ -261,3 +261,32 @@ def test_numpy_batch_oracle_matches_reference_golden():
         assert b["entry_hist"].tolist() == np.bincount(case["codes"].ravel(), minlength=20).tolist(), case["name"]
         closed = [t for tr in case["trades"] for t in tr if t["reason"] != 3]
         assert b["n_trades"] == len(closed)
+
+
+def test_generators_follow_the_host_numpy_laws():
+    """The C restatement of the Philox generators (bit-equal to the device's, tests/test_gpu_parity.py) against
+    independent numpy-Philox draws of the same laws, through the engine: the statistical tier of
+    tests/test_gpu_statistical.py at CPU-suite size (two-sample z tests per reason code, chi-square on the PnL histogram)."""
+    import tests.test_gpu_statistical as S
+    lv = H.sort_levels(F.levels_30())
+    price, solid = [x.price for x in lv], [x.solid for x in lv]
+    # GBM: oracle Philox4x32-10 + Box-Muller (fp32) vs numpy float64 GBM
+    params = abi.make_params(contact_prox=0.10, cooldown_s=120)
+    c1 = F.host_gbm_closes(60_000, 390, seed=11)
+    c2, _, _ = CO.gen_gbm(12, 0, 90_000, 390, abi.make_gbm())
+    a1 = CO.run_paths(c1, price, solid, params, lr=S.LR, n_threads=8)["agg"]
+    a2 = CO.run_paths(c2, price, solid, params, lr=S.LR, n_threads=8)["agg"]
+    var = S.per_path_variances(CO.run_paths(np.ascontiguousarray(c1[:, :30_000]), price, solid, params, lr=S.LR, want_codes=True,
+                                            max_trades=96, n_threads=8), 390, 30_000)
+    S.compare(a2, 90_000, a1, 60_000, var)
+    # block bootstrap: oracle generator vs numpy
+    w = F.synthetic_window(40)
+    p2 = abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True)
+    c, h, l = S.numpy_block_bootstrap(w, 50_000, 390, 5, seed=5)
+    oc, oh, ol = CO.gen_bootstrap(77, 0, 70_000, 390, w, 5)
+    b1 = CO.run_paths(c, price, solid, p2, high=h, low=l, lr=S.LR, n_threads=8)["agg"]
+    b2 = CO.run_paths(oc, price, solid, p2, high=oh, low=ol, lr=S.LR, n_threads=8)["agg"]
+    var = S.per_path_variances(CO.run_paths(np.ascontiguousarray(c[:, :30_000]), price, solid, p2, lr=S.LR, want_codes=True, max_trades=128,
+                                            high=np.ascontiguousarray(h[:, :30_000]), low=np.ascontiguousarray(l[:, :30_000]),
+                                            n_threads=8), 390, 30_000)
+    S.compare(b2, 70_000, b1, 50_000, var)

@@ -26,7 +26,7 @@ def _check(levels, params, closes, lr=None, pol=None, volume=None):
         vj = None if volume is None else [float(x) for x in volume[:, j]]
         ref = rh.drive_reference_path(closes[:, j], levels, settings_for(params), lr_model=models,
                                       policy_w=pol, disable_policy_gate=P.disable_policy_gate, volume=vj,
-                                      online_retrain=P.online_retrain)
+                                      online_retrain=P.online_retrain, steps_per_day=P.steps_per_day)
         o = H.run_path(closes[:, j], lv, P, lr=lr, policy=pol, volume=vj)
         assert [H.ENTRY_CODES[c] for c in o.codes] == ref["codes"]
         assert len(o.trades) == len(ref["trades"])
@@ -169,3 +169,59 @@ def test_lr_contract_matches_sklearn_predict_proba():
         x = [1.0, abs(648.76 - (648.76 - 0.35)), float(rng.integers(1, 4)), float(rng.integers(2))]
         ours = H.lr_prob(H.LRModel(coef.tolist(), b), *x)
         assert ours == pytest.approx(float(m.predict_proba([x])[0][1]), abs=1e-15)  # scipy expit vs 1/(1+exp(-z)): last-bit differences only
+
+
+def _random_levels(rng):
+    """4..22 levels around the start price: duplicate prices (first-wins ties across colours), pairs closer than the
+    contact window (overlapping windows: latch release cases), a far outlier; both types, shuffled colours/indices."""
+    n = int(rng.integers(4, 23))
+    base = F.GBM_S0 + np.round(rng.normal(0, 2.5, n), 2)
+    if n >= 6:
+        base[1] = base[0]                                  # exact duplicate
+        base[3] = base[2] + float(rng.choice([0.03, 0.09, 0.11]))     # inside / at the edge of a 0.1 window
+        base[5] = base[4] - 0.2                            # windows touch at prox 0.1, overlap at 0.2
+    base[-1] = float(rng.choice([500.0, 700.0]))
+    colours = ["black", "blue", "orange", "teal"]
+    seen, out = {}, []
+    for p in base:
+        c, t = str(rng.choice(colours)), str(rng.choice(["solid", "dashed"]))
+        i = seen.get((c, t), 0)
+        seen[(c, t)] = i + 1
+        out.append({"color": c, "type": t, "index": i, "price": float(p)})
+    return out
+
+
+def _shaped_closes(rng, n, steps):
+    """GBM with flat stretches, exact returns to an earlier price (zero net move) and cent rounding on half the paths."""
+    sigma = float(rng.choice([0.03, 0.1, 0.15, 0.4]))
+    c = F.host_gbm_closes(n, steps, seed=int(rng.integers(1 << 30)), sigma=sigma, round_cents=bool(rng.integers(2))).copy()
+    for j in range(n):
+        for _ in range(int(rng.integers(0, 4))):
+            a = int(rng.integers(0, steps - 2)); b = min(steps, a + int(rng.integers(2, 30)))
+            c[a:b, j] = c[a, j]                            # flat stretch (DIR from last_direction, M:1536)
+        if rng.random() < 0.3:
+            c[: int(rng.integers(2, 12)), j] = c[0, j]     # flat start: DIR_UNKNOWN prefix
+    return c
+
+
+@pytest.mark.parametrize("seed", range(2000, 2040))
+def test_wide_seeded_differential_against_reference(seed):
+    """40 seeds x 8 paths = 320 paths through the UNMODIFIED reference engine and the oracle, step by step: random level
+    sets (duplicates, overlapping windows, outliers), every flag combination, flat stretches, 1-3 day logistic and
+    policy tables, short and long cooldowns.  The reference costs ~15 ms per path; the C oracle and the GPU are pinned
+    to headless.py on tens of thousands of paths elsewhere, this test is the independent anchor."""
+    rng = np.random.default_rng(seed)
+    days = int(rng.choice([1, 1, 2, 3]))
+    steps = int(rng.choice([60, 150, 390])) if days == 1 else 130 * days
+    params = dict(contact_prox=float(rng.choice([0.05, 0.1, 0.2])), stop_padding=float(rng.choice([0.1, 0.35, 0.85])),
+                  tp_padding=float(rng.choice([0.15, 0.25, 0.5])), cooldown_s=int(rng.choice([0, 8, 60, 120, 900])),
+                  q_min_prob=float(rng.choice([0.3, 0.6, 0.75, 0.9])), use_blend=bool(rng.integers(2)),
+                  enable_veto=bool(rng.integers(2)), disable_policy_gate=bool(rng.integers(2)),
+                  disable_ml_gate=bool(rng.random() < 0.25))
+    if params["use_blend"]:
+        params.update(w_rules=float(rng.choice([0.7, 0.5, 1.0])), w_ml=float(rng.choice([0.3, 0.5, 0.0])))
+    if days > 1:
+        params["steps_per_day"] = 130
+    lr = [H.LRModel(rng.normal(0, 0.6, 4).tolist(), float(rng.normal(0.5, 0.6))) for _ in range(days)] if rng.random() < 0.8 else None
+    pol = [{k: rng.normal(0.3, 0.8, 7).tolist() for k in ("go_long", "go_short", "skip")} for _ in range(days)]
+    _check(_random_levels(rng), params, _shaped_closes(rng, 8, steps), lr=lr, pol=pol)
