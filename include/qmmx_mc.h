@@ -87,7 +87,7 @@ enum { QMMX_EXIT_STOP = 0, QMMX_EXIT_TARGET, QMMX_EXIT_ESCALATE, QMMX_EXIT_OPEN 
 #define QMMX_F_ONLINE_RETRAIN       (1u << 6)  /* the OnlinePolicy go_long / go_short heads learn from the path's own closed
                                                  * trades (update_entry M:357-363 through _retrain_from_labeled_events
                                                  * M:3753-3803, lr 0.03, l2 1e-6 of M:290): qmmx_set_policy gives ONE table, the
-                                                 * initial weights; needs the policy gate on, one combo, resident bars */
+                                                 * initial weights; needs the policy gate on, one combo, the lean engine (<= 32 levels for the fused kernels) */
 
 typedef struct qmmx_params {
     uint32_t struct_size;      /* = sizeof(qmmx_params) */

@@ -916,7 +916,27 @@ int qmmx_run_scan(qmmx_ctx* c, qmmx_agg* agg_out, qmmx_trade* trades_out, int32_
     return qmmx_fetch_agg(ctx, agg_out);
 }
 
-// QMMX_F_ONLINE_RETRAIN keeps per-path weights beside resident bars: the fused (register-only) paths do not carry them
+// QMMX_F_ONLINE_RETRAIN in the fused (register-only) kernels: the bars never exist, the per-path learnt heads do --
+// [14][pitch] float64 in HBM, read and written once per closed trade (112 B), as in the resident-bar scan
+static int setup_fused_retrain(qmmx_ctx* ctx, ScanArgs& A, int64_t paths, bool wide) {
+    const bool band = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
+    if (ctx->params.size() != 1 || !ctx->lean_ok || ctx->force_v1 || !band || ctx->n_pol != 1 || wide)
+        return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN (fused) needs one combo, one policy table, <= 32 levels and the lean engine");
+    const int64_t pitch = round_up(std::max<int64_t>(paths, 1), 32);
+    if (!ctx->d_polw || ctx->polw_pitch != pitch) {
+        if (ctx->d_polw) cudaFree(ctx->d_polw);
+        ctx->d_polw = nullptr;
+        CK(cudaMalloc(&ctx->d_polw, (size_t)14 * (size_t)pitch * sizeof(double)));
+        ctx->polw_pitch = pitch;
+    }
+    ctx->polw_paths = paths;
+    polw_init_kernel<<<(unsigned)std::min<int64_t>((14 * pitch + 255) / 256, 65535), 256, 0, ctx->stream>>>(ctx->d_polw, ctx->d_pol, pitch);
+    ctx->launches++;
+    CK(cudaGetLastError());
+    A.polw = ctx->d_polw; A.pitch = pitch;
+    return QMMX_OK;
+}
+
 static bool any_retrain(const qmmx_ctx* ctx) {
     for (const DevCombo& D : ctx->h_combos)
         if ((D.flags & QMMX_F_ONLINE_RETRAIN) && !(D.flags & QMMX_F_DISABLE_POLICY_GATE)) return true;
@@ -969,7 +989,7 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
     if (paths < 0 || steps < 0) return fail(ctx, QMMX_E_BADARG, "negative size");
     if ((rc = prepare(ctx)) != 0) return rc;
     if (ctx->any_tiny) return fail(ctx, QMMX_E_UNSUPPORTED, "TINY_PRICES is not available in the fused GBM kernel");
-    if (any_retrain(ctx)) return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN runs over resident bars (qmmx_run_scan)");
+    const bool retrain = any_retrain(ctx);
     if (ctx->any_hl && gbm->sub_steps != 4) return fail(ctx, QMMX_E_STATE, "EXIT_ON_HL needs sub_steps = 4 (OHLC bars)");
     const GbmDev g = make_gbm(gbm, seed, path_offset);
     const size_t smem = scan_smem_bytes(ctx);
@@ -1004,7 +1024,17 @@ int qmmx_run_fused_gbm_async(qmmx_ctx* c, uint64_t seed, uint64_t path_offset, i
         const bool multiday = ctx->n_lr > 1;
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
         const bool band_ok = A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0;
-        if (ctx->lean_ok && !ctx->force_v1 && band_ok && !hl && !wide && !ctx->no_tile) {
+        if (retrain) {              // per-path OnlinePolicy heads learn from the path's own trades
+            if ((rc = setup_fused_retrain(ctx, A, paths, wide)) != 0) return rc;
+#define LFUSED_L(MDv, HLv)                                                                    \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, lean_fused_gbm_kernel<MDv, HLv, false, true, true>, lean_smem)) != 0) return rc;   \
+            lean_fused_gbm_kernel<MDv, HLv, false, true, true><<<lean_grid, kLeanThreads, lean_smem, ctx->stream>>>(A, g);  \
+        } while (0)
+            if (multiday) { if (hl) LFUSED_L(true, true); else LFUSED_L(true, false); }
+            else { if (hl) LFUSED_L(false, true); else LFUSED_L(false, false); }
+#undef LFUSED_L
+        } else if (ctx->lean_ok && !ctx->force_v1 && band_ok && !hl && !wide && !ctx->no_tile) {
             const size_t tsm = tile_smem_bytes();
 #define TFUSED(MDv, SLv)                                                                      \
         do {                                                                                  \
@@ -1039,7 +1069,7 @@ int qmmx_run_fused_bootstrap_async(qmmx_ctx* c, uint64_t seed, uint64_t path_off
     int rc = prepare(ctx);
     if (rc != 0) return rc;
     if (ctx->any_tiny || !ctx->lean_ok) return fail(ctx, QMMX_E_UNSUPPORTED, "fused bootstrap needs the lean engine (no TINY_PRICES, positive level prices)");
-    if (any_retrain(ctx)) return fail(ctx, QMMX_E_UNSUPPORTED, "ONLINE_RETRAIN runs over resident bars (qmmx_run_scan)");
+    const bool retrain = any_retrain(ctx);
     if (steps > 65535) return fail(ctx, QMMX_E_BADARG, "steps per path must be <= 65535 (16-bit per-path tallies)");
     std::vector<float> ratios(3 * (size_t)nret);
     for (int t = 1; t < window_len; ++t) {
@@ -1070,6 +1100,20 @@ int qmmx_run_fused_bootstrap_async(qmmx_ctx* c, uint64_t seed, uint64_t path_off
         if (!(A.combo.sp >= 0.0 && A.combo.tp >= 0.0 && A.combo.sp + A.combo.tp > 0.0))
             return fail(ctx, QMMX_E_UNSUPPORTED, "fused bootstrap needs stop_padding, tp_padding >= 0 and not both 0");
         const bool slow = (A.combo.flags & QMMX_F_USE_BLEND) || !(A.combo.flags & QMMX_F_DISABLE_POLICY_GATE);
+        if (retrain) {
+            if ((rc = setup_fused_retrain(ctx, A, paths, wide)) != 0) return rc;
+#define FB_L(MDv, HLv)                                                                        \
+        do {                                                                                  \
+            if ((rc = set_smem_attr(ctx, lean_fused_boot_kernel<MDv, HLv, false, true, true>, smem)) != 0) return rc;   \
+            lean_fused_boot_kernel<MDv, HLv, false, true, true><<<grid, kLeanThreads, smem, ctx->stream>>>(A, g);       \
+        } while (0)
+            if (multiday) { if (hl) FB_L(true, true); else FB_L(true, false); }
+            else { if (hl) FB_L(false, true); else FB_L(false, false); }
+#undef FB_L
+            ctx->launches++;
+            CK(cudaGetLastError());
+            continue;
+        }
 #define FB(MDv, HLv, Wv, SLv)                                                                 \
         do {                                                                                  \
             if ((rc = set_smem_attr(ctx, lean_fused_boot_kernel<MDv, HLv, Wv, SLv>, smem)) != 0) return rc;   \

@@ -57,22 +57,39 @@ struct LeanLayout {
 };
 inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
 
-#define QMMX_LDS(type, ptxty, cons)                                                                         \
+// -DQMMX_DEBUG_BOUNDS (build.py build_library(defines=...)): every shared-memory access of the lean and tile kernels
+// is checked against the kernel's dynamic window and its natural alignment, a violation traps (compute-sanitizer is
+// closed on this pool: profiles/r2/sanitizer_closed.log).  The product build compiles the check away.
+#ifdef QMMX_DEBUG_BOUNDS
+__device__ __forceinline__ void smem_chk(uint32_t a, uint32_t bytes) {
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(g_cell);
+    uint32_t size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(size));
+    if (a < base || a + bytes > base + size || (a & (bytes - 1u)) != 0u) __trap();
+}
+#else
+__device__ __forceinline__ void smem_chk(uint32_t, uint32_t) {}
+#endif
+
+#define QMMX_LDS(type, ptxty, cons, nbytes)                                                                 \
     template <int OFF> __device__ __forceinline__ type lds_##ptxty(uint32_t a) {                            \
+        smem_chk(a + OFF, nbytes);                                                                          \
         type v; asm("ld.shared." #ptxty " %0, [%1+%2];" : "=" cons(v) : "r"(a), "n"(OFF)); return v; }
-QMMX_LDS(uint32_t, u8, "r")
-QMMX_LDS(uint32_t, u32, "r")
-QMMX_LDS(unsigned long long, u64, "l")
-QMMX_LDS(double, f64, "d")
-QMMX_LDS(float, f32, "f")
+QMMX_LDS(uint32_t, u8, "r", 1)
+QMMX_LDS(uint32_t, u32, "r", 4)
+QMMX_LDS(unsigned long long, u64, "l", 8)
+QMMX_LDS(double, f64, "d", 8)
+QMMX_LDS(float, f32, "f", 4)
 #undef QMMX_LDS
 template <int OFF> __device__ __forceinline__ float2 lds_f2(uint32_t a) {
+    smem_chk(a + OFF, 8);
     float2 v; asm("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(a), "n"(OFF)); return v; }
 template <int OFF> __device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    smem_chk(a + OFF, 16);
     float4 v; asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a), "n"(OFF)); return v; }
 // touch bytes are read-modify-written by their own thread only; volatile keeps the asm statements in program order
-__device__ __forceinline__ uint32_t touch_ld(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
-__device__ __forceinline__ void touch_st(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v)); }
+__device__ __forceinline__ uint32_t touch_ld(uint32_t a) { smem_chk(a, 1); uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void touch_st(uint32_t a, uint32_t v) { smem_chk(a, 1); asm volatile("st.shared.u8 [%0], %1;" :: "r"(a), "r"(v)); }
 
 // per-CTA tables.  gate[(k*2+side)*16+tc] from the exact confidence intervals, the overtouch limit and (single day,
 // AND mode) the host-evaluated logistic mask.  Encoding: in range & y>0 -> OK; in range & y<0 -> ML_CONF_LOW;
@@ -424,12 +441,12 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
 // ---- fused GBM generate + scan on the lean engine: bars live in registers only (Philox4x32-10 + Box-Muller) ----------
 // The DIR_UNKNOWN prefix needs close[0] and the index of the first differing close before the walk starts: the
 // first Philox group(s) are generated twice (one extra group per path, ~1 % of the generator work).
-template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW>
+template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
     block_setup(A);
     lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
-    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW> E;
+    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW, false, LEARN> E;      // LEARN: QMMX_F_ONLINE_RETRAIN, heads in A.polw [14][A.pitch]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
@@ -500,7 +517,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm
 // ---- fused block bootstrap + scan (BASELINE config 5 without the 12 B/step round trip through HBM) ----------------
 // Same draws and the same IEEE products as gen_bootstrap_kernel (Philox counter (path id, block group, stream 1),
 // start = umulhi(r, nret), circular blocks), consumed in registers.  Bars carry no volume here: the soft veto is inert.
-template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW>
+template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boot_kernel(const __grid_constant__ ScanArgs A, const BootDev g) {
     typedef LeanLayout<WIDE ? 64 : 32> Y;
     block_setup(A);
@@ -512,7 +529,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boo
         }
     }
     __syncthreads();
-    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW> E;
+    LeanEngine<MULTIDAY, HL, false, WIDE, SLOW, false, LEARN> E;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;

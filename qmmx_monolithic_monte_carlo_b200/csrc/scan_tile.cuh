@@ -58,16 +58,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) if (++spins > (1 << 24)) __trap();     // a lost copy must not hang the device
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+    smem_chk(dst, 128); smem_chk(dst + (kChunk - 1) * 128, 128); smem_chk(bar, 8);
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  :: "r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
 }
 
 __device__ __forceinline__ void cp_async4(uint32_t dst, const char* src) {
+    smem_chk(dst, 4);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-__device__ __forceinline__ float ring_ld(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
-__device__ __forceinline__ void ring_st(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(v)); }
+__device__ __forceinline__ float ring_ld(uint32_t a) { smem_chk(a, 4); float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void ring_st(uint32_t a, float v) { smem_chk(a, 4); asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(v)); }
 
 // SRC: 0 = resident bars [step][pitch], 1 = Philox GBM generated in registers (close-only, sub_steps = 1)
 template <bool MULTIDAY, bool SLOW, int SRC>

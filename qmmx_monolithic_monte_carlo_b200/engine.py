@@ -33,7 +33,7 @@ def load_library(path: Optional[str] = None):
     global _LIB
     if _LIB is not None and path is None:
         return _LIB
-    p = path or _LIB_PATH
+    p = path or os.environ.get("QMMX_LIB") or _LIB_PATH      # QMMX_LIB: a tuning / debug build beside the product library
     if not os.path.exists(p):
         raise QmmxError(abi.E_STATE, f"{p} not found: build it with `python -m qmmx_monolithic_monte_carlo_b200.build` "
                                      "(there is no CPU fallback)")

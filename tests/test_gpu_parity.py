@@ -759,9 +759,23 @@ def test_gpu_online_policy_retrain(eng, hl):
     configure(eng, price, solid, [params, params], pol=pol)
     with pytest.raises(E.QmmxError):
         eng.run_scan()
+    # the fused generate+scan kernels carry the per-path heads too (SURVEY 8f-4 over Philox GBM and bootstrap paths): the
+    # same paths scanned from HBM give the same aggregates and bit-identical learnt weights
     configure(eng, price, solid, params, pol=pol)
-    with pytest.raises(E.QmmxError):
-        eng.run_fused_gbm(1, 0, 100, 390, g)
+    eng.gen_gbm(77, 0, P, T, g)
+    scan = eng.run_scan()[0].agg
+    w_scan = eng.download_policy_weights(P)
+    fused = eng.run_fused_gbm(77, 0, P, T, g)[0].agg
+    assert_agg_equal(fused, scan)
+    assert np.array_equal(eng.download_policy_weights(P), w_scan) and fused.entry_hist[abi.ENTRY_CODES.index("ONLINE_POLICY")] > 0
+    window = F.synthetic_window(40)
+    if hl:
+        eng.gen_bootstrap(5, 1000, P, T, window, 5)
+        scan = eng.run_scan()[0].agg
+        w_scan = eng.download_policy_weights(P)
+        fused = eng.run_fused_bootstrap(5, 1000, P, T, window, 5)[0].agg
+        assert_agg_equal(fused, scan)
+        assert np.array_equal(eng.download_policy_weights(P), w_scan)
 
 
 def _levels_48(seed=9):
