@@ -454,6 +454,20 @@ def sub_lines(args, eng, stream, rank, local_rank, world, torch, dist, D):
                               "equal": bool(int_aggs_equal(fused, o))}
         assert c3["oracle_check"]["equal"], "C3: fused kernel aggregates differ from the oracle"
     out["c3"] = c3
+    # ---- c2 with the OnlinePolicy gate ON (the reference's own default, M:3090; synthetic weights) -----
+    Pp = args.paths or 1_000_000
+    prng = np.random.default_rng(3)
+    eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, disable_policy_gate=False))
+    eng.set_policy(prng.normal(0.3, 0.6, (1, 3, 7)))
+    eng.gen_gbm(F.HOST_SEED, rank * Pp, Pp, STEPS_PER_PATH, g)
+    eng.run_scan_async()
+    ms = _timed(eng, stream, world, local_rank, torch, dist, D, eng.run_scan_async)
+    res = eng.fetch_agg()
+    out["c2_policy_gate"] = {"workload": f"C2 with DISABLE_POLICY_GATE=0: {Pp} resident GBM paths x 390 per GPU, float64 OnlinePolicy gate "
+                                         "(Neumaier dot, M:3046-3109) after the LR filter",
+                             "value": Pp * world * STEPS_PER_PATH / (ms * 1e-3), "unit": UNIT, "ms": ms, "scaling": "weak",
+                             "n_trades": res[0].n_trades, "online_policy_skips": res[0].entry_hist["ONLINE_POLICY"]}
+    eng.set_policy(None)
     # ---- c4: 256-combo sweep over resident bars (weak: 1M paths per GPU) ----------------------------------------
     P4 = args.paths or 1_000_000
     grid = [abi.make_params(contact_prox=0.10, stop_padding=0.10 + 0.05 * i, tp_padding=tp, cooldown_s=cd)

@@ -25,11 +25,25 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
     return c;
 }
 
-// Box-Muller on two 32-bit draws (same operation order as oracle/qmmx_oracle.c; MUFU transcendentals)
+// the same permutation with the ten round keys precomputed on the host (k + r * Weyl constant): kernel-parameter words,
+// i.e. constant-bank operands of the XORs, instead of 18 integer adds per call
+__device__ __forceinline__ uint4 philox4x32_10_rk(uint4 c, const uint32_t (&rk)[20]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ rk[2 * r], lo1, hi0 ^ c.w ^ rk[2 * r + 1], lo0);
+    }
+    return c;
+}
+
+__device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// Box-Muller on two 32-bit draws (same operation order as oracle/qmmx_oracle.c; MUFU transcendentals, square root included)
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
     const float u1 = __fmul_rn(__fadd_rn(__uint2float_rn(a), 0.5f), 2.3283064365386963e-10f);
     const float u2 = __fmul_rn(__fadd_rn(__uint2float_rn(b >> 8), 0.5f), 5.9604644775390625e-08f);
-    const float r = sqrtf(__fmul_rn(-2.0f, __logf(u1)));
+    const float r = sqrt_approx(__fmul_rn(-2.0f, __logf(u1)));
     const float ang = __fsub_rn(__fmul_rn(u2, 6.28318530717958648f), 3.14159265358979324f);
     float s, c;
     __sincosf(ang, &s, &c);
@@ -41,12 +55,13 @@ struct GbmDev {
     int32_t sub_steps, cents;
     uint32_t k0, k1;
     uint64_t path_offset;
+    uint32_t rk[20];            // Philox round keys: rk[2r] = k0 + r * 0x9E3779B9, rk[2r + 1] = k1 + r * 0xBB67AE85
 };
 
 __device__ __forceinline__ float round_cents(float s) { return __fdiv_rn(rintf(__fmul_rn(s, 100.0f)), 100.0f); }
 
 __device__ __forceinline__ void gbm_normals(const GbmDev& g, uint64_t gid, uint32_t group, float z[4]) {
-    const uint4 x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), group, 0u), g.k0, g.k1);
+    const uint4 x = philox4x32_10_rk(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), group, 0u), g.rk);
     box_muller(x.x, x.y, z[0], z[1]);
     box_muller(x.z, x.w, z[2], z[3]);
 }
