@@ -529,6 +529,19 @@ def python_reference_timing():
         return None
 
 
+def _nb_worker(job):
+    """one process of the all-cores NumPy batch baseline: its own GBM paths (the headline recipe, its own seed)"""
+    seed, n, levels, lr_row = job
+    from oracle import headless as H, numpy_batch as NB
+    lv = H.sort_levels(levels)
+    P = H.Params(contact_prox=0.10, stop_padding=0.35, tp_padding=0.25, q_min_prob=0.60, cooldown_s=120)
+    m = H.LRModel(list(lr_row[:4]), float(lr_row[4])) if lr_row is not None else None
+    bars = F.host_gbm_closes(n, STEPS_PER_PATH, seed=seed)
+    t0 = time.perf_counter()
+    NB.run_batch(bars, lv, P, m)
+    return time.perf_counter() - t0
+
+
 def python_baselines(close, levels, lr):
     """The Python/NumPy CPU baselines SURVEY 8(d) names, on bounded samples of the headline bars (rank 0, host cores):
     the NumPy batch headless engine (oracle/numpy_batch.py), the scalar headless function (oracle/headless.run_path), and
@@ -551,6 +564,20 @@ def python_baselines(close, levels, lr):
            "headless_scalar": {"value": sc_paths * STEPS_PER_PATH / dt_sc, "unit": UNIT, "cores": 1,
                                "sample": f"first {sc_paths} paths, oracle/headless.run_path (pure Python)"},
            "host_cpu": cpu_model(), "host_logical_cores": os.cpu_count()}
+    try:        # the same NumPy batch engine on every core: spawned workers, no CUDA in them
+        import multiprocessing as mp
+        cores = os.cpu_count() or 1
+        per = 10_000
+        jobs = [(1000 + k, per, levels, None if lr is None else [float(x) for x in lr[0]]) for k in range(cores)]
+        with mp.get_context("spawn").Pool(cores) as pool:
+            pool.map_async(_nb_worker, [(1, 200, levels, jobs[0][3])] * cores).get(timeout=90)     # import + warm-up
+            t0 = time.perf_counter()
+            pool.map_async(_nb_worker, jobs, chunksize=1).get(timeout=120)      # a stuck worker must not stall the line
+            dt_all = time.perf_counter() - t0
+        out["numpy_batch_all_cores"] = {"value": cores * per * STEPS_PER_PATH / dt_all, "unit": UNIT, "cores": cores,
+                                        "sample": f"{cores} processes x {per} GBM paths of the headline recipe (own seeds), oracle/numpy_batch.py"}
+    except Exception as e:
+        out["numpy_batch_all_cores"] = {"error": str(e)[:120]}
     ref = python_reference_timing()
     if ref:
         out["reference_evaluate_entry"] = {"value": ref["evaluate_entry"]["path_steps_per_s"], "unit": UNIT, "cores": 1,
