@@ -52,6 +52,7 @@ struct ScanArgs {
     int32_t cell_obase, cell_shift, cell_ncell;        // grid of the table (tables.h cell_of_bits), as constants
     float guard[4];                                    // far zones adjoining the grid (tables.h DevTables::guard)
     int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
+    unsigned int* tile_counter;                        // scan_tile.cuh: next unclaimed 32-path tile of this launch (zeroed by init_flat_kernel)
     DevCombo combo;
 };
 

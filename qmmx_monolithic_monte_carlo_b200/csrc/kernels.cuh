@@ -504,9 +504,11 @@ __global__ void merge_flat_kernel(unsigned long long* __restrict__ flat, const u
     }
 }
 
-__global__ void init_flat_kernel(unsigned long long* flat, int n_combos) {
+constexpr int kTileCounters = 4096;     // per-launch tile counters of one run (scan_tile.cuh), recycled round-robin
+__global__ void init_flat_kernel(unsigned long long* flat, int n_combos, unsigned int* counters) {
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
     const int n = n_combos * QMMX_AGG_SLOTS;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < kTileCounters; t += gridDim.x * blockDim.x) counters[t] = 0u;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         const int s = t % QMMX_AGG_SLOTS;
         flat[t] = (s >= QMMX_AGG_NU + QMMX_AGG_ND) ? (unsigned long long)__double_as_longlong(neg_inf) : 0ull;

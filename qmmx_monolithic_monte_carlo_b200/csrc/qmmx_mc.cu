@@ -42,6 +42,7 @@ struct qmmx_ctx {
     std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
     unsigned long long* d_flat = nullptr; int flat_combos = 0;
+    unsigned int* d_counters = nullptr; int counter_next = 0;      // scan_tile.cuh tile counters, one per launch of a run
     bool any_hl = false, any_tiny = false;
     bool no_sweep = false;     // QMMX_NO_SWEEP=1: one launch per combo even for sweep-shaped parameter sets
     bool lean_ok = false;      // scan_lean.cuh's sign-encoded gate table is valid for these levels
@@ -223,6 +224,11 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.regime = (cl && cl == ctx->d_close && ctx->d_vol) ? ctx->d_regime : nullptr;
     A.pitch = pitch; A.paths = paths; A.steps = steps; A.combo_index = c;
     A.tables = ctx->d_tables + D.table;
+    if (ctx->d_counters && ctx->counter_next == kTileCounters) {      // a run with more launches than counters: recycle them, in stream order
+        cudaMemsetAsync(ctx->d_counters, 0, kTileCounters * sizeof(unsigned int), ctx->stream);
+        ctx->counter_next = 0;
+    }
+    A.tile_counter = ctx->d_counters ? ctx->d_counters + ctx->counter_next++ : nullptr;
     A.flat = ctx->d_flat + (size_t)c * QMMX_AGG_SLOTS;
     const size_t per_mask = (size_t)ctx->n_lr * kMaxLevels;
     A.mlmask = (ctx->d_mlmask && (D.flags & kCbHasMl)) ? ctx->d_mlmask + per_mask * c : nullptr;
@@ -264,7 +270,9 @@ int compute_regime(qmmx_ctx* ctx) {
 
 int init_flat(qmmx_ctx* ctx) {
     const int nc = (int)ctx->params.size();
-    init_flat_kernel<<<std::max(1, (nc * QMMX_AGG_SLOTS + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, nc);
+    if (!ctx->d_counters) CK(cudaMalloc(&ctx->d_counters, kTileCounters * sizeof(unsigned int)));
+    ctx->counter_next = 0;
+    init_flat_kernel<<<std::max(1, (nc * QMMX_AGG_SLOTS + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_flat, nc, ctx->d_counters);
     ctx->agg_ran = true; ctx->agg_combos = nc;      // every scan / fused entry point starts here
     ctx->launches++;
     CK(cudaGetLastError());
@@ -616,7 +624,7 @@ int qmmx_destroy(qmmx_ctx* ctx) {
     for (int b = 0; b < 2; ++b) for (int f = 0; f < 3; ++f) cudaFree(ctx->d_stage[b][f]);
     cudaFree(ctx->d_tables); cudaFree(ctx->d_mlmask); cudaFree(ctx->d_mlprob);
     if (ctx->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->nccl_comm);
-    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios); cudaFree(ctx->d_polw); cudaFree(ctx->d_gather);
+    cudaFree(ctx->d_pol); cudaFree(ctx->d_flat); cudaFree(ctx->d_ratios); cudaFree(ctx->d_polw); cudaFree(ctx->d_gather); cudaFree(ctx->d_counters);
     cudaEventDestroy(ctx->ev0); cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) { cudaEventDestroy(ctx->ev_copied[i]); cudaEventDestroy(ctx->ev_done[i]); }
     cudaStreamDestroy(ctx->own_stream); cudaStreamDestroy(ctx->copy_stream);

@@ -359,6 +359,14 @@ struct LeanEngine {
     }
 };
 
+// Tiles are claimed from a per-launch counter instead of being dealt out round-robin: 1M paths are 6.6 tiles per resident
+// warp, so a static deal leaves 6 % of the machine idle behind the warps that drew 7, and tiles differ in work.
+__device__ __forceinline__ int64_t next_tile(const ScanArgs& A, int lane) {
+    unsigned int t = 0u;
+    if (lane == 0) t = atomicAdd(A.tile_counter, 1u);
+    return (int64_t)__shfl_sync(0xffffffffu, t, 0);
+}
+
 // Bars are [step][pitch]: one coalesced 128-byte line per warp, step and field; 2U rows are kept in flight per
 // thread in registers (register double buffer) -- at 1024 threads per SM a warp returns to the loop every ~0.3 us,
 // HBM latency is ~0.8 us.
@@ -426,7 +434,9 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
     // through a shuffle so that ptxas keeps the base in a register instead of rebuilding it from SR_CgaCtaId at every use
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(sb, path);
@@ -451,7 +461,9 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps;
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(sb, path);
@@ -534,7 +546,9 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boo
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps, nret = g.nret, block_len = g.block_len;
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(sb, path);

@@ -172,7 +172,9 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_kernel(const __grid
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps;
     const uint32_t pitch4 = (uint32_t)A.pitch * 4u;                 // bytes per row; kChunk rows fit 32 bits (checked on the host)
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);                    // dynamic: a warp takes the next unclaimed tile when it is done
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         T.begin(sb, rb, path, active);
@@ -236,7 +238,9 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_tma_kernel(const __
     uint32_t phase = 0;
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps;
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);                    // dynamic: a warp takes the next unclaimed tile when it is done
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         T.begin(sb, rb, path, active);
@@ -287,7 +291,9 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_fused_gbm_kernel(const _
     const uint32_t rb = tile_ring_base(sb) + warp * kRingBytes + lane * 4;
     const int64_t ntiles = (A.paths + 31) / 32;
     const int steps = A.steps;
-    for (int64_t tile = (int64_t)blockIdx.x * kLeanWarps + warp; tile < ntiles; tile += (int64_t)gridDim.x * kLeanWarps) {
+    for (;;) {
+        const int64_t tile = next_tile(A, lane);                    // dynamic: a warp takes the next unclaimed tile when it is done
+        if (tile >= ntiles) break;
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         T.begin(sb, rb, path, active);
