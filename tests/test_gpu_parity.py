@@ -984,3 +984,26 @@ def test_gpu_tile_kernel_volume_and_regime_gates(eng):
     assert_agg_equal(a.agg, o["agg"])
     assert a.entry_hist["VETO_CONTRA_VOL_LONG"] + a.entry_hist["VETO_CONTRA_VOL_SHORT"] > 0
     eng.upload_volume(None)
+
+
+def test_gpu_aggregate_reads_need_a_matching_run(eng):
+    """Round-1 advisor finding: fetch / agg_device / merge size their access by the CURRENT combo count, so they must
+    refuse to read after the configuration changed (more combos than the buffer of the last run holds) or when only a
+    generator / scorer has run; a new run makes them valid again."""
+    rows, price, solid = E.sort_levels(F.levels_30())
+    fresh = E.MCEngine(0)
+    try:
+        configure(fresh, price, solid, abi.make_params(contact_prox=0.1))
+        fresh.gen_gbm(1, 0, 1000, 50, abi.make_gbm())                   # a generator is not a scan: nothing to fetch
+        with pytest.raises(E.QmmxError):
+            fresh.fetch_agg()
+        assert fresh.run_scan()[0].n_paths == 1000
+        fresh.set_params([abi.make_params(contact_prox=0.1, cooldown_s=c) for c in (8, 60, 120, 300)])
+        for call in (fresh.fetch_agg, fresh.agg_device, lambda: fresh.merge_flat(0, 1), fresh.allreduce):
+            with pytest.raises(E.QmmxError):
+                call()
+        res = fresh.run_scan()
+        assert len(res) == 4 and all(r.n_paths == 1000 for r in res)
+        assert len(fresh.fetch_agg()) == 4
+    finally:
+        fresh.close()
