@@ -181,6 +181,16 @@ def bind_numa(local_rank: int, world: int):
     return info
 
 
+def headline_config(wl, world, n_levels):
+    """`config` of the headline line: the same dict in both arms (ours and --impl reference), so the driver sees one config"""
+    return {"workload": wl["workload"], "paths_per_gpu": wl["paths"], "steps_per_path": STEPS_PER_PATH,
+            "levels": n_levels, "lr_filter": bool(wl["lr"]), "bars": "fp32 close [step][path], resident in HBM",
+            "l2": "inputs (1.56 GB per GPU) larger than the 126 MB L2; no flush needed",
+            "policy_gate": "off (DISABLE_POLICY_GATE=1, as in the reference's recorded run, SURVEY B.2)",
+            "parallelism": f"paths sharded over {world} GPU(s); per step one NCCL all-gather of the 2.3 KB aggregate "
+                           "vector + the library's merge kernel"}
+
+
 def cpu_port_run(close, price, solid, params, lr, threads):
     from oracle import c_oracle as CO
     t0 = time.perf_counter()
@@ -215,9 +225,9 @@ def run_reference(args, wl, rank):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wl["workload"], "sample": f"{sample} of {wl['paths']} paths per step"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{sample} paths x {STEPS_PER_PATH} steps per step, oracle/qmmx_oracle.c, pthreads"},
+        "config": headline_config(wl, args.gpus, len(rows)),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "host_cpu": cpu_model(),
+                         "sample": f"{sample} of {wl['paths']} paths x {STEPS_PER_PATH} steps per step, oracle/qmmx_oracle.c, pthreads"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -757,12 +767,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32 bars; f64-exact decisions via fp32 thresholds; f64 PnL sums",
             "data": "synthetic",
-            "config": {"workload": wl["workload"], "paths_per_gpu": paths, "steps_per_path": STEPS_PER_PATH,
-                       "levels": len(rows), "lr_filter": bool(wl["lr"]), "bars": "fp32 close [step][path], resident in HBM",
-                       "l2": "inputs (1.56 GB per GPU) larger than the 126 MB L2; no flush needed",
-                       "policy_gate": "off (DISABLE_POLICY_GATE=1, as in the reference's recorded run, SURVEY B.2)",
-                       "parallelism": f"paths sharded over {world} GPU(s); per step one NCCL all-gather of the 2.3 KB aggregate "
-                                      "vector + the library's merge kernel"},
+            "config": headline_config(wl, world, len(rows)),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (cap or {}).get("dram_bytes") if paths == 1_000_000 else None,
                          "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch (%s)" %
