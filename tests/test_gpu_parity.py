@@ -439,6 +439,13 @@ def test_gpu_full_size_properties(eng):
     eng.gen_gbm(11, 0, P, T, g)
     scan = eng.run_scan()[0].agg
     assert list(scan.entry_hist) == list(a.entry_hist) and list(scan.pnl_hist) == list(a.pnl_hist)
+    # and the oracle itself at the full C2 size: all 1M paths of the resident bars through the C port on every host
+    # thread (~3 s), every counter, both histograms, the PnL histogram and the float64 sums
+    import os
+    bars = eng.download_bars(P, T)[0]
+    o = CO.run_paths(bars, price, solid, params, lr=lr, n_threads=os.cpu_count() or 4)["agg"]
+    assert_agg_equal(scan, o)
+    assert_agg_equal(a, o)
 
 
 @pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
