@@ -50,6 +50,7 @@ struct ScanArgs {
     qmmx_trade* trades; int32_t* tcounts; uint8_t* codes;
     int32_t max_trades, n_days, n_pol, n_levels;
     int32_t cell_obase, cell_shift, cell_ncell;        // grid of the table (tables.h cell_of_bits), as constants
+    uint32_t cell_lim;                                 // (ncell << shift) - 1: cell = min(bits - obase, cell_lim) >> shift (one add-min + one shift)
     float guard[4];                                    // far zones adjoining the grid (tables.h DevTables::guard)
     int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
     unsigned int* tile_counter;                        // scan_tile.cuh: next unclaimed 32-path tile of this launch (zeroed by init_flat_kernel)

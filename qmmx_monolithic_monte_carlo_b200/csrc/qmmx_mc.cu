@@ -238,6 +238,7 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.hist_lo = ctx->hist_lo; A.hist_inv_w = (double)QMMX_PNL_HIST_BINS / (ctx->hist_hi - ctx->hist_lo);
     A.n_levels = ctx->L;
     A.cell_obase = ctx->grids[D.table].obase; A.cell_shift = ctx->grids[D.table].shift; A.cell_ncell = ctx->grids[D.table].ncell;
+    A.cell_lim = ((uint32_t)A.cell_ncell << A.cell_shift) - 1u;
     A.cell_bytes = (int32_t)scan_smem_bytes(ctx);
     for (int g = 0; g < 4; ++g) A.guard[g] = ctx->grids[D.table].guard[g];
     A.combo = D;

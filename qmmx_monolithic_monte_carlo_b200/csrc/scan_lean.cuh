@@ -296,7 +296,7 @@ struct LeanEngine {
         prev = pf;
         if (PARITY && d == 0.f) code = QMMX_DIR_UNKNOWN;
         // nearest level within CONTACT_PROX (M:1543-1545): the cell byte is read by every lane, the branch is taken by few
-        const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase) >> A.cell_shift, (uint32_t)(A.cell_ncell - 1));
+        const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         uint32_t v = lds_u8<Y::kCell>(sb + c);
         if (elig && v != kFar) {
             if (v >= kMixBase) {                                  // the cell straddles a zone boundary
@@ -319,7 +319,7 @@ struct LeanEngine {
 
     // level whose contact zone holds p, or kFar: the cell byte of step(), fully resolved
     __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
-        const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase) >> A.cell_shift, (uint32_t)(A.cell_ncell - 1));
+        const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         uint32_t v = lds_u8<Y::kCell>(sb + c);
         if (v >= kMixBase && v != kFar) {
             if (v == kMixed) {

@@ -98,7 +98,7 @@ struct TileScan {
         }
         E.prev = p;
         dm = __funnelshift_l(__float_as_uint(dcur), dm, 1);
-        const uint32_t c = min((uint32_t)(__float_as_int(p) - A.cell_obase) >> A.cell_shift, (uint32_t)(A.cell_ncell - 1));
+        const uint32_t c = min((uint32_t)(__float_as_int(p) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         const uint32_t v = lds_u8<Y::kCell>(E.sb + c);
         fm = __funnelshift_l((v + 1u) << 23, fm, 1);              // v == kFar (0xff) -> bit 31
     }
