@@ -228,3 +228,33 @@ def test_results_sink_reason_histograms(tmp_path):
     t = pq.read_table(path)
     assert t.num_rows == 3 and t.column("n_trades").to_pylist() == [7, 8, 9]
     assert t.column("sum_pnl").to_pylist() == [0.0, -0.35, -0.7]
+
+
+def test_bench_helpers_on_cpu():
+    """bench.py pieces that need no GPU: both arms print one `config`, the aggregate digest is a function of the integer
+    aggregates only (float64 sums depend on the summation order and stay out), NUMA binding never fails, the committed
+    capture that feeds roofline.binding_limit parses, and the reference arm prints a well-formed line."""
+    import importlib
+    import json
+    import subprocess
+    import sys
+    bench = importlib.import_module("bench")
+    wl = bench.workload("c2")
+    assert bench.headline_config(wl, 4, 30) == bench.headline_config(dict(wl), 4, 30)
+    a, b = abi.Agg(), abi.Agg()
+    for x in (a, b):
+        x.n_paths, x.n_trades = 10, 7
+        x.entry_hist[5], x.pnl_hist[128] = 3900, 10
+    a.sum_pnl, b.sum_pnl = 1.25, 1.2500000001
+    from qmmx_monolithic_monte_carlo_b200 import engine as E
+    assert bench.agg_digest([E.MCResult(a)]) == bench.agg_digest([E.MCResult(b)])
+    b.entry_hist[5] += 1
+    assert bench.agg_digest([E.MCResult(a)]) != bench.agg_digest([E.MCResult(b)])
+    assert isinstance(bench.bind_numa(0, 1), dict) and isinstance(bench.bind_numa(3, 8), dict)
+    cap = bench.shipped_capture()
+    assert cap and cap["kernel"].startswith("void tile_scan_tma_kernel") and 0 < cap["issue_active_pct"] <= 100
+    out = subprocess.run([sys.executable, "bench.py", "--impl", "reference", "--steps", "1", "--warmup", "1", "--paths", "4096"],
+                         capture_output=True, text=True, timeout=300, cwd=bench.ROOT)
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["value"] > 0 and line["cpu_baseline"]["kind"] == "port"
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["config"]["workload"].startswith("C2")
