@@ -37,13 +37,18 @@ __device__ __forceinline__ uint4 philox4x32_10_rk(uint4 c, const uint32_t (&rk)[
     return c;
 }
 
-__device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// MUFU forms without the denormal guards nvcc wraps around __logf / sqrtf / __expf (scale by 2^24, test, rescale: 3 extra
+// instructions each).  The arguments here are never denormal: u1 >= 1.2e-10, -2 ln u1 is 0 or >= 2.4e-7, and the
+// exponent of a GBM step is ~1e-3; for normal arguments the results are bit-identical to the guarded forms.
+__device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float lg2_approx(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // Box-Muller on two 32-bit draws (same operation order as oracle/qmmx_oracle.c; MUFU transcendentals, square root included)
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
     const float u1 = __fmul_rn(__fadd_rn(__uint2float_rn(a), 0.5f), 2.3283064365386963e-10f);
     const float u2 = __fmul_rn(__fadd_rn(__uint2float_rn(b >> 8), 0.5f), 5.9604644775390625e-08f);
-    const float r = sqrt_approx(__fmul_rn(-2.0f, __logf(u1)));
+    const float r = sqrt_approx(__fmul_rn(-2.0f, __fmul_rn(lg2_approx(u1), 0.693147182464599609375f)));      // __logf = lg2 * ln 2
     const float ang = __fsub_rn(__fmul_rn(u2, 6.28318530717958648f), 3.14159265358979324f);
     float s, c;
     __sincosf(ang, &s, &c);
@@ -66,7 +71,7 @@ __device__ __forceinline__ void gbm_normals(const GbmDev& g, uint64_t gid, uint3
     box_muller(x.z, x.w, z[2], z[3]);
 }
 __device__ __forceinline__ float gbm_advance(const GbmDev& g, float S, float z) {
-    return __fmul_rn(S, __expf(__fadd_rn(g.drift, __fmul_rn(g.vol, z))));
+    return __fmul_rn(S, ex2_approx(__fmul_rn(__fadd_rn(g.drift, __fmul_rn(g.vol, z)), 1.44269502162933349609375f)));   // __expf = ex2(x * log2 e)
 }
 
 // warp-uniform day counter: day_off = min(step / steps_per_day, n_days - 1) * kMaxLevels without a division per step
