@@ -474,9 +474,9 @@ void oq_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out
 
 /* Box-Muller on two 32-bit draws; same operation order as the device code, libm transcendentals */
 static void box_muller(uint32_t a, uint32_t b, float* z0, float* z1) {
-    const float u1 = ((float)a + 0.5f) * 2.3283064365386963e-10f;          /* (0, 1] */
-    const float u2 = ((float)(b >> 8) + 0.5f) * 5.9604644775390625e-08f;   /* (0, 1) */
-    const float r = sqrtf(-2.0f * logf(u1));
+    const float u1 = fmaf((float)a, 2.3283064365386963e-10f, 1.16415321826934814453125e-10f);          /* (a + 0.5) 2^-32, (0, 1] */
+    const float u2 = fmaf((float)(b >> 8), 5.9604644775390625e-08f, 2.98023223876953125e-08f);          /* (0, 1) */
+    const float r = sqrtf(log2f(u1) * -1.38629436111989061883f);           /* -2 ln u1 = (-2 ln 2) lg2 u1 */
     const float ang = u2 * 6.28318530717958648f - 3.14159265358979324f;
     *z0 = r * cosf(ang); *z1 = r * sinf(ang);
 }
@@ -489,6 +489,8 @@ int oq_gen_gbm(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps
     const float drift = (float)(((double)g->mu_annual - 0.5 * (double)g->sigma_annual * (double)g->sigma_annual)
                                 * (double)g->dt_years / (double)g->sub_steps);
     const float vol = (float)((double)g->sigma_annual * sqrt((double)g->dt_years / (double)g->sub_steps));
+    /* the step in base 2, as the device takes it: S *= 2^(vol2 * z + drift2), one fused multiply-add */
+    const float drift2 = (float)((double)drift * 1.4426950408889634074), vol2 = (float)((double)vol * 1.4426950408889634074);
     const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     const int cents = (g->flags & QMMX_GBM_ROUND_CENTS) != 0;
     if (g->sub_steps != 1 && g->sub_steps != 4) return -1;
@@ -506,12 +508,12 @@ int oq_gen_gbm(uint64_t seed, uint64_t path_offset, int64_t paths, int32_t steps
                 box_muller(x[2], x[3], &z[2], &z[3]);
             }
             if (g->sub_steps == 1) {
-                S = S * expf(drift + vol * z[i & 3]);
+                S = S * exp2f(fmaf(vol2, z[i & 3], drift2));
                 close[(int64_t)i * paths + q] = cents ? round_cents(S) : S;
             } else {
                 float hi = S, lo = S;
                 for (int s = 0; s < 4; ++s) {
-                    S = S * expf(drift + vol * z[s]);
+                    S = S * exp2f(fmaf(vol2, z[s], drift2));
                     hi = fmaxf(hi, S); lo = fminf(lo, S);
                 }
                 close[(int64_t)i * paths + q] = cents ? round_cents(S) : S;

@@ -46,9 +46,10 @@ __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.
 
 // Box-Muller on two 32-bit draws (same operation order as oracle/qmmx_oracle.c; MUFU transcendentals, square root included)
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
-    const float u1 = __fmul_rn(__fadd_rn(__uint2float_rn(a), 0.5f), 2.3283064365386963e-10f);
-    const float u2 = __fmul_rn(__fadd_rn(__uint2float_rn(b >> 8), 0.5f), 5.9604644775390625e-08f);
-    const float r = sqrt_approx(__fmul_rn(-2.0f, __fmul_rn(lg2_approx(u1), 0.693147182464599609375f)));      // __logf = lg2 * ln 2
+    // (x + 0.5) * 2^-k as one fused multiply-add; -2 ln u1 = (-2 ln 2) lg2 u1 as one multiply (oracle: the same forms)
+    const float u1 = __fmaf_rn(__uint2float_rn(a), 2.3283064365386963e-10f, 1.16415321826934814453125e-10f);
+    const float u2 = __fmaf_rn(__uint2float_rn(b >> 8), 5.9604644775390625e-08f, 2.98023223876953125e-08f);
+    const float r = sqrt_approx(__fmul_rn(lg2_approx(u1), -1.38629436111989061883f));
     const float ang = __fsub_rn(__fmul_rn(u2, 6.28318530717958648f), 3.14159265358979324f);
     float s, c;
     __sincosf(ang, &s, &c);
@@ -56,7 +57,8 @@ __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, fl
 }
 
 struct GbmDev {
-    float s0, drift, vol;       // per sub-step log-drift and volatility
+    float s0, drift, vol;       // per sub-step log-drift and volatility; drift2 / vol2 = the same in base 2 (times log2 e):
+    float drift2, vol2;         // S *= 2^(vol2 * z + drift2), one fused multiply-add + MUFU.EX2 + one multiply per step
     int32_t sub_steps, cents;
     uint32_t k0, k1;
     uint64_t path_offset;
@@ -71,7 +73,7 @@ __device__ __forceinline__ void gbm_normals(const GbmDev& g, uint64_t gid, uint3
     box_muller(x.z, x.w, z[2], z[3]);
 }
 __device__ __forceinline__ float gbm_advance(const GbmDev& g, float S, float z) {
-    return __fmul_rn(S, ex2_approx(__fmul_rn(__fadd_rn(g.drift, __fmul_rn(g.vol, z)), 1.44269502162933349609375f)));   // __expf = ex2(x * log2 e)
+    return __fmul_rn(S, ex2_approx(__fmaf_rn(g.vol2, z, g.drift2)));
 }
 
 // warp-uniform day counter: day_off = min(step / steps_per_day, n_days - 1) * kMaxLevels without a division per step

@@ -541,6 +541,7 @@ GbmDev make_gbm(const qmmx_gbm* g, uint64_t seed, uint64_t path_offset) {
     d.drift = (float)(((double)g->mu_annual - 0.5 * (double)g->sigma_annual * (double)g->sigma_annual) *
                       (double)g->dt_years / (double)g->sub_steps);
     d.vol = (float)((double)g->sigma_annual * std::sqrt((double)g->dt_years / (double)g->sub_steps));
+    d.drift2 = (float)((double)d.drift * 1.4426950408889634074); d.vol2 = (float)((double)d.vol * 1.4426950408889634074);
     d.sub_steps = g->sub_steps; d.cents = (g->flags & QMMX_GBM_ROUND_CENTS) ? 1 : 0;
     d.k0 = (uint32_t)seed; d.k1 = (uint32_t)(seed >> 32); d.path_offset = path_offset;
     for (uint32_t r = 0; r < 10; ++r) { d.rk[2 * r] = d.k0 + r * 0x9E3779B9u; d.rk[2 * r + 1] = d.k1 + r * 0xBB67AE85u; }
