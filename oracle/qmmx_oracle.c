@@ -475,10 +475,10 @@ void oq_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out
 /* Box-Muller on two 32-bit draws; same operation order as the device code, libm transcendentals */
 static void box_muller(uint32_t a, uint32_t b, float* z0, float* z1) {
     const float u1 = fmaf((float)a, 2.3283064365386963e-10f, 1.16415321826934814453125e-10f);          /* (a + 0.5) 2^-32, (0, 1] */
-    const float u2 = fmaf((float)(b >> 8), 5.9604644775390625e-08f, 2.98023223876953125e-08f);          /* (0, 1) */
     const float r = sqrtf(log2f(u1) * -1.38629436111989061883f);           /* -2 ln u1 = (-2 ln 2) lg2 u1 */
-    const float ang = u2 * 6.28318530717958648f - 3.14159265358979324f;
-    *z0 = r * cosf(ang); *z1 = r * sinf(ang);
+    /* angle 2 pi u2 - pi, u2 = (b' + 0.5) 2^-24 in (0, 1): the half turn is taken as a sign, as the device does */
+    const float ang = fmaf((float)(b >> 8), 3.7450702829239286e-07f, 1.8725351414619643e-07f);
+    *z0 = -r * cosf(ang); *z1 = -r * sinf(ang);
 }
 
 static float round_cents(float s) { return rintf(s * 100.0f) / 100.0f; }

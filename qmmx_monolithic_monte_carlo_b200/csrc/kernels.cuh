@@ -48,12 +48,13 @@ __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
     // (x + 0.5) * 2^-k as one fused multiply-add; -2 ln u1 = (-2 ln 2) lg2 u1 as one multiply (oracle: the same forms)
     const float u1 = __fmaf_rn(__uint2float_rn(a), 2.3283064365386963e-10f, 1.16415321826934814453125e-10f);
-    const float u2 = __fmaf_rn(__uint2float_rn(b >> 8), 5.9604644775390625e-08f, 2.98023223876953125e-08f);
     const float r = sqrt_approx(__fmul_rn(lg2_approx(u1), -1.38629436111989061883f));
-    const float ang = __fsub_rn(__fmul_rn(u2, 6.28318530717958648f), 3.14159265358979324f);
+    // angle = 2 pi u2 - pi with u2 = (b' + 0.5) 2^-24: the half turn is a sign (sin(x - pi) = -sin x, cos(x - pi) = -cos x), so
+    // the angle is ONE fused multiply-add from the draw and the sign rides on r
+    const float ang = __fmaf_rn(__uint2float_rn(b >> 8), 3.7450702829239286e-07f, 1.8725351414619643e-07f);   // 2 pi 2^-24, pi 2^-24
     float s, c;
     __sincosf(ang, &s, &c);
-    z0 = __fmul_rn(r, c); z1 = __fmul_rn(r, s);
+    z0 = __fmul_rn(-r, c); z1 = __fmul_rn(-r, s);
 }
 
 struct GbmDev {
