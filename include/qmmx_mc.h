@@ -308,6 +308,23 @@ int  qmmx_run_last_bars(qmmx_ctx* ctx, const double* high, const double* low, in
                         const int32_t* cand_bar, const uint8_t* cand_side, const double* cand_stop,
                         const double* cand_target, int32_t n_cand, int32_t* out_outcome, int32_t* out_exit_bar);
 
+/* qmmx_run_last_bars without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results and the same kernel as qmmx_run_last_bars; the device copy of
+ * the bars and candidates and the two result arrays live in ONE file-scope `static __device__` array of 1 MiB inside the
+ * library (every GPU that loads the library holds it until the process exits) instead of a cudaMalloc'ed arena.
+ * Limits: n_bars <= QMMX_STATIC_MAX_BARS and n_cand <= QMMX_STATIC_MAX_CAND, beyond them QMMX_E_UNSUPPORTED with the
+ * limits in qmmx_last_error (use qmmx_run_last_bars).  The call makes no cudaMalloc / cudaFree / allocating library
+ * call; the ctx (qmmx_create resolves the array's device address once per device) must exist beforehand.
+ * The array is shared by EVERY ctx and call on a device and keeps the last call's contents; nothing in it has to start
+ * at zero (each call overwrites its inputs and writes both outputs of every candidate).  Calls that overlap on one GPU
+ * (two ctxs, two threads, two streams) race on it: serialise them. */
+#define QMMX_STATIC_MAX_BARS 12000
+#define QMMX_STATIC_MAX_CAND 16384
+int  qmmx_run_last_bars_static(qmmx_ctx* ctx, const double* high, const double* low, int32_t n_bars,
+                               const int32_t* cand_bar, const uint8_t* cand_side, const double* cand_stop,
+                               const double* cand_target, int32_t n_cand, int32_t* out_outcome, int32_t* out_exit_bar);
+
 /* Host-side check of the exact price-classification tables the kernels use (no device needed):
  * for each fp32 price, level_table/level_brute = touched level by table lookup / by the float64 brute force
  * of M:1543-1545 (-1 = TOO_FAR); conf_mask bit b = confidence gate passes for touch bucket b (tc<=1, 2, >=3)

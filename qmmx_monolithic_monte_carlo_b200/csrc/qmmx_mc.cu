@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -68,6 +69,9 @@ struct qmmx_ctx {
     // NCCL through dlopen (qmmx_allreduce)
     void* nccl_comm = nullptr;             // communicator made by qmmx_nccl_init (owned)
     unsigned long long* d_gather = nullptr; size_t gather_slots = 0;
+    // qmmx_run_last_bars_static: device address of g_static_scratch on this ctx's device (resolved in qmmx_create)
+    uint8_t* static_scratch = nullptr;
+    cudaError_t static_scratch_err = cudaErrorUnknown;
 };
 
 namespace {
@@ -556,6 +560,38 @@ int check_gbm(qmmx_ctx* ctx, const qmmx_gbm* g) {
 
 }  // namespace
 
+// ---- scratch of qmmx_run_last_bars_static: a file-scope device array, so that the entry point allocates nothing.
+// Every GPU that loads the library holds these kStaticScratchBytes until the process exits.  In HOST code the name
+// g_static_scratch is a host-side stand-in, not a device address: kernels get the pointer cudaGetSymbolAddress returns.
+constexpr size_t kStaticScratchBytes = (size_t)1 << 20;
+constexpr int kStaticMaxBars = QMMX_STATIC_MAX_BARS, kStaticMaxCand = QMMX_STATIC_MAX_CAND;
+constexpr size_t static_last_bars_bytes(size_t nb, size_t nk) { return (2 * nb + 2 * nk) * 8 + 3 * nk * 4 + nk; }
+static_assert(static_last_bars_bytes(kStaticMaxBars, kStaticMaxCand) <= kStaticScratchBytes, "static scratch too small for the stated maxima");
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static uint8_t* g_static_ptr[kStaticMaxDevices];
+static cudaError_t g_static_err[kStaticMaxDevices];
+static bool g_static_known[kStaticMaxDevices];
+
+// once per device, with that device current (qmmx_create has just made it so)
+static cudaError_t static_scratch_address(int device, uint8_t** out) {
+    *out = nullptr;
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_known[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) { cudaGetLastError(); p = nullptr; }
+        g_static_ptr[device] = static_cast<uint8_t*>(p);
+        g_static_err[device] = e;
+        g_static_known[device] = true;
+    }
+    *out = g_static_ptr[device];
+    return g_static_err[device];
+}
+
 #define ENTER(c)                                                         \
     if (!(c)) return QMMX_E_BADARG;                                      \
     qmmx_ctx* ctx = (c);                                                 \
@@ -614,6 +650,7 @@ int qmmx_create(int device, qmmx_ctx** out) {
     }
     ctx->z_go = sigmoid_threshold(0.60);     // M:3083-3085
     ctx->z_skip = sigmoid_threshold(0.55);
+    ctx->static_scratch_err = static_scratch_address(device, &ctx->static_scratch);   // only qmmx_run_last_bars_static needs it
     *out = ctx;
     return QMMX_OK;
 }
@@ -1374,6 +1411,52 @@ int qmmx_run_last_bars(qmmx_ctx* c, const double* high, const double* low, int32
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(arena);
     if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("run_last_bars: ") + cudaGetErrorString(e));
+    ctx->ran = true;
+    return QMMX_OK;
+}
+
+int qmmx_run_last_bars_static(qmmx_ctx* c, const double* high, const double* low, int32_t n_bars, const int32_t* cand_bar,
+                              const uint8_t* cand_side, const double* cand_stop, const double* cand_target,
+                              int32_t n_cand, int32_t* out_outcome, int32_t* out_exit_bar) {
+    ENTER(c);
+    if (!high || !low || n_bars < 1 || n_cand < 0 ||
+        (n_cand > 0 && (!cand_bar || !cand_side || !cand_stop || !cand_target || !out_outcome || !out_exit_bar)))
+        return fail(ctx, QMMX_E_BADARG, "run_last_bars_static: bad arguments");
+    if (n_bars > kStaticMaxBars || n_cand > kStaticMaxCand)
+        return fail(ctx, QMMX_E_UNSUPPORTED, "run_last_bars_static: n_bars " + std::to_string(n_bars) + " / n_cand " + std::to_string(n_cand) +
+                    " beyond the static scratch (QMMX_STATIC_MAX_BARS " + std::to_string(kStaticMaxBars) + ", QMMX_STATIC_MAX_CAND " +
+                    std::to_string(kStaticMaxCand) + "): use qmmx_run_last_bars");
+    if (ctx->static_scratch_err != cudaSuccess || !ctx->static_scratch)
+        return fail(ctx, QMMX_E_CUDA, std::string("run_last_bars_static: cudaGetSymbolAddress(g_static_scratch): ") +
+                    cudaGetErrorString(ctx->static_scratch_err));
+    if (n_cand == 0) return QMMX_OK;
+    const size_t nb = (size_t)n_bars, nk = (size_t)n_cand;
+    // same layout as qmmx_run_last_bars' arena, inside the shared array: f64 high, low, stop, target | i32 bar, outcome,
+    // exit_bar | u8 side.  Nothing has to start at zero: the inputs are overwritten here and the kernel writes both
+    // outputs of every candidate, so what the previous call left behind is never read.
+    double* d64 = reinterpret_cast<double*>(ctx->static_scratch);
+    int32_t* i32 = reinterpret_cast<int32_t*>(ctx->static_scratch + (2 * nb + 2 * nk) * 8);
+    uint8_t* u8 = reinterpret_cast<uint8_t*>(i32 + 3 * nk);
+    cudaError_t e = cudaSuccess;
+    auto up = [&](const void* src, void* dst, size_t n) {
+        if (e == cudaSuccess && n) e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream);
+    };
+    up(high, d64, nb * 8); up(low, d64 + nb, nb * 8);
+    up(cand_stop, d64 + 2 * nb, nk * 8); up(cand_target, d64 + 2 * nb + nk, nk * 8);
+    up(cand_bar, i32, nk * 4); up(cand_side, u8, nk);
+    if (e == cudaSuccess) {
+        const int64_t blocks = std::min<int64_t>((nk * 32 + kThreads - 1) / kThreads, (int64_t)ctx->sm_count * 8);
+        cudaEventRecord(ctx->ev0, ctx->stream);
+        last_bars_kernel<<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(d64, d64 + nb, n_bars, i32, u8, d64 + 2 * nb,
+                                                                         d64 + 2 * nb + nk, n_cand, i32 + nk, i32 + 2 * nk);
+        ctx->launches++;
+        e = cudaGetLastError();
+        cudaEventRecord(ctx->ev1, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_outcome, i32 + nk, nk * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_exit_bar, i32 + 2 * nk, nk * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) return fail(ctx, QMMX_E_CUDA, std::string("run_last_bars_static: ") + cudaGetErrorString(e));
     ctx->ran = true;
     return QMMX_OK;
 }

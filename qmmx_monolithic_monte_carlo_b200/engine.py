@@ -81,6 +81,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_run_jitter": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, dbl, dbl, vp, i64, u64, u64,
                                       vp, vp, vp, vp, vp, vp, vp]),
         "qmmx_run_last_bars": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp]),
+        "qmmx_run_last_bars_static": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp]),
         "qmmx_debug_classify": (C.c_int, [vp, vp, C.c_int, dbl, dbl, vp, i64, vp, vp, vp, vp, vp, vp]),
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
@@ -435,6 +436,20 @@ class MCEngine:
         oc = np.full(len(cands), 2, dtype=np.int32); xb = np.full(len(cands), -1, dtype=np.int32)
         self._ck(self._L.qmmx_run_last_bars(self._h, _ptr(high), _ptr(low), len(high), _ptr(cb), _ptr(cs), _ptr(st),
                                             _ptr(tg), len(cands), _ptr(oc), _ptr(xb)))
+        return oc, xb
+
+    def run_last_bars_static(self, high, low, cands):
+        """`run_last_bars` through `qmmx_run_last_bars_static`: no device allocation, scratch in the library's static
+        1 MiB device array (len(high) <= 12000, len(cands) <= 16384; no reference counterpart, see include/qmmx_mc.h)."""
+        high = np.ascontiguousarray(high, dtype=np.float64)
+        low = np.ascontiguousarray(low, dtype=np.float64)
+        cb = np.array([c["i"] for c in cands], dtype=np.int32)
+        cs = np.array([c["side"] for c in cands], dtype=np.uint8)
+        st = np.array([c["stop"] for c in cands], dtype=np.float64)
+        tg = np.array([c["target"] for c in cands], dtype=np.float64)
+        oc = np.full(len(cands), 2, dtype=np.int32); xb = np.full(len(cands), -1, dtype=np.int32)
+        self._ck(self._L.qmmx_run_last_bars_static(self._h, _ptr(high), _ptr(low), len(high), _ptr(cb), _ptr(cs), _ptr(st),
+                                                   _ptr(tg), len(cands), _ptr(oc), _ptr(xb)))
         return oc, xb
 
     def last_timing_ms(self) -> float:
