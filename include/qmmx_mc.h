@@ -329,10 +329,18 @@ int  qmmx_run_last_bars_static(qmmx_ctx* ctx, const double* high, const double* 
  * for each fp32 price, level_table/level_brute = touched level by table lookup / by the float64 brute force
  * of M:1543-1545 (-1 = TOO_FAR); conf_mask bit b = confidence gate passes for touch bucket b (tc<=1, 2, >=3)
  * by threshold compare, conf_brute = the same by float64 compute_confidence; near_table/near_brute = bit j set
- * when p is inside level j's contact window (|price_j - p| <= prox). Any output may be NULL. */
+ * when p is inside level j's contact window (|price_j - p| <= prox). Any output may be NULL.
+ * near_table comes from the CLASS partition the lean / tile kernels read (one record per price class = touched level +
+ * the levels whose window holds the price: the latch release of M:1572-1576 as one AND) whenever the level set has one;
+ * a class level that differs from level_table is reported as level_table = -100. */
 int  qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
                          const float* p, int64_t n, int32_t* level_table, int32_t* level_brute,
                          uint8_t* conf_mask, uint8_t* conf_brute, uint64_t* near_table, uint64_t* near_brute);
+
+/* Sizes of the class partition of a level set (host only): classes, runs along the fp32 line, single-boundary records.
+ * n_classes = -1: the set needs more than 254 classes or 640 runs and the first-generation kernels run instead. */
+int  qmmx_debug_class_partition(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
+                                int32_t* n_classes, int32_t* n_runs, int32_t* n_records);
 
 /* device time of the last run's kernels in ms (CUDA events on the ctx stream) */
 int  qmmx_last_timing(qmmx_ctx* ctx, float* ms);

@@ -52,6 +52,7 @@ struct ScanArgs {
     int32_t cell_obase, cell_shift, cell_ncell;        // grid of the table (tables.h cell_of_bits), as constants
     uint32_t cell_lim;                                 // (ncell << shift) - 1: cell = min(bits - obase, cell_lim) >> shift (one add-min + one shift)
     float guard[4];                                    // far zones adjoining the grid (tables.h DevTables::guard)
+    uint32_t mix_base;                                 // class partition: cell bytes >= mix_base are not class ids (tables.h DevTables::ncls)
     int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
     unsigned int* tile_counter;                        // scan_tile.cuh: next unclaimed 32-path tile of this launch (zeroed by init_flat_kernel)
     DevCombo combo;
@@ -533,7 +534,8 @@ __device__ __noinline__ void warp_accumulate(bool active, double pnl, double pnl
 }
 
 // per-CTA setup: zero the aggregate and build the shared tables from DevTables + this launch's combo
-__device__ inline void block_setup(const ScanArgs& A) {
+// fine = the class partition (lean / tile kernels): cell bytes, zone list and zone values are class ids
+__device__ inline void block_setup(const ScanArgs& A, bool fine = false) {
     BlockShared& S = g_S;
     const DevTables* __restrict__ T = A.tables;
     const double neg_inf = __longlong_as_double((long long)0xfff0000000000000ull);
@@ -542,7 +544,7 @@ __device__ inline void block_setup(const ScanArgs& A) {
     if (threadIdx.x < QMMX_AGG_ND) S.d[threadIdx.x] = 0.0;
     if (threadIdx.x == 0) {
         S.xmax = neg_inf; S.xnegmin = neg_inf;
-        S.L = T->L; S.Z = T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
+        S.L = T->L; S.Z = fine ? T->FZ : T->Z; S.ncell = T->ncell; S.shift = T->shift; S.obase = T->obase;
     }
     for (int k = threadIdx.x; k < kMaxLevels; k += blockDim.x) {
         const DevLevel D = T->lev[k];
@@ -556,9 +558,11 @@ __device__ inline void block_setup(const ScanArgs& A) {
         ColdLevel Cl; Cl.price = D.price; Cl.wlo = D.wlo; Cl.whi = D.whi; Cl.flags = D.flags; Cl.pad = 0u;
         S.cold[k] = Cl;
     }
-    for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) { S.zhi[t] = T->zhi[t]; S.zlev[t] = T->zlev[t]; }
+    for (int t = threadIdx.x; t < kMaxZones; t += blockDim.x) {
+        S.zhi[t] = fine ? T->fzhi[t] : T->zhi[t]; S.zlev[t] = fine ? T->fzcls[t] : T->zlev[t];
+    }
     const int n16 = (T->ncell + 15) / 16;
-    const uint4* src = reinterpret_cast<const uint4*>(T->cell);
+    const uint4* src = reinterpret_cast<const uint4*>(fine ? T->fcell : T->cell);
     uint4* dst = reinterpret_cast<uint4*>(g_cell);
     for (int t = threadIdx.x; t < n16; t += blockDim.x) dst[t] = src[t];
     __syncthreads();

@@ -38,7 +38,7 @@ struct qmmx_ctx {
     bool dirty = true;
     // derived device state
     DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
-    struct CellGrid { int32_t obase, shift, ncell; float guard[4]; };
+    struct CellGrid { int32_t obase, shift, ncell; float guard[4]; int32_t ncls; };
     std::vector<CellGrid> grids;
     std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
@@ -181,8 +181,9 @@ int prepare(qmmx_ctx* ctx) {
     ctx->n_tables = (int)tabs.size();
     ctx->max_ncell = 1;
     ctx->grids.clear();
-    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell, {t.guard[0], t.guard[1], t.guard[2], t.guard[3]}}); }
+    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell, {t.guard[0], t.guard[1], t.guard[2], t.guard[3]}, t.ncls}); }
     ctx->lean_ok = true;       // every non-empty confidence interval must have a positive upper bound (sign encoding)
+    for (auto& t : tabs) if (t.ncls < 0) ctx->lean_ok = false;      // and the class partition must fit one byte (tables.h)
     for (auto& t : tabs)
         for (int k = 0; k < t.L; ++k)
             for (int b = 0; b < 3; ++b)
@@ -245,6 +246,7 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.cell_lim = ((uint32_t)A.cell_ncell << A.cell_shift) - 1u;
     A.cell_bytes = (int32_t)scan_smem_bytes(ctx);
     for (int g = 0; g < 4; ++g) A.guard[g] = ctx->grids[D.table].guard[g];
+    A.mix_base = (uint32_t)std::max(0, ctx->grids[D.table].ncls);
     A.combo = D;
 }
 
@@ -1487,9 +1489,29 @@ int qmmx_debug_classify(const double* price, const uint8_t* solid, int n_levels,
             if (pf >= T[0].lev[j].wlo && pf <= T[0].lev[j].whi) nt |= 1ull << j;
             if (!(std::fabs(price[j] - (double)pf) > prox)) nbm |= 1ull << j;
         }
+        if (T[0].ncls >= 0) {
+            // the class partition of the lean / tile kernels: its level must be the level table's, and its window mask is what
+            // near_table reports (the mask of a far price is empty, as is the set of windows that hold it)
+            uint64_t cm = 0;
+            const int kf = classify_tables_fine(&T[0], pf, &cm);
+            if (kf != kt && level_table) level_table[i] = -100;
+            nt = cm;
+        }
         if (near_table) near_table[i] = nt;
         if (near_brute) near_brute[i] = nbm;
     }
+    return QMMX_OK;
+}
+
+int qmmx_debug_class_partition(const double* price, const uint8_t* solid, int n_levels, double prox, double qmin,
+                               int32_t* n_classes, int32_t* n_runs, int32_t* n_records) {
+    if (n_levels < 0 || n_levels > QMMX_MAX_LEVELS) return QMMX_E_BADARG;
+    std::vector<DevTables> T(1);
+    std::string e;
+    if (build_tables(n_levels, price, solid, prox, qmin, &T[0], &e) != 0) return QMMX_E_UNSUPPORTED;
+    if (n_classes) *n_classes = T[0].ncls;
+    if (n_runs) *n_runs = T[0].FZ;
+    if (n_records) *n_records = T[0].fnmixed;
     return QMMX_OK;
 }
 

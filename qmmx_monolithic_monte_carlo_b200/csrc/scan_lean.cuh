@@ -45,15 +45,17 @@ struct LeanLayout {
     static constexpr int kCell = 0;                                  // uint8 [kMaxCells]
     static constexpr int kGate = kCell + kMaxCells;                  // float4 [LPAD][2][16]: {lo, +-hi, exit-low, exit-high}
     static constexpr int kTouch = kGate + LPAD * 32 * 16;            // uint8 [LPAD][kTouchStride]
-    static constexpr int kWin = kTouch + LPAD * kTouchStride;        // float2 [LPAD]: contact window {wlo, whi}
-    static constexpr int kCand = kWin + LPAD * 8;                    // uint64 [LPAD]: levels whose window overlaps
-    static constexpr int kPrice = kCand + LPAD * 8;                  // double [LPAD]
-    static constexpr int kMix = kPrice + LPAD * 8;                   // {float bound, uint32 lo | hi << 8} [kMaxMixed]
-    static constexpr int kMask = kMix + kMaxMixed * 8;               // uint32 [kSmemDays][LPAD]: per-day logistic masks (MULTIDAY)
+    static constexpr int kPrice = kTouch + LPAD * kTouchStride;      // double [LPAD]
+    // one record per cell-byte value v (tables.h, class partition), kRecShift = log2 of its size:
+    //   v < mix_base: class  {level touched, levels whose contact window holds p (32 bits; 64 bits in .z/.w when LPAD = 64)}
+    //   else:         single-boundary cell {float bound, uint32 lo | hi << 8}: p <= bound ? lo : hi (class ids or kFar)
+    static constexpr int kRecShift = LPAD > 32 ? 4 : 3;
+    static constexpr int kRec = kPrice + LPAD * 8;
+    static constexpr int kMask = kRec + (256 << kRecShift);          // uint32 [kSmemDays][LPAD]: per-day logistic masks (MULTIDAY)
     static constexpr int kEnd = kMask + kSmemDays * LPAD * 4;
     static constexpr int kBoot = kEnd;                               // float [3][kMaxWindow]: bootstrap return ratios (fused bootstrap only)
     static constexpr int kEndBoot = kBoot + 3 * kMaxWindow * 4;
-    static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kWin % 8 == 0 && kMix % 8 == 0, "alignment");
+    static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kPrice % 8 == 0 && kRec % 16 == 0, "alignment");
 };
 inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
 
@@ -84,6 +86,9 @@ QMMX_LDS(float, f32, "f", 4)
 template <int OFF> __device__ __forceinline__ float2 lds_f2(uint32_t a) {
     smem_chk(a + OFF, 8);
     float2 v; asm("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(a), "n"(OFF)); return v; }
+template <int OFF> __device__ __forceinline__ uint4 lds_u4(uint32_t a) {
+    smem_chk(a + OFF, 16);
+    uint4 v; asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4+%5];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a), "n"(OFF)); return v; }
 template <int OFF> __device__ __forceinline__ float4 lds_f4(uint32_t a) {
     smem_chk(a + OFF, 16);
     float4 v; asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a), "n"(OFF)); return v; }
@@ -120,24 +125,19 @@ __device__ inline void lean_setup(const ScanArgs& A) {
         }
         gate[t] = g;
     }
-    float2* win = reinterpret_cast<float2*>(g_cell + Y::kWin);
-    unsigned long long* cand = reinterpret_cast<unsigned long long*>(g_cell + Y::kCand);
     double* price = reinterpret_cast<double*>(g_cell + Y::kPrice);
-    for (int k = threadIdx.x; k < LPAD; k += blockDim.x) {
-        const bool in = k < A.n_levels;
-        win[k] = in ? make_float2(T->lev[k].wlo, T->lev[k].whi) : make_float2(inf, -inf);
-        cand[k] = in ? (((unsigned long long)T->lev[k].cand_hi << 32) | T->lev[k].cand_lo) : 0ull;
-        price[k] = in ? T->lev[k].price : 0.0;
+    for (int k = threadIdx.x; k < LPAD; k += blockDim.x) price[k] = k < A.n_levels ? T->lev[k].price : 0.0;
+    for (int v = threadIdx.x; v < 256; v += blockDim.x) {
+        uint4 r = make_uint4(0u, 0u, 0u, 0u);
+        if (v < T->ncls) r = make_uint4(T->cls_lev[v], T->cls_mask_lo[v], T->cls_mask_lo[v], T->cls_mask_hi[v]);
+        else if (v < T->ncls + T->fnmixed) r.x = (uint32_t)__float_as_int(T->fmixb[v]), r.y = (uint32_t)T->fmixlo[v] | ((uint32_t)T->fmixhi[v] << 8);
+        else r.y = (uint32_t)kFar | ((uint32_t)kFar << 8);
+        if (LPAD > 32) reinterpret_cast<uint4*>(g_cell + Y::kRec)[v] = r;
+        else reinterpret_cast<uint2*>(g_cell + Y::kRec)[v] = make_uint2(r.x, r.y);
     }
     if (MULTIDAY && A.mlmask && A.n_days <= kSmemDays) {
         uint32_t* mk = reinterpret_cast<uint32_t*>(g_cell + Y::kMask);
         for (int t = threadIdx.x; t < A.n_days * LPAD; t += blockDim.x) mk[t] = A.mlmask[(t / LPAD) * kMaxLevels + (t % LPAD)];
-    }
-    uint2* mix = reinterpret_cast<uint2*>(g_cell + Y::kMix);
-    for (int m = threadIdx.x; m < kMaxMixed; m += blockDim.x) {
-        const bool in = m < T->nmixed;
-        mix[m] = in ? make_uint2((uint32_t)__float_as_int(T->mixb[m]), (uint32_t)T->mixlo[m] | ((uint32_t)T->mixhi[m] << 8))
-                    : make_uint2(0u, (uint32_t)kFar | ((uint32_t)kFar << 8));
     }
 }
 
@@ -226,20 +226,23 @@ struct LeanEngine {
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
     }
 
+    // cls: class id of the price (tables.h): the level touched and the levels whose contact window holds it.
     // side: M:1645, up -> long (0), down -> short (1)
-    __device__ __forceinline__ int contact(const ScanArgs& A, int k, float pf, int i, int day_off, int side) {
-        // latch + touch count (M:1562-1576)
-        const latch_t bit = (latch_t)1 << k;
-        const latch_t cand = WIDE ? (latch_t)lds_u64<Y::kCand>(sb + k * 8) : (latch_t)lds_u32<Y::kCand>(sb + k * 8);
-        const bool isnew = (latch & bit) == 0;
-        latch_t keep = latch & cand;
-        latch = bit;
-        while (keep) {      // a latched neighbour stays latched only while p is still inside its own window (M:1572-1576)
-            const int j = WIDE ? __ffsll((long long)keep) - 1 : __ffs((int)keep) - 1;
-            keep &= keep - 1;
-            const float2 w = lds_f2<Y::kWin>(sb + j * 8);
-            if (pf >= w.x && pf <= w.y) latch |= (latch_t)1 << j;
+    __device__ __forceinline__ int contact(const ScanArgs& A, int cls, float pf, int i, int day_off, int side) {
+        // latch + touch count (M:1562-1576): a latched level stays latched only while p is inside its own window, which is
+        // what the class mask says for every level at once (the touched level's own bit is in it)
+        int k;
+        latch_t win;
+        if (WIDE) {
+            const uint4 r = lds_u4<Y::kRec>(sb + (cls << 4));
+            k = (int)r.x; win = (latch_t)(((unsigned long long)r.w << 32) | r.z);
+        } else {
+            const unsigned long long r = lds_u64<Y::kRec>(sb + (cls << 3));
+            k = (int)(uint32_t)r; win = (latch_t)(r >> 32);
         }
+        const latch_t bit = (latch_t)1 << k;
+        const bool isnew = (latch & bit) == 0;
+        latch = (latch & win) | bit;
         const uint32_t ta = st + k * kTouchStride;
         uint32_t tc = touch_ld(ta);
         if (isnew) { tc = min(tc + 1u, 15u); touch_st(ta, tc); }
@@ -299,12 +302,12 @@ struct LeanEngine {
         const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         uint32_t v = lds_u8<Y::kCell>(sb + c);
         if (elig && v != kFar) {
-            if (v >= kMixBase) {                                  // the cell straddles a zone boundary
+            if (v >= A.mix_base) {                                // the cell straddles a class boundary
                 if (v == kMixed) {                                // several boundaries, or an end cell (price left the grid)
                     if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
                     else v = classify_zones(pf);
                 } else {
-                    const float2 r = lds_f2<Y::kMix>(sb + (v - kMixBase) * 8);
+                    const float2 r = lds_f2<Y::kRec>(sb + (v << Y::kRecShift));
                     const uint32_t lohi = (uint32_t)__float_as_int(r.y);
                     v = pf <= r.x ? (lohi & 0xffu) : (lohi >> 8);
                 }
@@ -317,16 +320,16 @@ struct LeanEngine {
         }
     }
 
-    // level whose contact zone holds p, or kFar: the cell byte of step(), fully resolved
+    // class of p (the argument contact() takes), or kFar: the cell byte of step(), fully resolved
     __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
         const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         uint32_t v = lds_u8<Y::kCell>(sb + c);
-        if (v >= kMixBase && v != kFar) {
+        if (v >= A.mix_base && v != kFar) {
             if (v == kMixed) {
                 if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
                 else v = classify_zones(pf);
             } else {
-                const float2 r = lds_f2<Y::kMix>(sb + (v - kMixBase) * 8);
+                const float2 r = lds_f2<Y::kRec>(sb + (v << Y::kRecShift));
                 const uint32_t lohi = (uint32_t)__float_as_int(r.y);
                 v = pf <= r.x ? (lohi & 0xffu) : (lohi >> 8);
             }
@@ -426,7 +429,7 @@ __device__ __forceinline__ void lean_scan_path(LeanEngine<MULTIDAY, HL, PARITY, 
 
 template <bool MULTIDAY, bool HL, bool PARITY, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kernel(const __grid_constant__ ScanArgs A) {
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
     LeanEngine<MULTIDAY, HL, PARITY, WIDE, SLOW, false, LEARN> E;
@@ -453,7 +456,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
 // first Philox group(s) are generated twice (one extra group per path, ~1 % of the generator work).
 template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     __syncthreads();
     LeanEngine<MULTIDAY, HL, false, WIDE, SLOW, false, LEARN> E;      // LEARN: QMMX_F_ONLINE_RETRAIN, heads in A.polw [14][A.pitch]
@@ -532,7 +535,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_gbm
 template <bool MULTIDAY, bool HL, bool WIDE, bool SLOW, bool LEARN = false>
 __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boot_kernel(const __grid_constant__ ScanArgs A, const BootDev g) {
     typedef LeanLayout<WIDE ? 64 : 32> Y;
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, WIDE ? 64 : 32>(A);
     {
         float* rb = reinterpret_cast<float*>(g_cell + Y::kBoot);
@@ -637,7 +640,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
                                                                      const __grid_constant__ SweepArgs W) {
     constexpr int LPAD = WIDE ? 64 : 32;
     typedef SweepLayout<LPAD> Z;
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<false, LPAD>(A);            // A.mlmask is null here: the gate table carries no logistic sign
     uint32_t* smask = reinterpret_cast<uint32_t*>(g_cell + Z::kSMask);
     double* sd = reinterpret_cast<double*>(g_cell + Z::kSD);

@@ -162,7 +162,7 @@ struct TileScan {
 
 template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_kernel(const __grid_constant__ ScanArgs A) {
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, 32>(A);
     __syncthreads();
     TileScan<MULTIDAY, SLOW, 0> T;
@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_kernel(const __grid
 template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_tma_kernel(const __grid_constant__ ScanArgs A,
                                                                          const __grid_constant__ CUtensorMap tmap) {
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, 32>(A);
     TileScan<MULTIDAY, SLOW, 0> T;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_tma_kernel(const __
 // Philox + Box-Muller + exp inside a loop whose other half runs at 15 active lanes), bars never leave the SM
 template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
-    block_setup(A);
+    block_setup(A, true);
     lean_setup<MULTIDAY, 32>(A);
     __syncthreads();
     TileScan<MULTIDAY, SLOW, 1> T;

@@ -9,6 +9,7 @@
 // bisects over the ordered set of fp32 values, so the kernels replace the O(L) float64 work by fp32
 // compares against exact thresholds and one shared-memory byte lookup.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 
 namespace qmmx {
@@ -16,7 +17,8 @@ namespace qmmx {
 constexpr int kThreads = 256;           // threads per CTA; one thread walks one path
 constexpr int kMaxLevels = 64;
 constexpr int kMaxCells = 32768;
-constexpr int kMaxZones = 272;
+constexpr int kMaxZones = 640;          // runs of the (finer) class partition as well as of the level partition
+constexpr int kMaxClasses = 254;        // class ids 0 .. ncls-1, single-boundary records ncls .. 0xFD, then kMixed, kFar
 constexpr int kMaxTables = 8;           // distinct (CONTACT_PROX, Q_MIN_PROB) pairs across the combos of one run
 constexpr int kMaxDays = 64;
 constexpr uint8_t kFar = 0xFF;
@@ -50,8 +52,23 @@ struct alignas(16) DevTables {          // arrays of DevTables: cell[] is copied
     float guard[4];
     float mixb[kMaxMixed];
     uint8_t mixlo[kMaxMixed], mixhi[kMaxMixed];
+    // ---- class partition (scan_lean.cuh / scan_tile.cuh): a class = (level touched, set of levels whose contact window
+    // holds p).  The second member is what the latch release of M:1572-1576 asks per latched neighbour; as a function of
+    // p it is piecewise constant, so one record per class replaces the per-neighbour window tests.  Same grid geometry as
+    // cell[]; ids: class c < ncls, single-boundary record ncls + m (p <= fmixb[id] ? fmixlo[id] : fmixhi[id], class ids
+    // or kFar), kMixed (zone search over fzhi / fzcls), kFar.  ncls < 0: the level set needs more than kMaxClasses
+    // classes or kMaxZones runs and the first-generation kernels run instead.
+    int32_t FZ, ncls, fnmixed, pad4;
+    float fzhi[kMaxZones];
+    uint8_t fzcls[kMaxZones];
+    alignas(16) uint8_t fcell[kMaxCells];
+    uint32_t cls_lev[256];              // level touched (class ids only)
+    uint32_t cls_mask_lo[256], cls_mask_hi[256];   // levels whose window holds p, the touched one included
+    float fmixb[256];
+    uint8_t fmixlo[256], fmixhi[256];
 };
 static_assert(sizeof(DevTables) % 16 == 0, "DevTables stride");
+static_assert(offsetof(DevTables, cell) % 16 == 0 && offsetof(DevTables, fcell) % 16 == 0, "cell tables are copied with 16-byte loads");
 
 struct DevCombo {                       // one parameter combination (qmmx_params, preprocessed)
     double sp, tp, qmin, prox, pmax, wr, wm;

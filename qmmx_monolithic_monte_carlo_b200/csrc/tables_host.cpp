@@ -48,7 +48,9 @@ struct Classifier {
 
 struct Zone { int32_t hi; int lev; };
 
-void refine(const Classifier& z, int64_t lo, int zlo, int64_t hi, int zhi, std::vector<Zone>& out) {
+using ClassFn = std::function<int(float)>;
+
+void refine(const ClassFn& z, int64_t lo, int zlo, int64_t hi, int zhi, std::vector<Zone>& out) {
     // invariant: z(lo) = zlo, z(hi) = zhi, lo < hi.  Emits (last ordinal of a run, its value) for every
     // change found in (lo, hi]; runs are assumed constant between probes that agree.
     if (zlo == zhi) return;
@@ -142,6 +144,7 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     if (L == 0) {
         T->Z = 1; T->zhi[0] = finf; T->zlev[0] = kFar;
         T->ncell = 1; T->shift = 0; T->obase = 0; T->cell[0] = kFar;
+        T->FZ = 1; T->fzhi[0] = finf; T->fzcls[0] = kFar; T->fcell[0] = kFar; T->ncls = 0;
         return 0;
     }
     const Classifier z{L, price, prox};
@@ -164,16 +167,19 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     std::sort(probes.begin(), probes.end());
     probes.erase(std::unique(probes.begin(), probes.end()), probes.end());
 
+    auto partition = [&](const ClassFn& cls, std::vector<Zone>& out) {
+        int64_t lo = probes[0];
+        int zlo = cls(o2f(lo));
+        for (size_t i = 1; i < probes.size(); ++i) {
+            const int64_t hi = probes[i];
+            const int zhi = cls(o2f(hi));
+            refine(cls, lo, zlo, hi, zhi, out);
+            lo = hi; zlo = zhi;
+        }
+        out.push_back({(int32_t)omax, zlo});
+    };
     std::vector<Zone> zones;
-    int64_t lo = probes[0];
-    int zlo = z(o2f(lo));
-    for (size_t i = 1; i < probes.size(); ++i) {
-        const int64_t hi = probes[i];
-        const int zhi = z(o2f(hi));
-        refine(z, lo, zlo, hi, zhi, zones);
-        lo = hi; zlo = zhi;
-    }
-    zones.push_back({(int32_t)omax, zlo});
+    partition([&](float pf) { return z(pf); }, zones);
     if ((int)zones.size() > kMaxZones) {
         if (err) *err = "level set produces too many price zones";
         return -1;
@@ -185,6 +191,38 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     }
     // +inf and NaN never compare <= a finite bound: the last zone is unbounded so the device search ends there
     T->zhi[T->Z - 1] = finf;
+
+    // class partition: (level touched, levels whose window holds p).  Window membership is the device's own test
+    // wlo <= p <= whi on the exact fp32 bounds found above, so a class mask IS what the per-neighbour loop would keep.
+    std::vector<std::pair<int, uint64_t>> classes;
+    auto class_of = [&](float pf) -> int {
+        const int k = z(pf);
+        if (k < 0) return -1;
+        uint64_t mask = 0;
+        for (int j = 0; j < L; ++j)
+            if (pf >= T->lev[j].wlo && pf <= T->lev[j].whi) mask |= 1ull << j;
+        const std::pair<int, uint64_t> key(k, mask);
+        for (size_t c = 0; c < classes.size(); ++c) if (classes[c] == key) return (int)c;
+        classes.push_back(key);
+        return (int)classes.size() - 1;
+    };
+    std::vector<Zone> fzones;
+    partition(class_of, fzones);
+    const bool fine_ok = (int)classes.size() <= kMaxClasses && (int)fzones.size() <= kMaxZones;
+    T->ncls = fine_ok ? (int)classes.size() : -1;
+    T->FZ = fine_ok ? (int)fzones.size() : 0;
+    if (fine_ok) {
+        for (int i = 0; i < T->FZ; ++i) {
+            T->fzhi[i] = o2f(fzones[i].hi);
+            T->fzcls[i] = fzones[i].lev < 0 ? kFar : (uint8_t)fzones[i].lev;
+        }
+        T->fzhi[T->FZ - 1] = finf;
+        for (size_t c = 0; c < classes.size(); ++c) {
+            T->cls_lev[c] = (uint32_t)classes[c].first;
+            T->cls_mask_lo[c] = (uint32_t)classes[c].second;
+            T->cls_mask_hi[c] = (uint32_t)(classes[c].second >> 32);
+        }
+    }
 
     // ---- grid over fp32 ordinals: full coverage of all windows when it fits at <= 64 ulps per cell,
     //      else the densest cluster of levels at 16 ulps per cell (prices outside resolve through the zones)
@@ -221,14 +259,15 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     const int ncell = (int)std::min<int64_t>(kMaxCells, ((o_hi - o_lo) >> shift) + 1);
     T->ncell = ncell; T->shift = shift; T->obase = (int32_t)o_lo;
 
-    auto zone_index = [&](int64_t o) {   // first zone whose upper ordinal >= o
-        int a = 0, b = (int)zones.size() - 1;
+    auto zone_index_in = [&](const std::vector<Zone>& zs, int64_t o) {   // first zone whose upper ordinal >= o
+        int a = 0, b = (int)zs.size() - 1;
         while (a < b) {
             const int m = (a + b) / 2;
-            if ((int64_t)zones[m].hi >= o) b = m; else a = m + 1;
+            if ((int64_t)zs[m].hi >= o) b = m; else a = m + 1;
         }
         return a;
     };
+    auto zone_index = [&](int64_t o) { return zone_index_in(zones, o); };
     for (int c = 0; c < ncell; ++c) {
         const int64_t c_lo = (c == 0) ? omin : o_lo + ((int64_t)c << shift);
         const int64_t c_hi = (c == ncell - 1) ? omax : o_lo + (((int64_t)c + 1) << shift) - 1;
@@ -239,6 +278,15 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
             T->mixb[m] = T->zhi[z0]; T->mixlo[m] = T->zlev[z0]; T->mixhi[m] = T->zlev[z1];
             T->cell[c] = (uint8_t)(kMixBase + m);
         } else T->cell[c] = kMixed;
+        if (fine_ok) {
+            const int f0 = zone_index_in(fzones, std::min(c_lo, omax)), f1 = zone_index_in(fzones, std::min(c_hi, omax));
+            if (f0 == f1) T->fcell[c] = T->fzcls[f0];
+            else if (f1 == f0 + 1 && T->ncls + T->fnmixed < (int)kMixed) {
+                const int id = T->ncls + T->fnmixed++;
+                T->fmixb[id] = T->fzhi[f0]; T->fmixlo[id] = T->fzcls[f0]; T->fmixhi[id] = T->fzcls[f1];
+                T->fcell[c] = (uint8_t)id;
+            } else T->fcell[c] = kMixed;
+        }
     }
     // guard intervals: the far zones that contain the ordinals just outside the grid
     {
@@ -257,6 +305,7 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     // scan_lean.cuh clamps with one unsigned min, which sends prices below the grid to the LAST cell: both end cells
     // must then resolve the same way (both far in the full-coverage case; else through the exact zone search)
     if (T->cell[0] != T->cell[ncell - 1]) { T->cell[0] = kMixed; T->cell[ncell - 1] = kMixed; }
+    if (fine_ok && T->fcell[0] != T->fcell[ncell - 1]) { T->fcell[0] = kMixed; T->fcell[ncell - 1] = kMixed; }
     return 0;
 }
 
@@ -329,6 +378,39 @@ int classify_tables(const DevTables* T, float p) {
         v = T->zlev[a];
     }
     return v == kFar ? -1 : (int)v;
+}
+
+// class lookup exactly as the lean / tile kernels do it: level touched (-1 = far) and the window mask
+int classify_tables_fine(const DevTables* T, float p, uint64_t* mask) {
+    *mask = 0;
+    if (T->ncls < 0) return -2;
+    int32_t bits;
+    std::memcpy(&bits, &p, 4);
+    uint8_t v = T->fcell[cell_of_bits(bits, T->obase, T->shift, T->ncell)];
+    if (v >= T->ncls && v < kMixed) v = p <= T->fmixb[v] ? T->fmixlo[v] : T->fmixhi[v];
+    else if (v == kMixed && ((p > T->guard[0] && p <= T->guard[1]) || (p > T->guard[2] && p <= T->guard[3]))) v = kFar;
+    else if (v == kMixed) {
+        int a = 0, b = T->FZ - 1;
+        while (a < b) {
+            const int m = (a + b) >> 1;
+            if (p <= T->fzhi[m]) b = m; else a = m + 1;
+        }
+        v = T->fzcls[a];
+    }
+    if (v == kFar) return -1;
+    *mask = ((uint64_t)T->cls_mask_hi[v] << 32) | T->cls_mask_lo[v];
+    return (int)T->cls_lev[v];
+}
+
+// float64 brute force of the same: nearest level within prox (first wins) and every level with |L - p| <= prox (M:1574)
+int classify_bruteforce_fine(int L, const double* price, double prox, float p, uint64_t* mask) {
+    *mask = 0;
+    if (L == 0) return -1;
+    const int k = Classifier{L, price, prox}(p);
+    if (k < 0) return -1;
+    for (int j = 0; j < L; ++j)
+        if (!(std::fabs(price[j] - (double)p) > prox)) *mask |= 1ull << j;
+    return k;
 }
 
 }  // namespace qmmx

@@ -11,6 +11,10 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
 int classify_bruteforce(int L, const double* price, double prox, float p);
 // the table lookup exactly as the kernels perform it (host mirror, for tests)
 int classify_tables(const DevTables* T, float p);
+// the class partition (tables.h): level touched (-1 far, -2 no class tables) and the levels whose contact window holds p,
+// through the tables as the lean / tile kernels read them, and by float64 brute force (M:1543-1545, M:1572-1576)
+int classify_tables_fine(const DevTables* T, float p, uint64_t* mask);
+int classify_bruteforce_fine(int L, const double* price, double prox, float p, uint64_t* mask);
 // compute_confidence (M:1415-1427) with direction known, plain IEEE float64
 double confidence_f64(double dist, bool solid, int tc, double prox);
 // host-evaluated sklearn-form LR gate: mask [n_lr][kMaxLevels], prob [n_lr][kMaxLevels][2][16] (or null)

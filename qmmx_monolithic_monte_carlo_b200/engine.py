@@ -83,6 +83,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_run_last_bars": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp]),
         "qmmx_run_last_bars_static": (C.c_int, [vp, vp, vp, i32, vp, vp, vp, vp, i32, vp, vp]),
         "qmmx_debug_classify": (C.c_int, [vp, vp, C.c_int, dbl, dbl, vp, i64, vp, vp, vp, vp, vp, vp]),
+        "qmmx_debug_class_partition": (C.c_int, [vp, vp, C.c_int, dbl, dbl, vp, vp, vp]),
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
         "qmmx_measure_fp32_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
@@ -491,3 +492,16 @@ def debug_classify(price, solid, prox, qmin, p):
     if rc != 0:
         raise QmmxError(rc, "qmmx_debug_classify")
     return out
+
+
+def debug_class_partition(price, solid, prox, qmin):
+    """(classes, runs, single-boundary records) of the class partition the lean / tile kernels read; classes = -1 when the
+    level set does not fit it (host only)."""
+    L = load_library()
+    price = np.ascontiguousarray(price, dtype=np.float64)
+    solid = np.ascontiguousarray(solid, dtype=np.uint8)
+    out = [C.c_int32(0) for _ in range(3)]
+    rc = L.qmmx_debug_class_partition(_ptr(price), _ptr(solid), len(price), float(prox), float(qmin), *[C.byref(o) for o in out])
+    if rc != 0:
+        raise QmmxError(rc, "qmmx_debug_class_partition")
+    return tuple(o.value for o in out)

@@ -71,6 +71,12 @@ def test_exact_tables_equal_float64_brute_force(lib, prox, qmin):
     p = np.concatenate(p + [np.array(edge), np.array([0, -1, 1e30, -1e30, np.inf])]).astype(np.float32)
     o = _check_tables(price, solid, prox, qmin, p)
     assert 0.1 < (o["level_brute"] >= 0).mean() < 0.7
+    # near_table above came from the class partition of the lean / tile kernels (one record per class of prices = touched
+    # level + the levels whose contact window holds the price), not from per-level window compares
+    ncls, nruns, nrec = E.debug_class_partition(price, solid, prox, qmin)
+    assert 30 <= ncls <= 254 and nruns >= ncls and 0 < nrec <= 254 - ncls
+    assert len({int(m) for m in o["near_brute"]}) <= ncls + 1
+    assert (np.array([bin(int(m)).count("1") for m in o["near_brute"]]) >= 2).any()      # 646.51 / 646.60 / 646.60 overlap
     # the duplicate 646.60 resolves to the FIRST level in load_levels order (black/solid[1])
     k = int(E.debug_classify(price, solid, prox, qmin, np.array([646.6], np.float32))["level_table"][0])
     assert (rows[k]["color"], rows[k]["type"], rows[k]["index"]) == ("black", "solid", 1)
@@ -87,6 +93,28 @@ def test_exact_tables_random_level_sets(levels, prox, qmin, seed):
     p = np.concatenate([rng.uniform(price.min() - 3 * prox, price.max() + 3 * prox, 4000),
                         np.repeat(price, 9) + np.tile(np.linspace(-1.2, 1.2, 9), len(price)) * prox]).astype(np.float32)
     _check_tables(price, solid, prox, qmin, p)
+
+
+def test_class_partition_dense_level_sets(lib):
+    """Level sets whose windows overlap heavily: up to 64 levels a cent or two apart with a window of +-0.5 (every level's
+    window holds dozens of others), duplicates included.  Either the class tables answer exactly like the float64 brute
+    force, or the set is reported as not fitting (classes = -1: the first-generation kernels run) and the per-level
+    windows answer."""
+    rng = np.random.default_rng(8)
+    fits = 0
+    for L, step, prox in ((64, 0.01, 0.5), (64, 0.05, 0.5), (48, 0.03, 0.2), (40, 0.2, 0.5), (64, 1.0, 0.4), (33, 0.0, 0.1)):
+        price = 100.0 + np.round(np.cumsum(rng.uniform(0, 2 * step, L)), 2)
+        dup = np.arange(7, L, 7)
+        price[dup] = price[dup - 1]                                                        # duplicates
+        solid = rng.integers(0, 2, L).astype(np.uint8)
+        grid = np.arange(price.min() - 2 * prox, price.max() + 2 * prox, 0.0007)
+        p = np.concatenate([grid, np.repeat(price, 5) + np.tile([-prox, -prox / 2, 0, prox / 2, prox], L)]).astype(np.float32)
+        p = np.concatenate([p, np.nextafter(p, np.float32(np.inf)), np.nextafter(p, np.float32(-np.inf))])
+        _check_tables(price, solid, prox, 0.6, p)
+        ncls, nruns, nrec = E.debug_class_partition(price, solid, prox, 0.6)
+        assert ncls == -1 or (1 <= ncls <= 254 and nruns <= 640)
+        fits += ncls > 0
+    assert fits >= 3
 
 
 def test_agg_flat_roundtrip():
