@@ -29,7 +29,10 @@
 namespace qmmx {
 
 constexpr int kRing = 32;                 // rows in the ring = bits in the masks
-constexpr int kChunk = 8;                 // rows staged per phase-1 pass
+#ifndef QMMX_TILE_CHUNK
+#define QMMX_TILE_CHUNK 8
+#endif
+constexpr int kChunk = QMMX_TILE_CHUNK;   // rows staged per phase-1 pass
 constexpr int kNoDir = 0x7ffffffe;        // `cool` of a flat path whose direction is still unknown (never eligible)
 constexpr int kRingBytes = kRing * 128;   // per warp
 

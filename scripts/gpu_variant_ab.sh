@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 for tag in "$@"; do
   lib=$PWD/qmmx_monolithic_monte_carlo_b200/libqmmx_mc_$tag.so
   [ "$tag" = base ] && lib=$PWD/qmmx_monolithic_monte_carlo_b200/libqmmx_mc.so
-  for w in c2 c3 c2hl; do
+  for w in ${WL:-c2 c3 c2hl}; do
     QMMX_LIB=$lib timeout 300 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu-baseline --no-e2e --no-sub > gpurun_out/ab_${tag}_$w.json 2> gpurun_out/ab_${tag}_$w.err || tail -3 gpurun_out/ab_${tag}_$w.err
     python -c "
 import json
