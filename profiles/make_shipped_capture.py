@@ -19,7 +19,7 @@ def main():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     git = subprocess.run(["git", "-C", root, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
     out = {"summary": os.path.relpath(path, root), "kernel": kernel, "git": git, "paths": paths, "steps": steps,
-           "kernel_ms_under_ncu": num("gpu__time_duration.sum"),
+           "kernel_ms_under_ncu": round(num("gpu__time_duration.sum") * {"ms": 1.0, "us": 1e-3, "ns": 1e-6, "s": 1e3}[kv["gpu__time_duration.sum"].split()[1]], 6),
            "dram_bytes": num("dram__bytes_read.sum") * unit("dram__bytes_read.sum") + num("dram__bytes_write.sum") * unit("dram__bytes_write.sum"),
            "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
            "warp_instructions_per_warp_step": round(num("smsp__inst_executed.sum") / warp_steps, 2),
