@@ -908,6 +908,40 @@ def test_gpu_wide_level_sets_first_generation_kernels(monkeypatch):
         v1.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
+def test_gpu_class_partition_at_capacity(eng, hl):
+    """64 levels ~0.2 apart with CONTACT_PROX 0.2: every window overlaps its neighbours', the class partition of the price
+    line (touched level + levels whose window holds the price) needs ~180 classes, the single-boundary records that are
+    left (254 - classes) run out and the remaining boundary cells resolve through the zone search.  Parity outputs,
+    aggregates and the fused kernel against the C oracle; 32 of the same levels on the tile-event kernel."""
+    rng = np.random.default_rng(8)
+    prices = 643.0 + np.round(np.cumsum(rng.uniform(0, 0.4, 64)), 2)
+    levels = [dict(color=("blue", "orange", "black", "teal")[i % 4], type="solid" if i % 3 else "dashed", index=i // 4,
+                   price=float(p)) for i, p in enumerate(prices)]
+    lr = np.array([[0.2, -0.5, -0.45, 0.35, 1.0]])
+    g = abi.make_gbm(sub_steps=4 if hl else 1)
+    for lv, overtouch in ((levels, 4), (levels[16:48], 6)):
+        rows, price, solid = E.sort_levels(lv)
+        ncls, nruns, nrec = E.debug_class_partition(price, solid, 0.2, 0.6)
+        assert ncls > 2.5 * len(price) and ncls + nrec <= 254
+        if len(price) == 64:
+            assert ncls + nrec == 254                      # capacity reached: some boundary cells use the zone search
+        P, T = 3001, 390
+        params = abi.make_params(contact_prox=0.2, cooldown_s=60, exit_on_hl=hl, overtouch_limit=overtouch)
+        configure(eng, price, solid, params, lr)
+        eng.gen_gbm(77, 3, P, T, g)
+        c, h, l = eng.download_bars(P, T, hl=hl)
+        res, tr, cnt, codes = eng.run_scan(trades=200, codes=True, paths_steps=(T, P))
+        o = CO.run_paths(c, price, solid, params, lr=lr, high=h, low=l, want_codes=True, max_trades=200, n_threads=8)
+        assert np.array_equal(codes, o["codes"])
+        assert_trades_equal(tr, cnt, o["trades"], o["counts"])
+        assert_agg_equal(res[0].agg, o["agg"])
+        assert_agg_equal(eng.run_scan()[0].agg, o["agg"])                                  # aggregate-only kernels (tile for 32 levels)
+        assert_agg_equal(eng.run_fused_gbm(77, 3, P, T, g)[0].agg, o["agg"], sums_rel=1e-9)
+        assert o["agg"].n_trades > 100 and o["agg"].n_trade_overflow == 0
+
+
 # ---- tile-event kernels (scan_tile.cuh): the production close-only scan and fused GBM kernels -----------------------
 TILE_CASES = [
     # (paths, steps, params, days, mode, cents, sigma)
