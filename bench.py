@@ -478,6 +478,24 @@ def sub_lines(args, eng, stream, rank, local_rank, world, torch, dist, D):
                              "value": Pp * world * STEPS_PER_PATH / (ms * 1e-3), "unit": UNIT, "ms": ms, "scaling": "weak",
                              "n_trades": res[0].n_trades, "online_policy_skips": res[0].entry_hist["ONLINE_POLICY"]}
     eng.set_policy(None)
+    # ---- c2hl: C2 with OHLC bars and exits on the bar's high / low (12 B per path-step; lockstep lean kernel) ------
+    Ph = args.paths or 1_000_000
+    eng.set_params(abi.make_params(contact_prox=0.10, cooldown_s=120, exit_on_hl=True))
+    eng.gen_gbm(F.HOST_SEED, rank * Ph, Ph, STEPS_PER_PATH, abi.make_gbm(sub_steps=4))
+    eng.run_scan_async()
+    hl_ms = [_timed(eng, stream, world, local_rank, torch, dist, D, eng.run_scan_async) for _ in range(5)]
+    ms = float(np.median(hl_ms))
+    res = eng.fetch_agg()
+    peak, peak_src = measured_peak_hbm()
+    gbs = 12.0 * Ph * STEPS_PER_PATH / (ms * 1e-3) / 1e9
+    out["c2hl"] = {"workload": f"C2-HL: {Ph} device GBM OHLC paths x 390 per GPU (4 sub-steps per bar), exits on bar high/low, "
+                               "stop before target (M:3621-3636); bars 4.68 GB per GPU, larger than L2",
+                   "value": Ph * world * STEPS_PER_PATH / (ms * 1e-3), "unit": UNIT, "ms": ms, "scaling": "weak",
+                   "n_trades": res[0].n_trades,
+                   "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                                "algorithmic_bytes_per_launch": 12.0 * Ph * STEPS_PER_PATH, "peak_source": peak_src,
+                                "kernel": "lean_scan_kernel<0, 1, 0, 0, 0, 0> (lockstep; the tile-event form was measured and loses, DESIGN.md section 8)",
+                                "timing": "median of 5 launches, CUDA events on the launching stream"}}
     # ---- c4: 256-combo sweep over resident bars (weak: 1M paths per GPU) ----------------------------------------
     P4 = args.paths or 1_000_000
     grid = [abi.make_params(contact_prox=0.10, stop_padding=0.10 + 0.05 * i, tp_padding=tp, cooldown_s=cd)
