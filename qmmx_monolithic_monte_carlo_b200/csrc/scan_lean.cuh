@@ -53,11 +53,15 @@ struct LeanLayout {
     static constexpr int kRec = kPrice + LPAD * 8;
     static constexpr int kMask = kRec + (256 << kRecShift);          // uint32 [kSmemDays][LPAD]: per-day logistic masks (MULTIDAY)
     static constexpr int kEnd = kMask + kSmemDays * LPAD * 4;
-    static constexpr int kBoot = kEnd;                               // float [3][kMaxWindow]: bootstrap return ratios (fused bootstrap only)
+    // exits on high/low only (lockstep kernels; the tile kernels end at kEnd): {double +-exit price, uint32 c_exit increment}
+    // per [level][side][low hit][high hit], 16 bytes each -- the stop/target level an exit pays (M:3636), negated for a short
+    static constexpr int kExit = (kEnd + 15) & ~15;
+    static constexpr int kEndExit = kExit + LPAD * 8 * 16;
+    static constexpr int kBoot = kEndExit;                           // float [3][kMaxWindow]: bootstrap return ratios (fused bootstrap only)
     static constexpr int kEndBoot = kBoot + 3 * kMaxWindow * 4;
     static_assert(kGate % 16 == 0 && kTouch % 16 == 0 && kPrice % 8 == 0 && kRec % 16 == 0, "alignment");
 };
-inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEnd : (size_t)LeanLayout<32>::kEnd; }
+inline size_t lean_smem_bytes(int L) { return L > 32 ? (size_t)LeanLayout<64>::kEndExit : (size_t)LeanLayout<32>::kEndExit; }
 
 // -DQMMX_DEBUG_BOUNDS (build.py build_library(defines=...)): every shared-memory access of the lean and tile kernels
 // is checked against the kernel's dynamic window and its natural alignment, a violation traps (compute-sanitizer is
@@ -104,7 +108,7 @@ __device__ __forceinline__ void touch_st(uint32_t a, uint32_t v) { smem_chk(a, 1
 // The sign encoding needs every non-empty confidence interval to have a positive upper bound (prices are
 // positive) -- checked on the host before a lean kernel is chosen (qmmx_mc.cu lean_ok).
 template <bool MULTIDAY, int LPAD>
-__device__ inline void lean_setup(const ScanArgs& A) {
+__device__ inline void lean_setup(const ScanArgs& A, bool exit_table = true) {
     typedef LeanLayout<LPAD> Y;
     const DevTables* __restrict__ T = A.tables;
     const float inf = __int_as_float(0x7f800000);
@@ -135,6 +139,19 @@ __device__ inline void lean_setup(const ScanArgs& A) {
         if (LPAD > 32) reinterpret_cast<uint4*>(g_cell + Y::kRec)[v] = r;
         else reinterpret_cast<uint2*>(g_cell + Y::kRec)[v] = make_uint2(r.x, r.y);
     }
+    if (exit_table && (A.combo.flags & QMMX_F_EXIT_ON_HL)) {      // not for the tile and sweep kernels: other data lives past kEnd there
+        // stop is tested first (M:3621-3636): a long stops on the low, a short on the high
+        for (int t = threadIdx.x; t < LPAD * 8; t += blockDim.x) {
+            const int k = t >> 3, side = (t >> 2) & 1, lo = (t >> 1) & 1, hi = t & 1;
+            const bool is_stop = side ? hi != 0 : lo != 0;
+            const double lp = k < A.n_levels ? T->lev[k].price : 0.0;
+            double px;
+            if (side == 0) px = is_stop ? lp - A.combo.sp : lp + A.combo.tp;
+            else px = is_stop ? lp + A.combo.sp : lp - A.combo.tp;
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(side ? -px : px);
+            reinterpret_cast<uint4*>(g_cell + Y::kExit)[t] = make_uint4((uint32_t)bits, (uint32_t)(bits >> 32), is_stop ? 1u : 0x10000u, 0u);
+        }
+    }
     if (MULTIDAY && A.mlmask && A.n_days <= kSmemDays) {
         uint32_t* mk = reinterpret_cast<uint32_t*>(g_cell + Y::kMask);
         for (int t = threadIdx.x; t < A.n_days * LPAD; t += blockDim.x) mk[t] = A.mlmask[(t / LPAD) * kMaxLevels + (t % LPAD)];
@@ -164,6 +181,7 @@ struct LeanEngine {
     float entry_s;         // entry price, sign flipped for a short: pnl = (+-exit) - entry_s
     uint32_t sgn;          // 0 long, 0x80000000 short
     int pos, entry_bar;    // level | side << 8 (stale when flat); entry_bar is only read in PARITY mode
+    uint32_t xoff;         // HL: byte offset of this position's (level, side) rows of the exit table
     uint32_t inc_lo;       // c_exit increment of an exit through the LOW threshold: 1 (stop, long) or 0x10000 (target, short)
     int a_inpos;           // sum of (exit bar - entry bar) = steps coded IN_POSITION (M:1508), kept as running -entry +exit
     latch_t latch;
@@ -176,7 +194,7 @@ struct LeanEngine {
     __device__ __forceinline__ void reset(uint32_t sb_, int64_t path_) {
         path = path_;
         sb = sb_; st = sb_ + Y::kTouch + threadIdx.x;
-        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry_s = 0.f; sgn = 0u; entry_bar = 0; inc_lo = 1u; a_inpos = 0;
+        prev = 0.f; d = 0.f; cool = 0; pos = -1; entry_s = 0.f; sgn = 0u; entry_bar = 0; inc_lo = 1u; a_inpos = 0; xoff = 0u;
         lo_thr = __int_as_float(0xff800000); hi_thr = __int_as_float(0x7f800000);
         latch = 0; c_gate = c_ml = c_exit = c_span = c_dir = 0u;
         pnl = 0.0; pnl2 = 0.0; mtm = 0.0; ntr = 0;
@@ -201,7 +219,15 @@ struct LeanEngine {
             tp = (double)xs - (double)entry_s;
             win = xs > entry_s;                                   // pnl > 0 (label, M:1936), decided on the fp32 operands
             c_exit += hit_lo ? inc_lo : (inc_lo ^ 0x10001u);      // exactly one threshold is hit by a single price
-        } else {                                                  // exit at the stop/target level itself (M:3636)
+        } else if (!SWEEP) {                                      // exit at the stop/target level itself (M:3636), from the exit table
+            // +-exit price (negated for a short, as entry_s is): pnl = (+-exit) - entry_s, exactly exit - entry or entry - exit
+            const uint4 r = lds_u4<Y::kExit>(sb + xoff + (hit_lo ? 32u : 0u) + (hit_hi ? 16u : 0u));
+            const double sx = __longlong_as_double((long long)(((unsigned long long)r.y << 32) | r.x));
+            tp = sx - (double)entry_s;
+            win = tp > 0;
+            c_exit += r.z;
+            if (PARITY) exit_f = (float)(is_short ? -sx : sx);
+        } else {                                                  // the sweep kernel: this lane's own paddings
             const double lp = lds_f64<Y::kPrice>(sb + (pos & 0xff) * 8);
             double exit_px;
             if (!is_short) exit_px = is_stop ? lp - sp_(A) : lp + tp_(A);
@@ -276,6 +302,7 @@ struct LeanEngine {
             hi_thr = __double2float_ru(side == 0 ? lp + l_tp : lp + l_sp);
         } else { lo_thr = g.z; hi_thr = g.w; }                    // M:1669-1674
         pos = k | (side << 8);
+        if (HL && !SWEEP) xoff = (uint32_t)(k * 2 + side) << 6;
         sgn = (uint32_t)side << 31;
         entry_s = __int_as_float(__float_as_int(pf) ^ sgn);
         inc_lo = side ? 0x10000u : 1u;
@@ -641,7 +668,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) lean_sweep_kernel(const __gri
     constexpr int LPAD = WIDE ? 64 : 32;
     typedef SweepLayout<LPAD> Z;
     block_setup(A, true);
-    lean_setup<false, LPAD>(A);            // A.mlmask is null here: the gate table carries no logistic sign
+    lean_setup<false, LPAD>(A, false);     // A.mlmask is null here: the gate table carries no logistic sign; exits use the lane's own paddings
     uint32_t* smask = reinterpret_cast<uint32_t*>(g_cell + Z::kSMask);
     double* sd = reinterpret_cast<double*>(g_cell + Z::kSD);
     uint32_t* su = reinterpret_cast<uint32_t*>(g_cell + Z::kSU);

@@ -166,7 +166,7 @@ struct TileScan {
 template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_kernel(const __grid_constant__ ScanArgs A) {
     block_setup(A, true);
-    lean_setup<MULTIDAY, 32>(A);
+    lean_setup<MULTIDAY, 32>(A, false);
     __syncthreads();
     TileScan<MULTIDAY, SLOW, 0> T;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -227,7 +227,7 @@ template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_tma_kernel(const __grid_constant__ ScanArgs A,
                                                                          const __grid_constant__ CUtensorMap tmap) {
     block_setup(A, true);
-    lean_setup<MULTIDAY, 32>(A);
+    lean_setup<MULTIDAY, 32>(A, false);
     TileScan<MULTIDAY, SLOW, 0> T;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t sb = __shfl_sync(0xffffffffu, (uint32_t)__cvta_generic_to_shared(g_cell), 0);
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(kLeanThreads, 1) tile_scan_tma_kernel(const __
 template <bool MULTIDAY, bool SLOW>
 __global__ void __launch_bounds__(kLeanThreads, 1) tile_fused_gbm_kernel(const __grid_constant__ ScanArgs A, const GbmDev g) {
     block_setup(A, true);
-    lean_setup<MULTIDAY, 32>(A);
+    lean_setup<MULTIDAY, 32>(A, false);
     __syncthreads();
     TileScan<MULTIDAY, SLOW, 1> T;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
