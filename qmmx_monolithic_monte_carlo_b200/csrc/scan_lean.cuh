@@ -29,6 +29,9 @@ namespace qmmx {
 #define QMMX_LEAN_THREADS 1024
 #define QMMX_LEAN_BLOCKS 1
 #endif
+#ifndef QMMX_LEAN_U
+#define QMMX_LEAN_U 2                 // rows per half of the register double buffer of the lockstep scan (2 * U rows in flight)
+#endif
 constexpr int kLeanThreads = QMMX_LEAN_THREADS;
 constexpr int kLeanBlocksPerSM = QMMX_LEAN_BLOCKS;
 constexpr int kLeanWarps = kLeanThreads / 32;
@@ -221,7 +224,10 @@ struct LeanEngine {
             c_exit += hit_lo ? inc_lo : (inc_lo ^ 0x10001u);      // exactly one threshold is hit by a single price
         } else if (!SWEEP) {                                      // exit at the stop/target level itself (M:3636), from the exit table
             // +-exit price (negated for a short, as entry_s is): pnl = (+-exit) - entry_s, exactly exit - entry or entry - exit
-            const uint4 r = lds_u4<Y::kExit>(sb + xoff + (hit_lo ? 32u : 0u) + (hit_hi ? 16u : 0u));
+            uint32_t xa = sb + xoff;
+            if (hit_lo) xa += 32u;
+            if (hit_hi) xa += 16u;
+            const uint4 r = lds_u4<Y::kExit>(xa);
             const double sx = __longlong_as_double((long long)(((unsigned long long)r.y << 32) | r.x));
             tp = sx - (double)entry_s;
             win = tp > 0;
@@ -470,7 +476,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_scan_kern
         const int64_t path = tile * 32 + lane;
         const bool active = path < A.paths;
         E.reset(sb, path);
-        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, 2, LEARN>(E, A, path); E.finish(A); }
+        if (active) { lean_scan_path<MULTIDAY, HL, PARITY, WIDE, SLOW, QMMX_LEAN_U, LEARN>(E, A, path); E.finish(A); }
         __syncwarp();
         warp_accumulate(active, E.pnl, E.pnl2, E.mtm, E.c_gate, E.c_ml, E.c_exit, E.c_span, E.c_dir, active && E.is_open());
     }
