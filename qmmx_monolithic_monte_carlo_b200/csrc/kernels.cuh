@@ -270,15 +270,13 @@ __global__ void __launch_bounds__(kThreads) gen_bootstrap_kernel(float* __restri
         const uint64_t gid = g.path_offset + (uint64_t)q;
         float S = g.s0;
         uint4 x = make_uint4(0, 0, 0, 0);
-        int start = 0, off = 0, blk = 0;
+        int idx = 0, off = 0, blk = 0;          // idx = (start + off) mod nret, kept as a running circular index (no division per bar)
         for (int i = 0; i < steps; ++i) {
             if (off == 0) {
                 if ((blk & 3) == 0) x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), (uint32_t)(blk >> 2), 1u), g.k0, g.k1);
                 const uint32_t r = (blk & 3) == 0 ? x.x : (blk & 3) == 1 ? x.y : (blk & 3) == 2 ? x.z : x.w;
-                start = (int)__umulhi(r, (uint32_t)g.nret);
-            }
-            int idx = start + off;
-            idx %= g.nret;
+                idx = (int)__umulhi(r, (uint32_t)g.nret);
+            } else if (++idx == g.nret) idx = 0;
             const size_t o = (size_t)i * pitch + q;
             if (high) __stcs(high + o, __fmul_rn(S, rh[idx]));
             if (low) __stcs(low + o, __fmul_rn(S, rl[idx]));

@@ -591,16 +591,14 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boo
         if (active) {
             const uint64_t gid = g.path_offset + (uint64_t)path;
             uint4 x = make_uint4(0, 0, 0, 0);
-            int start = 0, off = 0, blk = 0;
+            int idx = 0, off = 0, blk = 0;                   // idx = (start + off) mod nret as a running circular index
             float S = g.s0;
-            auto draw = [&](float& hi, float& lo) {          // one bar: advances (S, off, blk)
+            auto draw = [&](float& hi, float& lo) {          // one bar: advances (S, idx, off, blk)
                 if (off == 0) {
                     if ((blk & 3) == 0) x = philox4x32_10(make_uint4((uint32_t)gid, (uint32_t)(gid >> 32), (uint32_t)(blk >> 2), 1u), g.k0, g.k1);
                     const uint32_t r = (blk & 3) == 0 ? x.x : (blk & 3) == 1 ? x.y : (blk & 3) == 2 ? x.z : x.w;
-                    start = (int)__umulhi(r, (uint32_t)nret);
-                }
-                int idx = start + off;
-                idx %= nret;
+                    idx = (int)__umulhi(r, (uint32_t)nret);
+                } else if (++idx == nret) idx = 0;
                 const uint32_t a = sb + (uint32_t)idx * 4u;
                 if (HL) { hi = __fmul_rn(S, lds_f32<Y::kBoot>(a)); lo = __fmul_rn(S, lds_f32<Y::kBoot + kMaxWindow * 4>(a)); }
                 S = __fmul_rn(S, lds_f32<Y::kBoot + 2 * kMaxWindow * 4>(a));
@@ -614,7 +612,7 @@ __global__ void __launch_bounds__(kLeanThreads, kLeanBlocksPerSM) lean_fused_boo
                     if (i == 0) p0 = S; else if (S != p0) j0 = i;
                 }
                 E.prologue(p0, j0);
-                S = g.s0; start = 0; off = 0; blk = 0;
+                S = g.s0; idx = 0; off = 0; blk = 0;
             }
             DayTracker<MULTIDAY> day;
             day.init(A);
