@@ -53,6 +53,9 @@ struct ScanArgs {
     uint32_t cell_lim;                                 // (ncell << shift) - 1: cell = min(bits - obase, cell_lim) >> shift (one add-min + one shift)
     float guard[4];                                    // far zones adjoining the grid (tables.h DevTables::guard)
     uint32_t mix_base;                                 // class partition: cell bytes >= mix_base are not class ids (tables.h DevTables::ncls)
+    int32_t n_out;                                     // class runs outside the grid (tables.h DevTables::n_out), < 0: use the zone search
+    float grid_lo, grid_hi, out_lo[4], out_hi[4];
+    uint32_t out_cls[4];
     int32_t cell_bytes;                                // dynamic shared memory reserved for the cell bytes (scan_lean.cuh carves the rest)
     unsigned int* tile_counter;                        // scan_tile.cuh: next unclaimed 32-path tile of this launch (zeroed by init_flat_kernel)
     DevCombo combo;

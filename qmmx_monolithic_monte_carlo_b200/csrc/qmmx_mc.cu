@@ -38,7 +38,7 @@ struct qmmx_ctx {
     bool dirty = true;
     // derived device state
     DevTables* d_tables = nullptr; int n_tables = 0; int max_ncell = 1;
-    struct CellGrid { int32_t obase, shift, ncell; float guard[4]; int32_t ncls; };
+    struct CellGrid { int32_t obase, shift, ncell; float guard[4]; int32_t ncls; int32_t n_out; float grid_lo, grid_hi, out_lo[4], out_hi[4]; uint32_t out_cls[4]; };
     std::vector<CellGrid> grids;
     std::vector<DevCombo> h_combos;
     uint32_t* d_mlmask = nullptr; double* d_mlprob = nullptr; double* d_pol = nullptr;
@@ -181,7 +181,9 @@ int prepare(qmmx_ctx* ctx) {
     ctx->n_tables = (int)tabs.size();
     ctx->max_ncell = 1;
     ctx->grids.clear();
-    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); ctx->grids.push_back({t.obase, t.shift, t.ncell, {t.guard[0], t.guard[1], t.guard[2], t.guard[3]}, t.ncls}); }
+    for (auto& t : tabs) { ctx->max_ncell = std::max(ctx->max_ncell, t.ncell); qmmx_ctx::CellGrid G{t.obase, t.shift, t.ncell, {t.guard[0], t.guard[1], t.guard[2], t.guard[3]}, t.ncls, t.n_out, t.grid_lo, t.grid_hi, {}, {}, {}};
+        for (int j = 0; j < kMaxOut; ++j) { G.out_lo[j] = t.out_lo[j]; G.out_hi[j] = t.out_hi[j]; G.out_cls[j] = t.out_cls[j]; }
+        ctx->grids.push_back(G); }
     ctx->lean_ok = true;       // every non-empty confidence interval must have a positive upper bound (sign encoding)
     for (auto& t : tabs) if (t.ncls < 0) ctx->lean_ok = false;      // and the class partition must fit one byte (tables.h)
     for (auto& t : tabs)
@@ -247,6 +249,11 @@ void fill_args(qmmx_ctx* ctx, ScanArgs& A, int c, const float* cl, const float* 
     A.cell_bytes = (int32_t)scan_smem_bytes(ctx);
     for (int g = 0; g < 4; ++g) A.guard[g] = ctx->grids[D.table].guard[g];
     A.mix_base = (uint32_t)std::max(0, ctx->grids[D.table].ncls);
+    {
+        const qmmx_ctx::CellGrid& G = ctx->grids[D.table];
+        A.n_out = G.n_out; A.grid_lo = G.grid_lo; A.grid_hi = G.grid_hi;
+        for (int j = 0; j < kMaxOut; ++j) { A.out_lo[j] = G.out_lo[j]; A.out_hi[j] = G.out_hi[j]; A.out_cls[j] = G.out_cls[j]; }
+    }
     A.combo = D;
 }
 

@@ -337,8 +337,7 @@ struct LeanEngine {
         if (elig && v != kFar) {
             if (v >= A.mix_base) {                                // the cell straddles a class boundary
                 if (v == kMixed) {                                // several boundaries, or an end cell (price left the grid)
-                    if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
-                    else v = classify_zones(pf);
+                    v = resolve_mixed(A, pf);
                 } else {
                     const float2 r = lds_f2<Y::kRec>(sb + (v << Y::kRecShift));
                     const uint32_t lohi = (uint32_t)__float_as_int(r.y);
@@ -353,12 +352,28 @@ struct LeanEngine {
         }
     }
 
+    // a kMixed cell: the far zones next to the grid, then the few class runs outside the grid (a price that wandered off:
+    // bootstrap paths drift for days), then the zone search (interior cells with several boundaries)
+    __device__ __forceinline__ uint32_t resolve_mixed(const ScanArgs& A, float pf) const {
+        if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) return kFar;
+        if (A.n_out >= 0 && (pf < A.grid_lo || pf > A.grid_hi)) {
+            uint32_t v = kFar;
+#pragma unroll
+            for (int j = 0; j < kMaxOut; ++j) if (pf >= A.out_lo[j] && pf <= A.out_hi[j]) v = A.out_cls[j];
+            return v;
+        }
+        return classify_zones(pf);
+    }
+
     // class of p (the argument contact() takes), or kFar: the cell byte of step(), fully resolved
     __device__ __forceinline__ uint32_t classify(const ScanArgs& A, float pf) const {
         const uint32_t c = min((uint32_t)(__float_as_int(pf) - A.cell_obase), A.cell_lim) >> A.cell_shift;
         uint32_t v = lds_u8<Y::kCell>(sb + c);
         if (v >= A.mix_base && v != kFar) {
             if (v == kMixed) {
+                // tile-event and sweep kernels: without the list of class runs outside the grid (their prices rarely leave it, and
+                // the longer inline form costs the close-only tile kernel 1.3 % through the register allocation of its rounds;
+                // an out-of-line call costs 9 %)
                 if ((pf > A.guard[0] && pf <= A.guard[1]) || (pf > A.guard[2] && pf <= A.guard[3])) v = kFar;
                 else v = classify_zones(pf);
             } else {

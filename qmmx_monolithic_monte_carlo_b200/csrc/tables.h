@@ -66,7 +66,16 @@ struct alignas(16) DevTables {          // arrays of DevTables: cell[] is copied
     uint32_t cls_mask_lo[256], cls_mask_hi[256];   // levels whose window holds p, the touched one included
     float fmixb[256];
     uint8_t fmixlo[256], fmixhi[256];
+    // prices that leave the grid (both end cells are kMixed when levels lie outside it): p < grid_lo or p > grid_hi is far
+    // unless out_lo[j] <= p <= out_hi[j] for one of the n_out class runs outside the grid (class out_cls[j]).
+    // n_out < 0: more than kMaxOut such runs -- the zone search answers.
+    int32_t n_out, pad5[3];
+    float grid_lo, grid_hi;             // first fp32 value of cell 1, last fp32 value of cell ncell - 2
+    float out_lo[4], out_hi[4];
+    uint32_t out_cls[4];
+    uint32_t pad6[2];
 };
+constexpr int kMaxOut = 4;
 static_assert(sizeof(DevTables) % 16 == 0, "DevTables stride");
 static_assert(offsetof(DevTables, cell) % 16 == 0 && offsetof(DevTables, fcell) % 16 == 0, "cell tables are copied with 16-byte loads");
 

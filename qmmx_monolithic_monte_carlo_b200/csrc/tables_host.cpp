@@ -306,6 +306,32 @@ int build_tables(int L, const double* price, const uint8_t* solid, double prox, 
     // must then resolve the same way (both far in the full-coverage case; else through the exact zone search)
     if (T->cell[0] != T->cell[ncell - 1]) { T->cell[0] = kMixed; T->cell[ncell - 1] = kMixed; }
     if (fine_ok && T->fcell[0] != T->fcell[ncell - 1]) { T->fcell[0] = kMixed; T->fcell[ncell - 1] = kMixed; }
+    // class runs outside the interior cells (levels the grid does not cover): a short list instead of the zone search
+    T->n_out = -1;
+    if (fine_ok && ncell >= 3 && o_lo >= 0) {
+        const int64_t g_lo = o_lo + ((int64_t)1 << shift), g_hi = o_lo + (((int64_t)ncell - 1) << shift) - 1;   // interior ordinals
+        int n = 0;
+        bool fits = true;
+        int64_t run_lo = omin;
+        for (size_t zi = 0; zi < fzones.size() && fits; ++zi) {
+            const int64_t run_hi = fzones[zi].hi;
+            if (fzones[zi].lev >= 0) {
+                const int64_t parts[2][2] = {{run_lo, std::min(run_hi, g_lo - 1)}, {std::max(run_lo, g_hi + 1), run_hi}};
+                for (int s2 = 0; s2 < 2 && fits; ++s2) {
+                    if (parts[s2][0] > parts[s2][1]) continue;
+                    if (n == kMaxOut) { fits = false; break; }
+                    T->out_lo[n] = o2f(parts[s2][0]); T->out_hi[n] = o2f(parts[s2][1]); T->out_cls[n] = (uint32_t)fzones[zi].lev;
+                    ++n;
+                }
+            }
+            run_lo = run_hi + 1;
+        }
+        if (fits) {
+            T->n_out = n;
+            T->grid_lo = o2f(g_lo); T->grid_hi = o2f(g_hi);
+            for (int j = n; j < kMaxOut; ++j) { T->out_lo[j] = finf; T->out_hi[j] = -finf; T->out_cls[j] = kFar; }
+        }
+    }
     return 0;
 }
 
@@ -389,7 +415,10 @@ int classify_tables_fine(const DevTables* T, float p, uint64_t* mask) {
     uint8_t v = T->fcell[cell_of_bits(bits, T->obase, T->shift, T->ncell)];
     if (v >= T->ncls && v < kMixed) v = p <= T->fmixb[v] ? T->fmixlo[v] : T->fmixhi[v];
     else if (v == kMixed && ((p > T->guard[0] && p <= T->guard[1]) || (p > T->guard[2] && p <= T->guard[3]))) v = kFar;
-    else if (v == kMixed) {
+    else if (v == kMixed && T->n_out >= 0 && (p < T->grid_lo || p > T->grid_hi)) {
+        v = kFar;
+        for (int j = 0; j < T->n_out; ++j) if (p >= T->out_lo[j] && p <= T->out_hi[j]) v = (uint8_t)T->out_cls[j];
+    } else if (v == kMixed) {
         int a = 0, b = T->FZ - 1;
         while (a < b) {
             const int m = (a + b) >> 1;
