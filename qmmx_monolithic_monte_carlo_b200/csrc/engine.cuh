@@ -43,7 +43,7 @@ struct ScanArgs {
     unsigned long long* flat;                                   // reduction buffer of this combo
     const uint32_t* mlmask;       // [n_days][kMaxLevels]: bit side*16+tc = ML gate FAILS; null = gate off / no model
     const double* mlprob;         // [n_days][kMaxLevels][2][16] P(win) for blend mode; null when unused
-    const double* pol;            // [n_pol][3][7]
+    const double* pol;            // [n_pol][3][7], then [n_pol][3]: sum of |w| per head
     double z_go, z_skip;          // sigmoid(z) >= 0.60 <=> z >= z_go ; sigmoid(z) < 0.55 <=> z < z_skip
     double hist_lo, hist_inv_w;
     // parity-mode outputs (may be null)
@@ -230,21 +230,41 @@ __device__ __noinline__ bool policy_passes(const ScanArgs* A, int k, float pf, i
     const int spd = A->combo.spd;
     const double lp = g_S.cold[k].price;
     const double pa = fabs((double)pf - lp);
-    const double tod = (double)(i % spd) / 390.0;
+    const int day = i < spd ? 0 : i / spd;                                   // one division, and none on the first day
+    const double tod = (double)(i - day * spd) / 390.0;
     const double x1 = pa < 1.0 ? pa : 1.0;
     const double x3 = side == 1 ? 1.0 : 0.0, x4 = side == 0 ? 1.0 : 0.0;
-    const double x5 = (g_S.cold[k].flags & kLvConfl06) ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
-    const int day = i / spd;
-    const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * (day < A->n_pol ? day : A->n_pol - 1);
-    double z_side;
+    const bool confl = (g_S.cold[k].flags & kLvConfl06) != 0;
+    const double x5 = confl ? 1.0 : 0.0, x6 = tod < 1.0 ? tod : 1.0;
+    const int dsel = day < A->n_pol ? day : A->n_pol - 1;
+    const double* w = A->pol + QMMX_POLICY_HEADS * QMMX_POLICY_DIM * dsel;
+    // Fast path: the plain float64 sum of the same products differs from CPython's compensated sum by at most a few
+    // roundings of the partial sums, each below 2^-53 * sum|w| (every |x| <= 1), so outside a band of 2^-48 * sum|w|
+    // around the threshold both sums are on the same side of it; inside the band (practically never) the exact sum decides.
+    const double* sabs = A->pol + (size_t)QMMX_POLICY_HEADS * QMMX_POLICY_DIM * A->n_pol + QMMX_POLICY_HEADS * dsel;
+    auto plain = [&](const double* q) { return q[0] + q[1] * x1 + (side == 1 ? q[3] : q[4]) + (confl ? q[5] : 0.0) + q[6] * x6; };
+    const double band = 3.552713678800501e-15;                              // 2^-48
+    bool go;
     if (LEARNT) {
         double wl[QMMX_POLICY_DIM];
 #pragma unroll
         for (int q = 0; q < QMMX_POLICY_DIM; ++q) wl[q] = A->polw[(size_t)(side * QMMX_POLICY_DIM + q) * (size_t)A->pitch + (size_t)path];
-        z_side = dot_py312(wl, x1, x3, x4, x5, x6);
-    } else z_side = dot_py312(w + QMMX_POLICY_DIM * side, x1, x3, x4, x5, x6);
-    const double z_sk = dot_py312(w + QMMX_POLICY_DIM * 2, x1, x3, x4, x5, x6);
-    const bool pass = (z_side >= A->z_go) && (z_sk < A->z_skip);
+        go = dot_py312(wl, x1, x3, x4, x5, x6) >= A->z_go;
+    } else {
+        const double* q = w + QMMX_POLICY_DIM * side;
+        const double z = plain(q), b = sabs[side] * band;
+        if (z >= A->z_go + b) go = true;
+        else if (z < A->z_go - b) go = false;
+        else go = dot_py312(q, x1, x3, x4, x5, x6) >= A->z_go;
+    }
+    bool pass = false;
+    if (go) {                                                                // the skip head matters only when the go head passes
+        const double* q = w + QMMX_POLICY_DIM * 2;
+        const double z = plain(q), b = sabs[2] * band;
+        if (z < A->z_skip - b) pass = true;
+        else if (z >= A->z_skip + b) pass = false;
+        else pass = dot_py312(q, x1, x3, x4, x5, x6) < A->z_skip;
+    }
     if (!pass) smem_inc(&g_S.u[U_ENTRY + QMMX_ONLINE_POLICY]);
     return pass;
 }

@@ -210,7 +210,16 @@ int prepare(qmmx_ctx* ctx) {
         if ((rc = upload_vec(ctx, &ctx->d_mlmask, mask.data(), mask.size())) != 0) return rc;
         if (any_prob && (rc = upload_vec(ctx, &ctx->d_mlprob, prob.data(), prob.size())) != 0) return rc;
     }
-    if ((rc = upload_vec(ctx, &ctx->d_pol, ctx->pol.data(), ctx->pol.size())) != 0) return rc;
+    {   // policy table [n_pol][3][7], followed by the sum of |w| per (day, head): the error bound of the gate's fast path (engine.cuh)
+        std::vector<double> pol(ctx->pol);
+        for (int d = 0; d < ctx->n_pol; ++d)
+            for (int h = 0; h < QMMX_POLICY_HEADS; ++h) {
+                double sa = 0.0;
+                for (int q = 0; q < QMMX_POLICY_DIM; ++q) sa += std::fabs(ctx->pol[((size_t)d * QMMX_POLICY_HEADS + h) * QMMX_POLICY_DIM + q]);
+                pol.push_back(sa);
+            }
+        if ((rc = upload_vec(ctx, &ctx->d_pol, pol.data(), pol.size())) != 0) return rc;
+    }
     if (ctx->flat_combos < nc) {
         if (ctx->d_flat) cudaFree(ctx->d_flat);
         ctx->d_flat = nullptr;

@@ -908,6 +908,52 @@ def test_gpu_wide_level_sets_first_generation_kernels(monkeypatch):
         v1.close()
 
 
+def _sigmoid_threshold(target):
+    """smallest float64 z with 1 / (1 + exp(-z)) >= target, as the library derives it (M:20-26 with libm exp)"""
+    import math
+    sig = lambda x: 1.0 / (1.0 + math.exp(-x))
+    lo, hi = -50.0, 50.0
+    while True:
+        mid = lo + (hi - lo) / 2
+        if mid <= lo or mid >= hi:
+            break
+        if sig(mid) >= target:
+            hi = mid
+        else:
+            lo = mid
+    while sig(math.nextafter(hi, -math.inf)) >= target:
+        hi = math.nextafter(hi, -math.inf)
+    return hi
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bump", [-1, 0, 1], ids=["below", "at", "above"])
+def test_gpu_policy_gate_at_the_threshold(eng, bump):
+    """The OnlinePolicy gate (M:3083-3085) decides on a plain float64 sum when that sum is clear of the threshold by more
+    than its rounding band and on CPython's compensated sum inside the band.  Heads whose only non-zero weight is the bias
+    put EVERY evaluation inside the band: bias = the go threshold (0.60) or one ulp either side, skip bias = the skip
+    threshold (0.55) or one ulp either side; the oracle evaluates the sigmoids themselves."""
+    import math
+    z_go, z_sk = _sigmoid_threshold(0.60), _sigmoid_threshold(0.55)
+    step = lambda z, n: z if n == 0 else math.nextafter(z, math.inf if n > 0 else -math.inf)
+    rows, price, solid = E.sort_levels(F.levels_30())
+    close = F.host_gbm_closes(3000, 390, seed=91)
+    params = abi.make_params(contact_prox=0.1, cooldown_s=120, disable_policy_gate=False)
+    outcomes = []
+    for go_n, sk_n in ((bump, -1), (1, bump)):
+        pol = np.zeros((1, 3, 7))
+        pol[0, 0, 0] = pol[0, 1, 0] = step(z_go, go_n)
+        pol[0, 2, 0] = step(z_sk, sk_n)
+        configure(eng, price, solid, params, None, pol)
+        eng.upload_bars(close)
+        a = eng.run_scan()[0]
+        o = CO.run_paths(close, price, solid, params, policy=pol, n_threads=4)
+        assert_agg_equal(a.agg, o["agg"])
+        outcomes.append((a.n_trades > 0, a.entry_hist["ONLINE_POLICY"] > 0))
+    # go head: passes at and above its threshold (>= 0.60); skip head: passes strictly below its threshold (< 0.55)
+    assert outcomes[0] == ((bump >= 0), (bump < 0)) and outcomes[1] == ((bump < 0), (bump >= 0))
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("hl", [False, True], ids=["close", "hl"])
 def test_gpu_class_partition_at_capacity(eng, hl):
