@@ -322,15 +322,6 @@ struct JitterArgs {
     double* out_total; double* out_dd; int32_t* out_wins; int32_t* out_losses; int32_t* out_opens;
 };
 
-__device__ __forceinline__ void box_muller_f64(uint32_t a, uint32_t b, double& z0, double& z1) {
-    const double u1 = ((double)a + 0.5) * 2.3283064365386963e-10;
-    const double u2 = ((double)b + 0.5) * 2.3283064365386963e-10;
-    const double r = sqrt(-2.0 * log(u1));
-    double s, c;
-    sincospi(2.0 * u2, &s, &c);
-    z0 = r * c; z1 = r * s;
-}
-
 __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     double* sh = reinterpret_cast<double*>(smem_raw);
@@ -343,17 +334,21 @@ __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
         double eq = 0.0, peak = 0.0, max_dd = 0.0;
         int wins = 0, losses = 0, opens = 0;
         for (int ci = 0; ci < A.n_cand; ++ci) {
-            double nz[4], uni;
+            double nz[4], uni = 0.0;
             if (A.replay_normals) {
                 const double* r = A.replay_normals + ((size_t)t * A.n_cand + ci) * 4;
                 nz[0] = r[0]; nz[1] = r[1]; nz[2] = r[2]; nz[3] = r[3];
                 uni = A.replay_uniforms[(size_t)t * A.n_cand + ci];
             } else {
+                // Philox mode is the statistical tier (the reference draws from a Mersenne Twister): the normals come from the
+                // fp32 Box-Muller of the bar generators (MUFU lg2 / sqrt / sin / cos; jitter sigmas of cents make 1e-7 relative
+                // immaterial), the walk stays float64.  The tie uniform (stream 3 of the same counter) is drawn only when a bar
+                // reaches stop and target at once.
                 const uint4 x = philox4x32_10(make_uint4((uint32_t)gt, (uint32_t)(gt >> 32), (uint32_t)ci, 2u), A.k0, A.k1);
-                box_muller_f64(x.x, x.y, nz[0], nz[1]);
-                box_muller_f64(x.z, x.w, nz[2], nz[3]);
-                const uint4 y = philox4x32_10(make_uint4((uint32_t)gt, (uint32_t)(gt >> 32), (uint32_t)ci, 3u), A.k0, A.k1);
-                uni = ((double)y.x * 4294967296.0 + (double)y.y) * 5.421010862427522e-20;   // [0, 1)
+                float zf[4];
+                box_muller(x.x, x.y, zf[0], zf[1]);
+                box_muller(x.z, x.w, zf[2], zf[3]);
+                nz[0] = (double)zf[0]; nz[1] = (double)zf[1]; nz[2] = (double)zf[2]; nz[3] = (double)zf[3];
             }
             const int side = A.cand_side[ci];
             const double lvl_j = A.cand_level[ci] + nz[0] * A.sig[0];                    // M:3453
@@ -371,6 +366,10 @@ __global__ void __launch_bounds__(kThreads) jitter_kernel(const JitterArgs A) {
                 const bool stop_hit = (side == 0) ? (ll <= stop) : (hh >= stop);
                 const bool target_hit = (side == 0) ? (hh >= target) : (ll <= target);
                 if (stop_hit && target_hit) {
+                    if (!A.replay_normals) {
+                        const uint4 y = philox4x32_10(make_uint4((uint32_t)gt, (uint32_t)(gt >> 32), (uint32_t)ci, 3u), A.k0, A.k1);
+                        uni = ((double)y.x * 4294967296.0 + (double)y.y) * 5.421010862427522e-20;   // [0, 1)
+                    }
                     double up_span = hh - entry; if (!(up_span > 0.0)) up_span = 0.0;
                     double down_span = entry - ll; if (!(down_span > 0.0)) down_span = 0.0;
                     const double p_target_first = up_span / (up_span + down_span + 1e-9);
