@@ -778,6 +778,23 @@ def main():
         peak, peak_src = measured_peak_hbm()
         k_ms = float(np.mean(kernel_ms))
         cap = shipped_capture()
+        # the binding resource against a MEASURED ceiling: warp instructions per second of the scan (instruction counts of
+        # the committed capture of the same kernel on the same workload / the launch time measured in this run) next to
+        # what LOP3-only and LOP3 + FFMA probe kernels reach on this device in this run
+        issue = None
+        try:
+            alu_probe, mixed_probe = eng.measure_issue_peak()
+            if cap and paths == cap.get("paths") and cap.get("inst_executed"):
+                tot = cap["inst_executed"] / (k_ms * 1e-3) / 1e9
+                alu = cap["alu_inst_executed"] / (k_ms * 1e-3) / 1e9
+                issue = {"unit": "1e9 warp-instructions/s, whole device",
+                         "alu_pipe": {"achieved": alu, "probe": alu_probe, "frac": alu / alu_probe},
+                         "all_pipes": {"achieved": tot, "probe_alu_plus_fma": mixed_probe, "frac": tot / mixed_probe},
+                         "probe_source": "qmmx_measure_issue_peak: LOP3-only and LOP3 + FFMA kernels, this run"}
+            else:
+                issue = {"unit": "1e9 warp-instructions/s, whole device", "probe_alu": alu_probe, "probe_alu_plus_fma": mixed_probe}
+        except Exception as e:      # an older library without the probe
+            issue = {"error": str(e)}
         alg_bytes = 4.0 * paths * STEPS_PER_PATH
         achieved = alg_bytes / (k_ms * 1e-3) / 1e9
         line = {
@@ -797,6 +814,7 @@ def main():
                                            "warp_instructions_per_warp_step": (cap or {}).get("warp_instructions_per_warp_step"),
                                            "active_lanes_per_instruction": (cap or {}).get("active_lanes_per_instruction"),
                                            "alu_pipe_pct": (cap or {}).get("alu_pipe_pct"),
+                                           "measured_issue_rates": issue,
                                            "source": "committed ncu capture of the shipped build: %s at git %s (not re-measured per run)" %
                                                      ((cap or {}).get("summary"), (cap or {}).get("git"))}},
             "roofline_fp32": fp32_roofline(eng, paths * STEPS_PER_PATH / (k_ms * 1e-3), 12),

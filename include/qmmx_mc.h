@@ -347,6 +347,11 @@ int  qmmx_last_timing(qmmx_ctx* ctx, float* ms);
 /* FP32 FFMA throughput of this device in TFLOP/s, measured now with an FMA-only kernel (best of 3 after a warm-up).
  * The denominator of the FP32/issue roofline that SURVEY 8(d) asks for beside the HBM one; no reference counterpart. */
 int  qmmx_measure_fp32_peak(qmmx_ctx* ctx, double* tflops);
+/* Issue-rate probes of this device, measured now (best of 3 after a warm-up), in 1e9 warp-instructions per second over the
+ * whole device: *alu = a kernel of independent LOP3 chains (the ALU pipe: integer, logic, compare, select, shift -- the pipe
+ * the scan kernels keep busiest); *mixed = the same chains interleaved one-to-one with FFMA chains (ALU + FMA pipes fed
+ * together).  The ceilings `bench.py` quotes next to the scan's own instruction rates.  No reference counterpart. */
+int  qmmx_measure_issue_peak(qmmx_ctx* ctx, double* alu_gwips, double* mixed_gwips);
 /* number of kernel launches issued by this ctx since creation */
 int  qmmx_launch_count(qmmx_ctx* ctx, uint64_t* n);
 

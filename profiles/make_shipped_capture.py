@@ -21,6 +21,8 @@ def main():
     out = {"summary": os.path.relpath(path, root), "kernel": kernel, "git": git, "paths": paths, "steps": steps,
            "kernel_ms_under_ncu": round(num("gpu__time_duration.sum") * {"ms": 1.0, "us": 1e-3, "ns": 1e-6, "s": 1e3}[kv["gpu__time_duration.sum"].split()[1]], 6),
            "dram_bytes": num("dram__bytes_read.sum") * unit("dram__bytes_read.sum") + num("dram__bytes_write.sum") * unit("dram__bytes_write.sum"),
+           "inst_executed": num("smsp__inst_executed.sum"), "alu_inst_executed": num("sm__inst_executed_pipe_alu.sum"),
+           "fma_inst_executed": num("sm__inst_executed_pipe_fma.sum"),
            "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
            "warp_instructions_per_warp_step": round(num("smsp__inst_executed.sum") / warp_steps, 2),
            "active_lanes_per_instruction": num("smsp__thread_inst_executed_per_inst_executed.ratio"),

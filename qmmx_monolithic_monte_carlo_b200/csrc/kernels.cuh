@@ -545,4 +545,31 @@ __global__ void __launch_bounds__(1024, 1) fp32_probe_kernel(float* out, int ite
     out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// ---- issue-rate probes for the scan kernels' binding resources (round-1 verdict: "a measured issue-rate probe, not a
+// nominal figure").  MODE 0: 16 independent chains of three-input logic ops (LOP3, the ALU pipe: integer / logic / compare /
+// select / shift, which the scans keep ~73 % busy).  MODE 1: the same chains interleaved one-to-one with FFMA chains (the FMA
+// pipe, where ptxas also places IMAD moves and adds): what one SM partition can issue when both pipes are fed.
+template <int MODE>
+__global__ void __launch_bounds__(1024, 1) issue_probe_kernel(uint32_t* out, int iters, uint32_t a, uint32_t b, float fa, float fb) {
+    uint32_t x[16];
+    float y[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { x[k] = threadIdx.x * 2654435761u + k; y[k] = (float)(threadIdx.x + k) * 1e-3f; }
+#pragma unroll 1
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(x[k]) : "r"(a), "r"(b));     // x ^= a ^ b, one LOP3
+                if (MODE == 1) y[k] = __fmaf_rn(y[k], fa, fb);
+            }
+    }
+    uint32_t s = 0u;
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { s ^= x[k]; t += y[k]; }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s ^ __float_as_uint(t);
+}
+
 }  // namespace qmmx

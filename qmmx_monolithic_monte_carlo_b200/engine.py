@@ -87,6 +87,7 @@ def load_library(path: Optional[str] = None):
         "qmmx_last_timing": (C.c_int, [vp, C.POINTER(C.c_float)]),
         "qmmx_launch_count": (C.c_int, [vp, C.POINTER(u64)]),
         "qmmx_measure_fp32_peak": (C.c_int, [vp, C.POINTER(C.c_double)]),
+        "qmmx_measure_issue_peak": (C.c_int, [vp, vp, vp]),
         "qmmx_download_policy_weights": (C.c_int, [vp, vp, i64]),
     }
     for name, (res, args) in protos.items():
@@ -469,6 +470,12 @@ class MCEngine:
         v = C.c_double()
         self._ck(self._L.qmmx_measure_fp32_peak(self._h, C.byref(v)))
         return float(v.value)
+
+    def measure_issue_peak(self):
+        """(ALU-pipe, ALU + FMA) issue-rate probes of this device in 1e9 warp-instructions per second (measured now)."""
+        a, m = C.c_double(0.0), C.c_double(0.0)
+        self._ck(self._L.qmmx_measure_issue_peak(self._h, C.byref(a), C.byref(m)))
+        return a.value, m.value
 
     def launch_count(self) -> int:
         n = C.c_uint64()
